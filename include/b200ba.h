@@ -1,0 +1,150 @@
+/* b200ba.h -- C ABI of libb200ba.so, the B200 (sm_100a) bundle-adjustment engine.
+ *
+ * The reference (hammershock/SFM-Python) has no FFI; its boundary for this path is two Python
+ * imports in sfm_lite/sfm.py (":8" scipy.optimize.least_squares, ":20" compute_residuals /
+ * create_sparsity_matrix) used only at sfm_lite/sfm.py:264-268.  The entry points below are what
+ * a ctypes binding of that boundary needs; each one names the reference interface it replaces.
+ * Plain pointers and sizes only, no C++ or torch types.  All arithmetic is IEEE double.
+ *
+ * Conventions
+ *   x          parameter vector of sfm.py:255-257 / bundle_adjustment.py:38-39:
+ *              [ w0(3) T0(3) ... w_{C-1} T_{C-1} | X0(3) ... X_{P-1}(3) ],  6*C + 3*P doubles.
+ *   cam_idx    dense camera index per observation (sfm.py:256), 0 <= cam_idx < C.
+ *   pt_idx     point index per observation (sfm.py:249); any order is accepted, point-major
+ *              (non-decreasing, graph.py:186-191) is the fast path.
+ *   uv         observed pixels, N x 2 row-major doubles (the Python wrapper converts the int64
+ *              pixels of graph.py:112-113 exactly as numpy's promotion at bundle_adjustment.py:41).
+ *   K          3x3 intrinsics, row-major, all nine entries used (bundle_adjustment.py:27).
+ *   residuals  (2N) interleaved [du0,dv0,du1,dv1,...], projected - observed, in the CALLER's
+ *              observation order (bundle_adjustment.py:41).
+ *
+ * Return value: 0 = OK, negative = b200ba_status; b200ba_last_error(h) gives the message.
+ * No entry point keeps a caller pointer after it returns.  A handle is not re-entrant; different
+ * handles may be used from different threads (the reference calls BA from a Tk worker thread,
+ * app.py:84,109), every entry sets its CUDA device itself.
+ */
+#ifndef B200BA_H
+#define B200BA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200ba_handle b200ba_handle;
+
+enum b200ba_status {
+  B200BA_OK = 0,
+  B200BA_BAD_ARG = -1,
+  B200BA_CUDA = -2,
+  B200BA_NCCL = -3,
+  B200BA_NOT_FINITE = -4,
+  B200BA_OOM = -5,
+  B200BA_INDEX_RANGE = -6,
+  B200BA_NO_PROBLEM = -7
+};
+
+enum b200ba_solver { B200BA_SOLVER_AUTO = 0, B200BA_SOLVER_PCG = 1, B200BA_SOLVER_CHOLESKY = 2 };
+
+/* Options of b200ba_solve.  ftol/xtol/gtol/max_nfev have the meaning of the same-named keyword
+ * arguments of scipy.optimize.least_squares as called at sfm.py:266-268 (ftol = --ba_tol,
+ * main.py:36; xtol = gtol = 1e-8 scipy defaults; max_nfev <= 0 means 100 * n like scipy's TRF). */
+typedef struct b200ba_options {
+  double ftol;
+  double xtol;
+  double gtol;
+  int64_t max_nfev;
+  int32_t verbose;        /* 0 silent, 1 termination line, 2 per-iteration table (scipy's columns) */
+  int32_t solver;         /* b200ba_solver */
+  double lambda0;         /* initial Marquardt damping, <= 0 -> 1e-4 */
+  double pcg_rtol;        /* relative residual of the reduced-camera PCG, <= 0 -> 1e-6 */
+  int32_t pcg_max_iter;   /* <= 0 -> 500 */
+  int32_t fixed_iters;    /* > 0: run exactly this many LM iterations, ignoring the tolerances (benchmarks) */
+} b200ba_options;
+
+/* Result of b200ba_solve: the fields of scipy's OptimizeResult that parity tooling reads. */
+typedef struct b200ba_result {
+  double cost;            /* 0.5 * sum(r^2) at the returned x (whole job, all ranks) */
+  double initial_cost;
+  double optimality;      /* ||J^T r||_inf at the returned x */
+  double rms;             /* sqrt(mean(r^2)) */
+  double lambda_final;
+  int64_t nfev;           /* residual evaluations (1 + trial steps) */
+  int64_t njev;           /* linearisations */
+  int32_t status;         /* scipy codes: 0 max_nfev, 1 gtol, 2 ftol, 3 xtol, 4 ftol and xtol */
+  int32_t n_iter;         /* LM iterations (accepted + rejected) */
+  int64_t pcg_iters;      /* total PCG iterations */
+  double solve_ms;        /* device time of the LM loop (CUDA events) */
+} b200ba_result;
+
+/* Device-time counters, milliseconds / launches accumulated since b200ba_reset_stats. */
+typedef struct b200ba_stats {
+  double ms_cam_prep, ms_linearize_points, ms_camera_blocks, ms_schur, ms_allreduce, ms_camera_solve,
+      ms_backsub_trial, ms_residual;
+  int64_t launches;       /* kernels launched by this library */
+  int64_t n_linearize, n_pcg_iters;
+  int64_t schur_entries, schur_blocks;
+  int64_t bytes_device;   /* device memory held by the handle */
+} b200ba_stats;
+
+int b200ba_version(void);
+
+/* One handle = one GPU (one rank).  device = CUDA ordinal. */
+int b200ba_create(b200ba_handle** out, int device);
+int b200ba_destroy(b200ba_handle* h);
+const char* b200ba_last_error(const b200ba_handle* h);
+
+/* Multi-GPU (one process per GPU): rank 0 calls b200ba_nccl_unique_id, the host broadcasts the
+ * 128 bytes (torch.distributed), every rank calls b200ba_comm_init.  The reference has no
+ * collective; this is the all-reduce of the reduced camera system. */
+int b200ba_nccl_unique_id(void* id128);
+int b200ba_comm_init(b200ba_handle* h, const void* id128, int rank, int nranks);
+
+/* Replaces the argument packing of sfm.py:248-261 + create_sparsity_matrix (bundle_adjustment.py:6-17):
+ * copies the observation arrays to the device, builds the point-major SoA layout, the camera-sorted
+ * permutation and the Schur pair lists.  n_pts is the number of points THIS handle owns (its shard);
+ * pt_idx is local to the shard.  With a communicator attached this call is collective. */
+int b200ba_set_problem(b200ba_handle* h, int64_t n_cam, int64_t n_pts, int64_t n_obs, const int64_t* cam_idx,
+                       const int64_t* pt_idx, const double* uv, const double* K);
+
+/* compute_residuals (bundle_adjustment.py:35-42).  x, r_out (2N, may be NULL), cost_out (may be NULL) on the host. */
+int b200ba_residuals(b200ba_handle* h, const double* x, double* r_out, double* cost_out);
+/* same with DEVICE pointers (torch tensor .data_ptr()); r_out_dev may be NULL */
+int b200ba_residuals_dev(b200ba_handle* h, const double* x_dev, double* r_out_dev, double* cost_out);
+
+/* Analytic replacement of scipy's finite-difference Jacobian (sfm.py:266 jac='2-point' + jac_sparsity):
+ * Jc N x 2 x 6 ([d/dw | d/dT]), Jp N x 2 x 3, caller's observation order, host buffers. */
+int b200ba_jacobian_blocks(b200ba_handle* h, const double* x, double* Jc, double* Jp);
+/* device-pointer variant used by the residual+Jacobian sweep (config E); also writes r_dev (2N) if not NULL */
+int b200ba_jacobian_blocks_dev(b200ba_handle* h, const double* x_dev, double* r_dev, double* Jc_dev, double* Jp_dev);
+
+/* One linearisation: residual, Jacobian blocks, J^T J / J^T r blocks, point-block Schur elimination.
+ * Outputs (host, each may be NULL): S dense 6C x 6C row-major (only for n_cam <= 512), b (6C),
+ * grad (6C + 3P) = J^T r, cost.  With a communicator the reduced system is all-reduced. */
+int b200ba_normal_equations(b200ba_handle* h, const double* x, double lambda, double* S_out, double* b_out,
+                            double* grad_out, double* cost_out);
+/* device-resident linearisation only (benchmark leg): x_dev on the device, nothing copied back. */
+int b200ba_linearize_dev(b200ba_handle* h, const double* x_dev, double lambda);
+/* One damped step from x: delta (6C + 3P), predicted reduction, cost at x + delta (host buffers; test hook). */
+int b200ba_lm_step(b200ba_handle* h, const double* x, double lambda, int solver, double* delta_out,
+                   double* predicted_out, double* new_cost_out);
+
+/* Replaces scipy.optimize.least_squares at sfm.py:266-268: Levenberg-Marquardt on x_inout (host). */
+int b200ba_solve(b200ba_handle* h, double* x_inout, const b200ba_options* opt, b200ba_result* out);
+/* same with x resident on the device */
+int b200ba_solve_dev(b200ba_handle* h, double* x_inout_dev, const b200ba_options* opt, b200ba_result* out);
+
+int b200ba_get_stats(b200ba_handle* h, b200ba_stats* out);
+int b200ba_reset_stats(b200ba_handle* h);
+/* stream the library launches on (so callers can record CUDA events around its kernels) */
+void* b200ba_stream(b200ba_handle* h);
+
+/* Test hook: copy an internal device array to the host.  name in {"V","gp","U","gc","pp","Sup","blk_keys",
+ * "delta_c","rr","Y"}; returns the number of doubles (or int64 for keys) written, or a negative status. */
+int64_t b200ba_debug_fetch(b200ba_handle* h, const char* name, void* out, int64_t capacity_bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200BA_H */

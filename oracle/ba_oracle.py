@@ -1,0 +1,360 @@
+"""CPU oracle for the bundle-adjustment hot path.  TEST INFRASTRUCTURE ONLY.
+
+This module is the checker, never the product: only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline / ``--impl reference``
+legs may import it.  The product (``sfm-python_b200``) never routes through it
+and raises when its CUDA library is missing.
+
+It restates, in numpy, the algorithm of the reference path
+
+* ``sfm_lite/bundle_adjustment.py:20-32``  project_points   -> :func:`project_points_loop`
+* ``sfm_lite/bundle_adjustment.py:35-42``  compute_residuals -> :func:`residuals_loop`,
+  :func:`residuals` (vectorised twin, O1' in SURVEY.md section 8c)
+* ``sfm_lite/bundle_adjustment.py:6-17``   create_sparsity_matrix -> :func:`sparsity`
+* ``sfm_lite/sfm.py:266-268``              the scipy call -> :func:`scipy_solve`
+
+and adds the analytic pieces the CUDA engine implements (Jacobian blocks,
+normal equations, point-block Schur complement, a reference LM loop) so that
+every kernel has a numpy twin to be compared with.
+
+Parity pinning: the reference ships no tests or golden vectors for this path
+(SURVEY.md section 4), so the oracle is pinned against OUTPUTS OF THE REFERENCE
+ITSELF: ``oracle/make_golden.py`` imports ``/root/reference/sfm_lite/
+bundle_adjustment.py`` by path, evaluates it on seeded problems and on the
+frozen SceauxCastle BA dumps and commits the vectors under ``tests/golden/``;
+``tests/test_oracle.py`` checks every function below against those vectors.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+# --------------------------------------------------------------------------
+# Rodrigues / rotation-vector helpers
+# --------------------------------------------------------------------------
+
+_SMALL = 1e-4  # series switch-over for a=(1-cos t)/t^2, b=(t-sin t)/t^3
+
+
+def rodrigues(rvec):
+    """Rotation matrices for an (n,3) array of rotation vectors.
+
+    Same map as ``scipy.spatial.transform.Rotation.from_rotvec(...).as_matrix()``
+    used at ``bundle_adjustment.py:25`` (agrees to <= 7e-16):
+    R = I + s [w]x + a [w]x^2 with s = sin(t)/t, a = (1-cos t)/t^2.
+    """
+    w = np.atleast_2d(np.asarray(rvec, dtype=np.float64))
+    t2 = np.einsum("ij,ij->i", w, w)
+    t = np.sqrt(t2)
+    small = t < _SMALL
+    ts = np.where(small, 1.0, t)
+    s = np.where(small, 1.0 - t2 / 6.0 + t2 * t2 / 120.0, np.sin(ts) / ts)
+    # 1-cos t = 2 sin^2(t/2): avoids the cancellation of the naive form
+    a = np.where(small, 0.5 - t2 / 24.0 + t2 * t2 / 720.0, 2.0 * np.sin(0.5 * ts) ** 2 / (ts * ts))
+    Wx = skew(w)
+    W2 = Wx @ Wx
+    R = np.eye(3)[None] + s[:, None, None] * Wx + a[:, None, None] * W2
+    return R
+
+
+def skew(v):
+    v = np.atleast_2d(np.asarray(v, dtype=np.float64))
+    z = np.zeros(len(v))
+    return np.stack(
+        [
+            np.stack([z, -v[:, 2], v[:, 1]], -1),
+            np.stack([v[:, 2], z, -v[:, 0]], -1),
+            np.stack([-v[:, 1], v[:, 0], z], -1),
+        ],
+        -2,
+    )
+
+
+def right_jacobian(rvec):
+    """J_r(w) = I - a [w]x + b [w]x^2 (right Jacobian of SO(3)); d(R(w)Y)/dw = -R [Y]x J_r."""
+    w = np.atleast_2d(np.asarray(rvec, dtype=np.float64))
+    t2 = np.einsum("ij,ij->i", w, w)
+    t = np.sqrt(t2)
+    small = t < _SMALL
+    ts = np.where(small, 1.0, t)
+    a = np.where(small, 0.5 - t2 / 24.0 + t2 * t2 / 720.0, 2.0 * np.sin(0.5 * ts) ** 2 / (ts * ts))
+    b = np.where(small, 1.0 / 6.0 - t2 / 120.0 + t2 * t2 / 5040.0, (ts - np.sin(ts)) / (ts * ts * ts))
+    Wx = skew(w)
+    return np.eye(3)[None] - a[:, None, None] * Wx + b[:, None, None] * (Wx @ Wx)
+
+
+# --------------------------------------------------------------------------
+# Residual (reference: bundle_adjustment.py:20-42)
+# --------------------------------------------------------------------------
+
+def unpack(x, n_cameras, n_points):
+    """``x`` layout of sfm.py:255-257 / bundle_adjustment.py:38-39."""
+    x = np.asarray(x, dtype=np.float64)
+    cams = x[: 6 * n_cameras].reshape(n_cameras, 6)
+    pts = x[6 * n_cameras: 6 * n_cameras + 3 * n_points].reshape(n_points, 3)
+    return cams, pts
+
+
+def project_points_loop(points, camera_params, K):
+    """Per-observation restatement of bundle_adjustment.py:20-32 (one 3x4 matrix per observation).
+
+    Deliberately keeps the reference's cost structure (a Python loop and a scipy
+    ``Rotation`` per observation) because it doubles as the timed "port" CPU
+    baseline of bench.py.
+    """
+    from scipy.spatial.transform import Rotation
+
+    K = np.asarray(K, dtype=np.float64)
+    out = np.empty((len(points), 2))
+    for n in range(len(points)):
+        cam = camera_params[n]
+        R = Rotation.from_rotvec(cam[:3]).as_matrix()
+        M = K @ np.column_stack((R, -(R @ cam[3:6])))       # K [R | -R T]
+        ph = M @ np.array([points[n][0], points[n][1], points[n][2], 1.0])
+        out[n, 0] = ph[0] / ph[2]
+        out[n, 1] = ph[1] / ph[2]
+    return out
+
+
+def residuals_loop(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
+    """Faithful (slow) restatement of bundle_adjustment.py:35-42."""
+    cams, pts = unpack(x, n_cameras, n_points)
+    proj = project_points_loop(pts[point_indices], cams[camera_indices], K)
+    return (proj - points_2d).ravel()
+
+
+def residuals(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
+    """Vectorised twin of :func:`residuals_loop`: r = pi(K R(w)(X - T)) - uv, interleaved (2N,)."""
+    cams, pts = unpack(x, n_cameras, n_points)
+    K = np.asarray(K, dtype=np.float64)
+    R = rodrigues(cams[:, :3])
+    ci = np.asarray(camera_indices)
+    pi = np.asarray(point_indices)
+    Y = pts[pi] - cams[ci, 3:6]
+    Z = np.einsum("nij,nj->ni", R[ci], Y)
+    p = Z @ K.T
+    proj = p[:, :2] / p[:, 2:3]
+    return (proj - np.asarray(points_2d)).ravel()
+
+
+def sparsity(n_cameras, n_points, n_obs, camera_indices, point3d_indices, fixed_camera_indices=()):
+    """0/1 Jacobian structure of bundle_adjustment.py:6-17 as CSR (built without the Python loop)."""
+    from scipy.sparse import csr_matrix
+
+    ci = np.asarray(camera_indices, dtype=np.int64)
+    pi = np.asarray(point3d_indices, dtype=np.int64)
+    assert len(ci) == len(pi)
+    obs = np.arange(n_obs, dtype=np.int64)
+    free = ~np.isin(ci, np.asarray(list(fixed_camera_indices), dtype=np.int64))
+    rows, cols = [], []
+    for r in range(2):
+        for k in range(6):
+            rows.append(2 * obs[free] + r)
+            cols.append(6 * ci[free] + k)
+        for k in range(3):
+            rows.append(2 * obs + r)
+            cols.append(6 * n_cameras + 3 * pi + k)
+    rows = np.concatenate(rows)
+    cols = np.concatenate(cols)
+    return csr_matrix((np.ones(len(rows), dtype=int), (rows, cols)),
+                      shape=(2 * n_obs, 6 * n_cameras + 3 * n_points))
+
+
+# --------------------------------------------------------------------------
+# Analytic Jacobian blocks (replaces scipy's 2-point FD at sfm.py:266)
+# --------------------------------------------------------------------------
+
+def jacobian_blocks(x, n_cameras, n_points, camera_indices, point_indices, K):
+    """Per-observation blocks Jc (N,2,6) [d/dw | d/dT] and Jp (N,2,3) = d/dX.
+
+    Y = X - T, Z = R Y, p = K Z, (u,v) = p[:2]/p[2];
+    A = [[1,0,-u],[0,1,-v]]/p2, B = A K;  J_X = B R;  J_T = -J_X;  J_w = -J_X [Y]x J_r(w).
+    """
+    cams, pts = unpack(x, n_cameras, n_points)
+    K = np.asarray(K, dtype=np.float64)
+    ci = np.asarray(camera_indices)
+    pi = np.asarray(point_indices)
+    R = rodrigues(cams[:, :3])[ci]
+    Jr = right_jacobian(cams[:, :3])[ci]
+    Y = pts[pi] - cams[ci, 3:6]
+    Z = np.einsum("nij,nj->ni", R, Y)
+    p = Z @ K.T
+    u = p[:, 0] / p[:, 2]
+    v = p[:, 1] / p[:, 2]
+    n = len(ci)
+    A = np.zeros((n, 2, 3))
+    A[:, 0, 0] = 1.0
+    A[:, 1, 1] = 1.0
+    A[:, 0, 2] = -u
+    A[:, 1, 2] = -v
+    A /= p[:, 2][:, None, None]
+    B = A @ K
+    JX = B @ R
+    Jw = -(JX @ skew(Y)) @ Jr
+    Jc = np.concatenate([Jw, -JX], axis=2)
+    return Jc, JX
+
+
+def dense_jacobian(x, n_cameras, n_points, camera_indices, point_indices, K):
+    Jc, Jp = jacobian_blocks(x, n_cameras, n_points, camera_indices, point_indices, K)
+    n = len(camera_indices)
+    J = np.zeros((2 * n, 6 * n_cameras + 3 * n_points))
+    for i in range(n):
+        c = int(camera_indices[i])
+        p = int(point_indices[i])
+        J[2 * i:2 * i + 2, 6 * c:6 * c + 6] = Jc[i]
+        J[2 * i:2 * i + 2, 6 * n_cameras + 3 * p:6 * n_cameras + 3 * p + 3] = Jp[i]
+    return J
+
+
+# --------------------------------------------------------------------------
+# Normal equations + point-block Schur complement
+# --------------------------------------------------------------------------
+
+def normal_blocks(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
+    """U (C,6,6), V (P,3,3), gc (C,6), gp (P,3), cost = 0.5 sum r^2, plus per-observation Jc, Jp, r."""
+    ci = np.asarray(camera_indices)
+    pi = np.asarray(point_indices)
+    r = residuals(x, n_cameras, n_points, ci, pi, points_2d, K).reshape(-1, 2)
+    Jc, Jp = jacobian_blocks(x, n_cameras, n_points, ci, pi, K)
+    U = np.zeros((n_cameras, 6, 6))
+    V = np.zeros((n_points, 3, 3))
+    gc = np.zeros((n_cameras, 6))
+    gp = np.zeros((n_points, 3))
+    np.add.at(U, ci, np.einsum("nri,nrj->nij", Jc, Jc))
+    np.add.at(V, pi, np.einsum("nri,nrj->nij", Jp, Jp))
+    np.add.at(gc, ci, np.einsum("nri,nr->ni", Jc, r))
+    np.add.at(gp, pi, np.einsum("nri,nr->ni", Jp, r))
+    return dict(U=U, V=V, gc=gc, gp=gp, cost=0.5 * float(np.sum(r * r)), Jc=Jc, Jp=Jp, r=r)
+
+
+def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam):
+    """Dense reduced camera system with Marquardt damping  (H + lam diag H) d = -g.
+
+    S = U* - sum_p W_p V_p*^-1 W_p^T,  b = -gc + sum_p W_p V_p*^-1 gp  (SURVEY 8 a8).
+    Returns S (6C,6C), b (6C,), and the pieces needed for back-substitution.
+    """
+    ci = np.asarray(camera_indices)
+    pi = np.asarray(point_indices)
+    nb = normal_blocks(x, n_cameras, n_points, ci, pi, points_2d, K)
+    U, V, gc, gp, Jc, Jp = nb["U"], nb["V"], nb["gc"], nb["gp"], nb["Jc"], nb["Jp"]
+    Us = U.copy()
+    Vs = V.copy()
+    i6 = np.arange(6)
+    i3 = np.arange(3)
+    Us[:, i6, i6] *= (1.0 + lam)
+    Vs[:, i3, i3] *= (1.0 + lam)
+    Vinv = np.linalg.inv(Vs) if n_points else Vs
+    W = np.einsum("nri,nrj->nij", Jc, Jp)                    # (N,6,3)
+    n = 6 * n_cameras
+    S = np.zeros((n, n))
+    b = -gc.reshape(-1).copy()
+    for c in range(n_cameras):
+        S[6 * c:6 * c + 6, 6 * c:6 * c + 6] = Us[c]
+    WVi = np.einsum("nij,njk->nik", W, Vinv[pi])             # (N,6,3)
+    np.add.at(b.reshape(n_cameras, 6), ci, np.einsum("nij,nj->ni", WVi, gp[pi]))
+    order = np.argsort(pi, kind="stable")
+    starts = np.flatnonzero(np.r_[True, pi[order][1:] != pi[order][:-1], True])
+    for a, e in zip(starts[:-1], starts[1:]):
+        idx = order[a:e]
+        for i in idx:
+            for j in idx:
+                S[6 * ci[i]:6 * ci[i] + 6, 6 * ci[j]:6 * ci[j] + 6] -= WVi[i] @ W[j].T
+    return dict(S=S, b=b, Vinv=Vinv, W=W, **nb)
+
+
+def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam):
+    """One damped Gauss-Newton step via the Schur complement; returns (delta, predicted_reduction, sys)."""
+    s = schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam)
+    ci = np.asarray(camera_indices)
+    pi = np.asarray(point_indices)
+    dc = np.linalg.solve(s["S"], s["b"])
+    Wt_dc = np.zeros((n_points, 3))
+    np.add.at(Wt_dc, pi, np.einsum("nij,ni->nj", s["W"], dc.reshape(n_cameras, 6)[ci]))
+    dp = np.einsum("pij,pj->pi", s["Vinv"], -s["gp"] - Wt_dc)
+    delta = np.concatenate([dc, dp.reshape(-1)])
+    g = np.concatenate([s["gc"].reshape(-1), s["gp"].reshape(-1)])
+    d2 = np.concatenate([np.einsum("cii->ci", s["U"]).reshape(-1), np.einsum("pii->pi", s["V"]).reshape(-1)])
+    pred = 0.5 * (lam * float(delta @ (d2 * delta)) - float(g @ delta))
+    return delta, pred, s
+
+
+def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
+             ftol=1e-10, xtol=1e-8, gtol=1e-8, max_iter=100, lam0=1e-4, verbose=0):
+    """Reference LM loop (numpy twin of the engine's b200ba_solve).
+
+    Marquardt damping lam*diag(H); accept iff the cost decreases; Nielsen update
+    lam *= max(1/3, 1-(2 rho-1)^3) on accept, lam *= nu, nu *= 2 on reject;
+    scipy-compatible termination (scipy _lsq/common.py check_termination).
+    """
+    x = np.array(x0, dtype=np.float64)
+    args = (n_cameras, n_points, camera_indices, point_indices, points_2d, K)
+    r = residuals(x, *args)
+    cost = 0.5 * float(r @ r)
+    lam, nu = lam0, 2.0
+    status, nfev, it = 0, 1, 0
+    while it < max_iter:
+        it += 1
+        delta, pred, s = lm_step(x, *args, lam)
+        g = np.concatenate([s["gc"].reshape(-1), s["gp"].reshape(-1)])
+        gnorm = float(np.max(np.abs(g)))
+        if gnorm < gtol:
+            status = 1
+            break
+        x_new = x + delta
+        r_new = residuals(x_new, *args)
+        nfev += 1
+        cost_new = 0.5 * float(r_new @ r_new)
+        actual = cost - cost_new
+        rho = actual / pred if pred > 0 else -1.0
+        step_norm = float(np.linalg.norm(delta))
+        if verbose:
+            print(f"it {it:3d} cost {cost:.9e} -> {cost_new:.9e} rho {rho:+.3f} lam {lam:.2e} |d| {step_norm:.2e} |g| {gnorm:.2e}")
+        if np.isfinite(cost_new) and actual > 0:
+            ftol_ok = actual < ftol * cost and rho > 0.25
+            xtol_ok = step_norm < xtol * (xtol + float(np.linalg.norm(x)))
+            x, cost = x_new, cost_new
+            lam *= max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3)
+            nu = 2.0
+            if ftol_ok and xtol_ok:
+                status = 4
+            elif ftol_ok:
+                status = 2
+            elif xtol_ok:
+                status = 3
+            if status:
+                break
+        else:
+            xtol_ok = step_norm < xtol * (xtol + float(np.linalg.norm(x)))
+            if xtol_ok:
+                status = 3
+                break
+            lam *= nu
+            nu *= 2.0
+    r = residuals(x, *args)
+    return dict(x=x, cost=0.5 * float(r @ r), fun=r, status=status, nit=it, nfev=nfev,
+                rms=float(np.sqrt(np.mean(r * r))))
+
+
+# --------------------------------------------------------------------------
+# The reference solver call (sfm.py:266-268)
+# --------------------------------------------------------------------------
+
+def scipy_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
+                ftol=1e-10, verbose=0, max_nfev=None, fun=None, xtol=1e-8, **kw):
+    """scipy.optimize.least_squares with exactly the keyword arguments of sfm.py:266-268.
+
+    ``fun`` defaults to the vectorised residual (R2 of BASELINE.md); pass
+    :func:`residuals_loop` for the faithful per-observation port (R1).
+    """
+    from scipy.optimize import least_squares
+
+    fun = residuals if fun is None else fun
+    S = sparsity(n_cameras, n_points, len(camera_indices), camera_indices, point_indices)
+    return least_squares(fun, np.asarray(x0, dtype=np.float64), jac_sparsity=S, verbose=verbose,
+                         x_scale="jac", ftol=ftol, xtol=xtol, method="trf", max_nfev=max_nfev,
+                         args=(n_cameras, n_points, camera_indices, point_indices, points_2d, K), **kw)
+
+
+def rms(r):
+    r = np.asarray(r)
+    return float(np.sqrt(np.mean(r * r)))

@@ -1,0 +1,222 @@
+"""Generate tests/golden/*.npz from the REAL reference (run in the build container only).
+
+TEST INFRASTRUCTURE.  ``/root/reference`` does not exist on the GPU box, so the
+vectors produced here are committed and nothing at test time reads the reference.
+
+    python oracle/make_golden.py residual      # seeded problems -> reference compute_residuals / sparsity
+    python oracle/make_golden.py sceaux        # SceauxCastle --use_ba: frozen per-call BA problem dumps
+    python oracle/make_golden.py scipy [k...]  # scipy (sfm.py:266-268 kwargs) on the dumps -> cost / RMS
+    python oracle/make_golden.py synthB        # scipy vs oracle LM on a reduced synthetic problem
+
+What is pinned:
+* ``ref_residual_*.npz``  -- outputs of ``/root/reference/sfm_lite/bundle_adjustment.py``
+  (``compute_residuals`` :35-42, ``create_sparsity_matrix`` :6-17), imported by path.
+* ``sceaux_ba_k.npz``     -- arguments of the k-th ``least_squares`` call made by
+  ``SFM._apply_bundle_adjustment`` (sfm.py:266-268) on the SceauxCastle images, captured by
+  replacing ``sfm_lite.sfm.least_squares`` in a writable copy of the reference, plus the
+  reference residual at ``x0`` and the converged cost of scipy run with the reference kwargs.
+"""
+from __future__ import annotations
+
+import ast
+import importlib.util
+import os
+import shutil
+import sys
+import time
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+GOLD = os.path.join(ROOT, "tests", "golden")
+REF = "/root/reference"
+sys.path.insert(0, HERE)
+import ba_oracle as O  # noqa: E402
+
+
+def load_by_path(name, path):
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules[name] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def ref_ba():
+    return load_by_path("ref_ba", os.path.join(REF, "sfm_lite", "bundle_adjustment.py"))
+
+
+def synthetic():
+    return load_by_path("b200ba_synthetic", os.path.join(ROOT, "sfm-python_b200", "synthetic.py"))
+
+
+# ---------------------------------------------------------------- residual fixtures
+def gen_residual():
+    ref = ref_ba()
+    syn = synthetic()
+    rng = np.random.default_rng(1234)
+    os.makedirs(GOLD, exist_ok=True)
+
+    def dump(name, x, n_cam, n_pts, ci, pi, uv, K, with_sparsity=False):
+        r = ref.compute_residuals(x, n_cam, n_pts, ci, pi, uv, K)
+        out = dict(x=x, n_cam=n_cam, n_pts=n_pts, ci=ci, pi=pi, uv=uv, K=K, r_ref=r)
+        if with_sparsity:
+            S = ref.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi).tocoo()
+            order = np.lexsort((S.col, S.row))
+            out.update(sp_row=S.row[order].astype(np.int32), sp_col=S.col[order].astype(np.int32),
+                       sp_shape=np.array(S.shape))
+        np.savez_compressed(os.path.join(GOLD, name), **out)
+        print(name, "N", len(ci), "max|r|", np.abs(r).max())
+
+    # (1) small synthetic, float pixels, identity camera at index 0, with sparsity pattern
+    pb = syn.make_problem(6, 80, 300, seed=3, window=6)
+    dump("ref_residual_small.npz", pb.x0, pb.n_cam, pb.n_pts, pb.camera_indices, pb.point_indices,
+         pb.points_2d, pb.K, with_sparsity=True)
+    # (2) int64 truncated pixels (graph.py:112-113), unsorted observation order, identity camera moved to index 2
+    pb = syn.make_problem(5, 60, 200, seed=4, window=5, int_pixels=True)
+    perm = rng.permutation(pb.n_obs)
+    cams = pb.x0[:30].reshape(5, 6).copy()
+    cams[[0, 2]] = cams[[2, 0]]
+    ci = pb.camera_indices.copy()
+    ci = np.where(ci == 0, 2, np.where(ci == 2, 0, ci))
+    x = np.concatenate([cams.ravel(), pb.x0[30:]])
+    dump("ref_residual_int_unsorted.npz", x, 5, 60, ci[perm], pb.point_indices[perm], pb.points_2d[perm], pb.K)
+    # (3) rotation-angle edge cases and a skewed K with a non-unit last row
+    thetas = [0.0, 1e-12, 1e-9, 1e-7, 2.4e-5, 9.9e-5, 1.01e-4, 1e-3, 0.5, 0.99, 2.95, np.pi - 1e-9, np.pi, 3.3]
+    n_cam = len(thetas)
+    axes = rng.standard_normal((n_cam, 3))
+    axes /= np.linalg.norm(axes, axis=1, keepdims=True)
+    cams = np.concatenate([axes * np.array(thetas)[:, None], 0.3 * rng.standard_normal((n_cam, 3))], 1)
+    n_pts = 40
+    pts = rng.standard_normal((n_pts, 3)) * 2.0
+    ci = np.repeat(np.arange(n_cam), n_pts)
+    pi = np.tile(np.arange(n_pts), n_cam)
+    Ksk = np.array([[2905.88, 3.5, 1416.0], [0.0, 2890.1, 1064.0], [1e-5, -2e-5, 1.02]])
+    # move every point in front of every camera is impossible here; residuals are still well defined (z may be < 0)
+    uv = rng.uniform(0, 2000, size=(len(ci), 2))
+    x = np.concatenate([cams.ravel(), pts.ravel()])
+    dump("ref_residual_angles_skewK.npz", x, n_cam, n_pts, ci, pi, uv, Ksk)
+    # (4) one camera / nine points known-answer data of cv2_lite/solve_pnp.py:70-83 (parsed, not copied into the repo source)
+    src = open(os.path.join(REF, "cv2_lite", "solve_pnp.py")).read()
+    tree = ast.parse(src)
+    lits = {}
+    for node in ast.walk(tree):
+        if isinstance(node, ast.Assign) and isinstance(node.targets[0], ast.Name) \
+                and node.targets[0].id in ("point3ds", "point2ds", "K") and isinstance(node.value, ast.Call):
+            lits[node.targets[0].id] = np.array(ast.literal_eval(node.value.args[0]), dtype=np.float64)
+    p3, p2, Kp = lits["point3ds"], lits["point2ds"], lits["K"]
+    import cv2
+    ok, rvec, tvec = cv2.solvePnP(p3, p2, Kp, None)
+    R, _ = cv2.Rodrigues(rvec)
+    centre = (-R.T @ tvec).ravel()                      # BA convention: T is the camera centre
+    x = np.concatenate([rvec.ravel(), centre, p3.ravel()])
+    dump("ref_residual_pnp9.npz", x, 1, 9, np.zeros(9, dtype=np.int64), np.arange(9), p2, Kp, with_sparsity=True)
+    # (5) a 2000-observation slice of config B at its start
+    pb = syn.make_config("B")
+    n = 2000
+    dump("ref_residual_B2000.npz", pb.x0, pb.n_cam, pb.n_pts, pb.camera_indices[:n], pb.point_indices[:n],
+         pb.points_2d[:n], pb.K)
+
+
+# ---------------------------------------------------------------- SceauxCastle dumps
+def gen_sceaux(workdir="/tmp/ref_copy", max_calls=11):
+    if not os.path.isdir(workdir):
+        shutil.copytree(REF, workdir)
+    stub = os.path.join(workdir, "_stubs", "matplotlib")
+    os.makedirs(stub, exist_ok=True)
+    with open(os.path.join(stub, "__init__.py"), "w") as f:
+        f.write("def use(*a, **k):\n    pass\n")
+    open(os.path.join(stub, "pyplot.py"), "w").close()
+    sys.path.insert(0, os.path.join(workdir, "_stubs"))
+    sys.path.insert(0, workdir)
+    os.chdir(workdir)
+    import sfm_lite.sfm as S
+    from sfm_lite import SFM, load_calibration_data
+
+    calls = []
+
+    class _Res:
+        pass
+
+    def spy(fun, x0, **kw):
+        k = len(calls)
+        n_cam, n_pts, ci, pi, uv, K = kw["args"]
+        t = time.time()
+        r0 = fun(x0, *kw["args"])                                  # the reference residual itself
+        t_ref = time.time() - t
+        rec = dict(x0=np.array(x0), n_cam=n_cam, n_pts=n_pts, ci=np.asarray(ci), pi=np.asarray(pi),
+                   uv=np.asarray(uv), K=np.asarray(K), r0_ref=r0, ftol=kw["ftol"], t_ref_residual=t_ref)
+        t = time.time()
+        sc = O.scipy_solve(x0, n_cam, n_pts, ci, pi, uv, K, ftol=kw["ftol"], max_nfev=600)
+        t_sc = time.time() - t
+        lm = O.lm_solve(x0, n_cam, n_pts, ci, pi, uv, K, ftol=kw["ftol"])
+        rec.update(scipy_cost=sc.cost, scipy_rms=O.rms(sc.fun), scipy_status=sc.status, scipy_nfev=sc.nfev,
+                   scipy_max_nfev=600, scipy_t=t_sc, lm_cost=lm["cost"], lm_rms=lm["rms"], lm_nit=lm["nit"],
+                   scipy_fun="oracle.residuals (vectorised twin; reference-residual runs are in sceaux_scipy_ref.npz)")
+        print(f"[BA call {k}] C/P/N {n_cam}/{n_pts}/{len(ci)} rms0 {O.rms(r0):.1f} | scipy status {sc.status} nfev {sc.nfev} "
+              f"cost {sc.cost:.6f} ({t_sc:.1f}s) | lm nit {lm['nit']} cost {lm['cost']:.6f}", flush=True)
+        np.savez_compressed(os.path.join(GOLD, f"sceaux_ba_{k}.npz"), **rec)
+        calls.append(rec)
+        res = _Res()
+        # continue the incremental run from scipy's answer where scipy converged (pure-reference trajectory
+        # up to 1e-8), otherwise from the exact-Schur LM answer (scipy stalls from call 8 on)
+        res.x = sc.x if sc.status > 0 else lm["x"]
+        return res
+
+    S.least_squares = spy
+    K = load_calibration_data("./ImageDataset_SceauxCastle/images/K.txt")
+    sfm = SFM("./ImageDataset_SceauxCastle/images", K)
+    sfm.construct(min_matches=80, use_ba=True, ba_tol=1e-10, verbose=0)
+    print("BA calls:", len(calls))
+
+
+# ---------------------------------------------------------------- true-reference scipy on dumps
+def gen_scipy(ks):
+    """scipy + the REAL reference residual and sparsity (R1 of BASELINE.md) on selected dumps."""
+    ref = ref_ba()
+    from scipy.optimize import least_squares
+    out_path = os.path.join(GOLD, "sceaux_scipy_ref.npz")
+    out = dict(np.load(out_path)) if os.path.exists(out_path) else {}
+    for k in ks:
+        d = np.load(os.path.join(GOLD, f"sceaux_ba_{k}.npz"))
+        args = (int(d["n_cam"]), int(d["n_pts"]), d["ci"], d["pi"], d["uv"], d["K"])
+        t = time.time()
+        S = ref.create_sparsity_matrix(args[0], args[1], len(d["ci"]), d["ci"], d["pi"])
+        res = least_squares(ref.compute_residuals, d["x0"], jac_sparsity=S, verbose=0, x_scale="jac",
+                            ftol=float(d["ftol"]), method="trf", args=args)
+        dt = time.time() - t
+        out[f"cost_{k}"] = res.cost
+        out[f"rms_{k}"] = O.rms(res.fun)
+        out[f"status_{k}"] = res.status
+        out[f"nfev_{k}"] = res.nfev
+        out[f"njev_{k}"] = res.njev
+        out[f"t_{k}"] = dt
+        print(f"[ref scipy {k}] cost {res.cost:.9f} rms {O.rms(res.fun):.6f} status {res.status} nfev {res.nfev} {dt:.1f}s",
+              flush=True)
+        np.savez_compressed(out_path, **out)
+
+
+def gen_synthB():
+    """A reduced BAL-shaped problem where scipy (reference kwargs) can be run to the end."""
+    syn = synthetic()
+    pb = syn.make_problem(12, 400, 1500, seed=7, window=8)
+    t = time.time()
+    sc = O.scipy_solve(pb.x0, *pb.args(), ftol=1e-10)
+    lm = O.lm_solve(pb.x0, *pb.args(), ftol=1e-10)
+    print("scipy", sc.cost, sc.status, sc.nfev, time.time() - t, "lm", lm["cost"], lm["nit"])
+    np.savez_compressed(os.path.join(GOLD, "synth_small_scipy.npz"), seed=7, n_cam=12, n_pts=400, n_obs=1500, window=8,
+                        scipy_cost=sc.cost, scipy_rms=O.rms(sc.fun), scipy_status=sc.status, scipy_nfev=sc.nfev,
+                        lm_cost=lm["cost"], lm_rms=lm["rms"], x0_sum=float(pb.x0.sum()))
+
+
+if __name__ == "__main__":
+    what = sys.argv[1] if len(sys.argv) > 1 else "residual"
+    if what == "residual":
+        gen_residual()
+    elif what == "sceaux":
+        gen_sceaux()
+    elif what == "scipy":
+        gen_scipy([int(a) for a in sys.argv[2:]] or [0, 1, 2])
+    elif what == "synthB":
+        gen_synthB()
