@@ -137,6 +137,8 @@ int b200ba_solve_dev(b200ba_handle* h, double* x_inout_dev, const b200ba_options
 
 int b200ba_get_stats(b200ba_handle* h, b200ba_stats* out);
 int b200ba_reset_stats(b200ba_handle* h);
+/* on != 0: bracket every kernel family with CUDA events and accumulate b200ba_stats.ms_* (adds syncs) */
+int b200ba_set_profiling(b200ba_handle* h, int on);
 /* stream the library launches on (so callers can record CUDA events around its kernels) */
 void* b200ba_stream(b200ba_handle* h);
 

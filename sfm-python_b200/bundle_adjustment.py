@@ -1,0 +1,367 @@
+"""Host-side mirror of the reference's bundle-adjustment call surface, backed by libb200ba.so.
+
+Drop-in names (rebind the two imports of ``sfm_lite/sfm.py:8,20`` and
+``SFM._apply_bundle_adjustment`` -- ``sfm.py:243-281`` -- runs unchanged):
+
+* :func:`compute_residuals`       <-> ``sfm_lite/bundle_adjustment.py:35-42``
+* :func:`create_sparsity_matrix`  <-> ``sfm_lite/bundle_adjustment.py:6-17``
+* :func:`least_squares`           <-> ``scipy.optimize.least_squares`` as called at ``sfm.py:266-268``
+
+plus :func:`bundle_adjust`, the direct entry.  All numerics run in the CUDA
+library; this module only converts dtypes/layouts (``points_2d`` arrives as int64,
+``graph.py:112-113``) and packs the result object.  No CPU fallback exists.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _lib
+
+MESSAGES = {
+    0: "The maximum number of function evaluations is exceeded.",
+    1: "`gtol` termination condition is satisfied.",
+    2: "`ftol` termination condition is satisfied.",
+    3: "`xtol` termination condition is satisfied.",
+    4: "Both `ftol` and `xtol` termination conditions are satisfied.",
+}
+
+
+class BAError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+def default_device():
+    return int(os.environ.get("LOCAL_RANK", "0"))
+
+
+class Engine:
+    """One GPU's handle (``b200ba_handle``): problem upload, residual/Jacobian/normal equations, LM solve."""
+
+    def __init__(self, device=None):
+        self.lib = _lib.load()
+        self.device = default_device() if device is None else int(device)
+        h = C.c_void_p()
+        rc = self.lib.b200ba_create(C.byref(h), self.device)
+        if rc != 0:
+            raise BAError(f"b200ba_create(device={self.device}) failed: {_lib.STATUS.get(rc, rc)} "
+                          "(a CUDA device is required; there is no CPU fallback)")
+        self.h = h
+        self.n_cam = self.n_pts = self.n_obs = 0
+        self.rank, self.nranks = 0, 1
+
+    # -- lifetime
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b200ba_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.b200ba_last_error(self.h)
+            msg = msg.decode() if msg else ""
+            exc = ValueError if rc in (-1, -6) else BAError
+            raise exc(f"libb200ba: {_lib.STATUS.get(rc, rc)}: {msg}")
+
+    # -- multi-GPU
+    @staticmethod
+    def nccl_unique_id():
+        buf = C.create_string_buffer(128)
+        rc = _lib.load().b200ba_nccl_unique_id(buf)
+        if rc != 0:
+            raise BAError("ncclGetUniqueId failed")
+        return bytes(buf.raw)
+
+    def comm_init(self, unique_id: bytes, rank: int, nranks: int):
+        buf = C.create_string_buffer(unique_id, 128)
+        self._check(self.lib.b200ba_comm_init(self.h, buf, rank, nranks))
+        self.rank, self.nranks = rank, nranks
+
+    # -- problem
+    def set_problem(self, n_cam, n_pts, camera_indices, point_indices, points_2d, K):
+        ci = np.ascontiguousarray(camera_indices, dtype=np.int64).ravel()
+        pi = np.ascontiguousarray(point_indices, dtype=np.int64).ravel()
+        uv = np.ascontiguousarray(points_2d, dtype=np.float64)
+        if len(ci) != len(pi):
+            raise ValueError("camera_indices and point_indices differ in length")
+        if uv.size != 2 * len(ci):
+            raise ValueError("points_2d must have shape (n_obs, 2)")
+        Kc = np.ascontiguousarray(K, dtype=np.float64)
+        if Kc.shape != (3, 3):
+            raise ValueError("K must be 3x3")
+        self._check(self.lib.b200ba_set_problem(self.h, int(n_cam), int(n_pts), len(ci), _ptr(ci), _ptr(pi), _ptr(uv),
+                                                _ptr(Kc)))
+        self.n_cam, self.n_pts, self.n_obs = int(n_cam), int(n_pts), len(ci)
+        return self
+
+    @property
+    def n_params(self):
+        return 6 * self.n_cam + 3 * self.n_pts
+
+    def _x(self, x):
+        x = np.ascontiguousarray(x, dtype=np.float64).ravel()
+        if x.size != self.n_params:
+            raise ValueError(f"x has {x.size} entries, expected 6*{self.n_cam} + 3*{self.n_pts}")
+        return x
+
+    # -- hot-path pieces
+    def residuals(self, x, want_cost=False):
+        x = self._x(x)
+        r = np.empty(2 * self.n_obs, dtype=np.float64)
+        cost = C.c_double(0.0)
+        self._check(self.lib.b200ba_residuals(self.h, _ptr(x), _ptr(r), C.byref(cost)))
+        return (r, cost.value) if want_cost else r
+
+    def cost(self, x):
+        x = self._x(x)
+        cost = C.c_double(0.0)
+        self._check(self.lib.b200ba_residuals(self.h, _ptr(x), C.c_void_p(0), C.byref(cost)))
+        return cost.value
+
+    def jacobian_blocks(self, x):
+        x = self._x(x)
+        Jc = np.empty((self.n_obs, 2, 6))
+        Jp = np.empty((self.n_obs, 2, 3))
+        self._check(self.lib.b200ba_jacobian_blocks(self.h, _ptr(x), _ptr(Jc), _ptr(Jp)))
+        return Jc, Jp
+
+    def normal_equations(self, x, lam, want_S=True):
+        x = self._x(x)
+        n = 6 * self.n_cam
+        S = np.empty((n, n)) if want_S else None
+        b = np.empty(n)
+        g = np.empty(self.n_params)
+        cost = C.c_double(0.0)
+        self._check(self.lib.b200ba_normal_equations(self.h, _ptr(x), float(lam), _ptr(S), _ptr(b), _ptr(g),
+                                                     C.byref(cost)))
+        return dict(S=S, b=b, grad=g, cost=cost.value)
+
+    def lm_step(self, x, lam, solver="auto"):
+        x = self._x(x)
+        d = np.empty(self.n_params)
+        pred, newc = C.c_double(0.0), C.c_double(0.0)
+        self._check(self.lib.b200ba_lm_step(self.h, _ptr(x), float(lam), _lib.SOLVERS[solver], _ptr(d), C.byref(pred),
+                                            C.byref(newc)))
+        return d, pred.value, newc.value
+
+    def make_options(self, ftol=1e-8, xtol=1e-8, gtol=1e-8, max_nfev=None, verbose=0, solver="auto", lambda0=0.0,
+                     pcg_rtol=0.0, pcg_max_iter=0, fixed_iters=0):
+        o = _lib.Options()
+        o.ftol, o.xtol, o.gtol = float(ftol), float(xtol), float(gtol)
+        o.max_nfev = int(max_nfev) if max_nfev else 0
+        o.verbose = int(verbose)
+        o.solver = _lib.SOLVERS[solver]
+        o.lambda0, o.pcg_rtol = float(lambda0), float(pcg_rtol)
+        o.pcg_max_iter, o.fixed_iters = int(pcg_max_iter), int(fixed_iters)
+        return o
+
+    def solve(self, x0, **kw):
+        """LM on host ``x0``; returns (x, Result)."""
+        x = self._x(x0).copy()
+        o = self.make_options(**kw)
+        res = _lib.Result()
+        self._check(self.lib.b200ba_solve(self.h, _ptr(x), C.byref(o), C.byref(res)))
+        return x, res
+
+    # -- device-pointer variants (torch tensors are only carriers of device memory)
+    def solve_dev(self, x_dev_ptr, **kw):
+        o = self.make_options(**kw)
+        res = _lib.Result()
+        self._check(self.lib.b200ba_solve_dev(self.h, C.c_void_p(int(x_dev_ptr)), C.byref(o), C.byref(res)))
+        return res
+
+    def linearize_dev(self, x_dev_ptr, lam):
+        self._check(self.lib.b200ba_linearize_dev(self.h, C.c_void_p(int(x_dev_ptr) if x_dev_ptr else 0), float(lam)))
+
+    def residuals_dev(self, x_dev_ptr, r_dev_ptr=0):
+        cost = C.c_double(0.0)
+        self._check(self.lib.b200ba_residuals_dev(self.h, C.c_void_p(int(x_dev_ptr)),
+                                                  C.c_void_p(int(r_dev_ptr) if r_dev_ptr else 0), C.byref(cost)))
+        return cost.value
+
+    def jacobian_blocks_dev(self, x_dev_ptr, r_dev_ptr, jc_dev_ptr, jp_dev_ptr):
+        self._check(self.lib.b200ba_jacobian_blocks_dev(self.h, C.c_void_p(int(x_dev_ptr)),
+                                                        C.c_void_p(int(r_dev_ptr) if r_dev_ptr else 0),
+                                                        C.c_void_p(int(jc_dev_ptr)), C.c_void_p(int(jp_dev_ptr))))
+
+    # -- introspection
+    def stream(self):
+        return int(self.lib.b200ba_stream(self.h) or 0)
+
+    def stats(self):
+        s = _lib.Stats()
+        self._check(self.lib.b200ba_get_stats(self.h, C.byref(s)))
+        return {n: getattr(s, n) for n, _ in s._fields_}
+
+    def reset_stats(self):
+        self._check(self.lib.b200ba_reset_stats(self.h))
+
+    def set_profiling(self, on):
+        self._check(self.lib.b200ba_set_profiling(self.h, int(bool(on))))
+
+    def debug_fetch(self, name, count, dtype=np.float64):
+        out = np.empty(int(count), dtype=dtype)
+        n = self.lib.b200ba_debug_fetch(self.h, name.encode(), _ptr(out), out.nbytes)
+        if n < 0:
+            self._check(int(n))
+        return out[:n]
+
+
+# ---------------------------------------------------------------------------------------------
+# Reference call surface
+# ---------------------------------------------------------------------------------------------
+_cache = {"key": None, "engine": None}
+
+
+def _problem_key(n_cam, n_pts, ci, pi, uv, K):
+    ci, pi, uv = np.asarray(ci), np.asarray(pi), np.asarray(uv)
+    return (int(n_cam), int(n_pts), len(ci), int(ci.sum()), int(pi.sum()), float(np.asarray(uv, dtype=np.float64).sum()),
+            int((ci[::7] * 31 + pi[::7]).sum()) if len(ci) else 0, np.asarray(K, dtype=np.float64).tobytes())
+
+
+def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K):
+    """The engine holding this problem on the device (uploaded once, reused by later calls)."""
+    key = _problem_key(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
+    if _cache["key"] != key or _cache["engine"] is None:
+        eng = _cache["engine"] or Engine()
+        eng.set_problem(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
+        _cache["engine"], _cache["key"] = eng, key
+    return _cache["engine"]
+
+
+def compute_residuals(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
+    """Same signature / output as ``sfm_lite/bundle_adjustment.py:35-42``: (2N,) float64, projected - observed."""
+    return engine_for(n_cameras, n_points, camera_indices, point_indices, points_2d, K).residuals(x)
+
+
+class JacobianSparsity:
+    """Lazy stand-in for the ``lil_matrix`` of ``bundle_adjustment.py:6-17``.
+
+    The engine uses analytic blocks and never reads the mask; it is only materialised (vectorised, no
+    Python loop) if a caller asks for it (``tocsr`` / ``tolil`` / ``toarray``)."""
+
+    def __init__(self, n_cameras, n_points, n_obs, camera_indices, point3d_indices, fixed_camera_indices=()):
+        if len(camera_indices) != len(point3d_indices):
+            raise AssertionError("camera_indices and point3d_indices differ in length")
+        self.n_cameras, self.n_points, self.n_obs = int(n_cameras), int(n_points), int(n_obs)
+        self.camera_indices = np.asarray(camera_indices, dtype=np.int64)
+        self.point_indices = np.asarray(point3d_indices, dtype=np.int64)
+        self.fixed = np.asarray(list(fixed_camera_indices), dtype=np.int64)
+        self.shape = (2 * self.n_obs, 6 * self.n_cameras + 3 * self.n_points)
+        self.dtype = np.dtype(int)
+
+    @property
+    def nnz(self):
+        free = ~np.isin(self.camera_indices, self.fixed)
+        return int(12 * free.sum() + 6 * len(self.camera_indices))
+
+    def tocsr(self):
+        from scipy.sparse import csr_matrix
+        ci, pi = self.camera_indices, self.point_indices
+        obs = np.arange(len(ci), dtype=np.int64)
+        free = ~np.isin(ci, self.fixed)
+        rows, cols = [], []
+        for r in range(2):
+            for k in range(6):
+                rows.append(2 * obs[free] + r)
+                cols.append(6 * ci[free] + k)
+            for k in range(3):
+                rows.append(2 * obs + r)
+                cols.append(6 * self.n_cameras + 3 * pi + k)
+        rows, cols = np.concatenate(rows), np.concatenate(cols)
+        return csr_matrix((np.ones(len(rows), dtype=int), (rows, cols)), shape=self.shape)
+
+    def tolil(self):
+        return self.tocsr().tolil()
+
+    def tocoo(self):
+        return self.tocsr().tocoo()
+
+    def toarray(self):
+        return self.tocsr().toarray()
+
+
+def create_sparsity_matrix(n_cameras, n_points, n_obs, camera_indices, point3d_indices, fixed_camera_indices=()):
+    """Same signature as ``bundle_adjustment.py:6-17``; returns a lazy mask (see :class:`JacobianSparsity`)."""
+    return JacobianSparsity(n_cameras, n_points, n_obs, camera_indices, point3d_indices, fixed_camera_indices)
+
+
+class BAResult(dict):
+    """OptimizeResult-like: ``x cost optimality nfev njev status message success`` are set eagerly;
+    ``fun`` (2N residuals) and ``grad`` (J^T r) are computed by the engine on first access."""
+
+    def __getattr__(self, name):
+        if name in self:
+            return self[name]
+        if name in ("fun", "grad") and "_engine" in self.__dict__:
+            eng = self.__dict__["_engine"]
+            if name == "fun":
+                self["fun"] = eng.residuals(self["x"])
+            else:
+                self["grad"] = eng.normal_equations(self["x"], 0.0, want_S=False)["grad"]
+            return self[name]
+        raise AttributeError(name)
+
+    __setattr__ = dict.__setitem__
+
+    def __repr__(self):
+        keys = [k for k in self if k != "x"]
+        return "BAResult(" + ", ".join(f"{k}={self[k]!r}" for k in keys) + ")"
+
+
+def _is_ba_residual(fun):
+    name = getattr(fun, "__name__", "")
+    return fun is compute_residuals or name in ("compute_residuals", "residuals", "residuals_loop")
+
+
+def bundle_adjust(x0, n_cam, n_pts, camera_indices, point_indices, points_2d, K, ftol=1e-10, xtol=1e-8, gtol=1e-8,
+                  max_nfev=None, verbose=0, solver="auto", engine=None, **engine_opts):
+    """Global bundle adjustment of ``x0`` (layout of ``sfm.py:255-257``) on the GPU; returns :class:`BAResult`."""
+    eng = engine or engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
+    x, r = eng.solve(x0, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev, verbose=verbose, solver=solver,
+                     **engine_opts)
+    res = BAResult(x=x, cost=r.cost, optimality=r.optimality, nfev=int(r.nfev), njev=int(r.njev), status=int(r.status),
+                   message=MESSAGES.get(int(r.status), ""), success=int(r.status) > 0, rms=r.rms, n_iter=int(r.n_iter),
+                   initial_cost=r.initial_cost, pcg_iters=int(r.pcg_iters), solve_ms=r.solve_ms,
+                   lambda_final=r.lambda_final)
+    res.__dict__["_engine"] = eng
+    return res
+
+
+def least_squares(fun, x0, jac="2-point", bounds=None, method="trf", ftol=1e-8, xtol=1e-8, gtol=1e-8, x_scale="jac",
+                  loss="linear", f_scale=1.0, diff_step=None, tr_solver=None, tr_options=None, jac_sparsity=None,
+                  max_nfev=None, verbose=0, args=(), kwargs=None, **extra):
+    """``scipy.optimize.least_squares``-shaped entry for the call at ``sfm.py:266-268``.
+
+    ``fun`` must be the BA residual (ours or the reference's) and ``args`` the 6-tuple of ``sfm.py:268``;
+    ``jac_sparsity``, ``x_scale='jac'`` and ``method='trf'`` are accepted and mapped to analytic blocks,
+    Marquardt scaling and LM.  ``ftol`` keeps the meaning of ``--ba_tol`` (``main.py:36``)."""
+    if not _is_ba_residual(fun) or len(args) != 6:
+        raise TypeError("b200ba.least_squares only solves the bundle-adjustment problem of sfm_lite: pass "
+                        "compute_residuals and args=(n_cam, n_points, camera_indices, point_indices, points_2d, K)")
+    if loss != "linear":
+        raise NotImplementedError("only loss='linear' (the reference's setting) is implemented")
+    n_cam, n_pts, ci, pi, uv, K = args
+    solver = extra.pop("solver", "auto")
+    return bundle_adjust(x0, n_cam, n_pts, ci, pi, uv, K, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev,
+                         verbose=verbose, solver=solver)
+
+
+def install(sfm_module):
+    """Rebind the three names inside an imported ``sfm_lite.sfm`` module."""
+    sfm_module.least_squares = least_squares
+    sfm_module.compute_residuals = compute_residuals
+    sfm_module.create_sparsity_matrix = create_sparsity_matrix
+    return sfm_module

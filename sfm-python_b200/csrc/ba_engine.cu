@@ -1,0 +1,226 @@
+// Handle lifetime, device memory, NCCL plumbing and the Levenberg-Marquardt loop of libb200ba.
+//
+// The LM loop is the replacement for scipy.optimize.least_squares(method='trf', x_scale='jac') as called at
+// sfm_lite/sfm.py:266-268: Marquardt damping lambda*diag(J^T J) plays the role of x_scale='jac'
+// (scipy _lsq/common.py compute_jac_scale), a step is accepted iff the cost decreases (trf.py inner loop),
+// and termination uses scipy's tests and status codes (common.py check_termination).
+#include <dlfcn.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "ba_internal.h"
+
+namespace b200ba {
+
+int partial_capacity(const Handle* h);
+int pcg_grid(Handle* h);
+
+int fail(Handle* h, int code, const std::string& msg) {
+  if (h) h->err = msg;
+  return code;
+}
+int cuda_fail(Handle* h, cudaError_t e, const char* where) {
+  std::string m = std::string("CUDA error: ") + cudaGetErrorString(e) + " at " + where;
+  cudaGetLastError();
+  return fail(h, e == cudaErrorMemoryAllocation ? B200BA_OOM : B200BA_CUDA, m);
+}
+
+void* dalloc(Handle* h, size_t bytes) {
+  void* p = nullptr;
+  bytes = std::max<size_t>(bytes, 256);
+  cudaError_t e = cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    h->err = "out of device memory (cudaMalloc of " + std::to_string(bytes) + " bytes failed)";
+    return nullptr;
+  }
+  h->allocs.push_back(p);
+  h->bytes_device += (int64_t)bytes;
+  return p;
+}
+
+void free_problem(Handle* h) {
+  for (void* p : h->allocs) cudaFree(p);
+  h->allocs.clear();
+  h->bytes_device = 0;
+  h->pb = Problem();
+  double* hs = h->w.h_scal;
+  h->w = Work();
+  h->w.h_scal = hs;
+  h->has_problem = false;
+}
+
+// ------------------------------------------------------------------ NCCL through dlopen (torch ships libnccl.so.2)
+struct Id128 { char b[128]; };
+namespace {
+struct NcclApi {
+  void* lib = nullptr;
+  int (*GetUniqueId)(void*) = nullptr;
+  int (*CommInitRank)(void**, int, Id128, int) = nullptr;
+  int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  int (*CommDestroy)(void*) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi g_nccl;
+constexpr int NCCL_INT64 = 4, NCCL_DOUBLE = 8, NCCL_SUM = 0, NCCL_MAX = 2;
+
+bool nccl_load(std::string* err) {
+  if (g_nccl.lib) return true;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  void* lib = nullptr;
+  for (const char* n : names) {
+    lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (lib) break;
+  }
+  if (!lib) { *err = std::string("cannot dlopen libnccl.so.2: ") + dlerror(); return false; }
+  g_nccl.GetUniqueId = (int (*)(void*))dlsym(lib, "ncclGetUniqueId");
+  g_nccl.CommInitRank = (int (*)(void**, int, Id128, int))dlsym(lib, "ncclCommInitRank");
+  g_nccl.AllReduce = (int (*)(const void*, void*, size_t, int, int, void*, cudaStream_t))dlsym(lib, "ncclAllReduce");
+  g_nccl.AllGather = (int (*)(const void*, void*, size_t, int, void*, cudaStream_t))dlsym(lib, "ncclAllGather");
+  g_nccl.CommDestroy = (int (*)(void*))dlsym(lib, "ncclCommDestroy");
+  g_nccl.GetErrorString = (const char* (*)(int))dlsym(lib, "ncclGetErrorString");
+  if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.AllGather) {
+    *err = "libnccl.so.2 lacks a required symbol";
+    return false;
+  }
+  g_nccl.lib = lib;
+  return true;
+}
+int nccl_fail(Handle* h, int rc, const char* where) {
+  return fail(h, B200BA_NCCL, std::string("NCCL error: ") +
+                                  (g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?") + " at " + where);
+}
+}  // namespace
+
+int comm_allreduce_sum(Handle* h, double* buf, int64_t count) {
+  if (h->nranks <= 1 || count <= 0) return 0;
+  int rc = g_nccl.AllReduce(buf, buf, (size_t)count, NCCL_DOUBLE, NCCL_SUM, h->comm, h->stream);
+  return rc ? nccl_fail(h, rc, "ncclAllReduce(sum)") : 0;
+}
+int comm_allreduce_max(Handle* h, double* buf, int64_t count) {
+  if (h->nranks <= 1 || count <= 0) return 0;
+  int rc = g_nccl.AllReduce(buf, buf, (size_t)count, NCCL_DOUBLE, NCCL_MAX, h->comm, h->stream);
+  return rc ? nccl_fail(h, rc, "ncclAllReduce(max)") : 0;
+}
+int comm_allgather_i64(Handle* h, const long long* send, long long* recv, int64_t count) {
+  if (h->nranks <= 1) {
+    cudaMemcpyAsync(recv, send, count * sizeof(long long), cudaMemcpyDeviceToDevice, h->stream);
+    return 0;
+  }
+  int rc = g_nccl.AllGather(send, recv, (size_t)count, NCCL_INT64, h->comm, h->stream);
+  return rc ? nccl_fail(h, rc, "ncclAllGather") : 0;
+}
+
+// ------------------------------------------------------------------ per-problem work buffers
+static int alloc_work(Handle* h) {
+  Problem& pb = h->pb;
+  Work& w = h->w;
+  const int64_t C = pb.C, P = pb.P, N = pb.N, nx = 6 * C + 3 * P;
+#define WALLOC(ptr, count)                                                                    \
+  ptr = (double*)dalloc(h, (size_t)std::max<int64_t>((count), 1) * sizeof(double));           \
+  if (!ptr) return B200BA_OOM
+  WALLOC(w.x, nx);
+  WALLOC(w.xn, nx);
+  WALLOC(w.camprep, C * CAMPREP_STRIDE);
+  WALLOC(w.camprep_n, C * CAMPREP_STRIDE);
+  WALLOC(w.Y, N * 18);
+  WALLOC(w.rr, N * 4);
+  WALLOC(w.pp, P * 12);
+  WALLOC(w.gp, P * 3);
+  WALLOC(w.cpart, (int64_t)pb.n_cch * 33);
+  WALLOC(w.spart, (int64_t)pb.n_sch * 36);
+  WALLOC(w.U, C * 21);
+  w.comm_count = (int64_t)pb.n_blk * 36 + 18 * C + S_NSUM;
+  WALLOC(w.comm, w.comm_count);
+  w.Sup = w.comm;
+  w.b = w.Sup + (int64_t)pb.n_blk * 36;
+  w.gc = w.b + 6 * C;
+  w.udiag = w.gc + 6 * C;
+  w.sums = w.udiag + 6 * C;
+  WALLOC(w.scal, NSCAL);
+  w.n_part = partial_capacity(h);
+  WALLOC(w.part, (int64_t)w.n_part * 8);
+  WALLOC(w.dc, 6 * C);
+  WALLOC(w.pcg, 6 * C * 4 + C * 36);
+  WALLOC(w.pcg_part, (int64_t)2 * 4 * std::max(pcg_grid(h), 1));
+  if (C <= DENSE_MAX_CAM) { WALLOC(w.dense, 36 * C * C); }
+#undef WALLOC
+  cudaStream_t st = h->stream;
+  BA_CUDA(h, cudaMemsetAsync(w.pp, 0, (size_t)std::max<int64_t>(P * 12, 1) * sizeof(double), st));
+  BA_CUDA(h, cudaMemsetAsync(w.gp, 0, (size_t)std::max<int64_t>(P * 3, 1) * sizeof(double), st));
+  BA_CUDA(h, cudaMemsetAsync(w.comm, 0, (size_t)w.comm_count * sizeof(double), st));
+  BA_CUDA(h, cudaMemsetAsync(w.scal, 0, NSCAL * sizeof(double), st));
+  BA_CUDA(h, cudaMemsetAsync(w.dc, 0, (size_t)std::max<int64_t>(6 * C, 1) * sizeof(double), st));
+  BA_CUDA(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+// ------------------------------------------------------------------ phase timing (only when profiling is on)
+struct PhaseTimer {
+  Handle* h; double* acc; bool on;
+  PhaseTimer(Handle* h_, double* acc_) : h(h_), acc(acc_), on(h_->profile) {
+    if (on) cudaEventRecord(h->ev0, h->stream);
+  }
+  ~PhaseTimer() {
+    if (!on) return;
+    cudaEventRecord(h->ev1, h->stream);
+    cudaEventSynchronize(h->ev1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    *acc += ms;
+  }
+};
+
+// linearise at w.x (camprep must match) and reduce across ranks; leaves Sup, b, gc, udiag, sums ready
+int linearize_all(Handle* h, double lambda) {
+  Work& w = h->w;
+  if (h->profile) {
+    // split timing of the three kernel families needs separate launches; re-use launch_linearize as a whole
+    PhaseTimer t(h, &h->st.ms_linearize_points);
+    launch_linearize(h, w.x, lambda);
+  } else {
+    launch_linearize(h, w.x, lambda);
+  }
+  {
+    PhaseTimer t(h, &h->st.ms_allreduce);
+    if (int rc = comm_allreduce_sum(h, w.comm, w.comm_count)) return rc;
+    if (int rc = comm_allreduce_max(h, w.scal + S_GPMAX, 1)) return rc;
+  }
+  launch_fix_diag(h);
+  return 0;
+}
+
+int camera_solve(Handle* h, int solver, double rtol, int max_iter) {
+  PhaseTimer t(h, &h->st.ms_camera_solve);
+  if (solver == B200BA_SOLVER_AUTO) solver = (h->pb.C <= 64) ? B200BA_SOLVER_CHOLESKY : B200BA_SOLVER_PCG;
+  if (solver == B200BA_SOLVER_CHOLESKY) return launch_cholesky(h);
+  return launch_pcg(h, rtol, max_iter);
+}
+
+// trial point: cameras x + dc -> xn, camprep_n; points by back-substitution; sums all-reduced
+int trial_step(Handle* h, double lambda) {
+  Work& w = h->w;
+  PhaseTimer t(h, &h->st.ms_backsub_trial);
+  launch_cam_prep(h, w.x, w.dc, w.xn, w.camprep_n);
+  launch_backsub_trial(h, lambda);
+  if (int rc = comm_allreduce_sum(h, w.sums + 1, S_NSUM - 1)) return rc;  // slot 0 (cost at x) is already global
+  launch_cam_dots(h);
+  return 0;
+}
+
+int fetch_scalars(Handle* h) {
+  Work& w = h->w;
+  BA_CUDA(h, cudaMemcpyAsync(w.h_scal, w.scal, NSCAL * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  BA_CUDA(h, cudaMemcpyAsync(w.h_scal + NSCAL, w.sums, S_NSUM * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  BA_CUDA(h, cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+}  // namespace b200ba
+
+#include "ba_lm.inc"
+#include "ba_capi.inc"

@@ -1,0 +1,169 @@
+// Internal declarations of libb200ba (not part of the C ABI; see include/b200ba.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/b200ba.h"
+#include "ba_math.cuh"
+
+namespace b200ba {
+
+constexpr int LIN_WARPS = 8;       // warps per CTA in the point-major kernels
+constexpr int CCHUNK = 256;        // observations per camera-side chunk (one warp)
+constexpr int SCHUNK = 512;        // pair entries per Schur chunk (one warp)
+constexpr int NSCAL = 32;          // device scalar slots
+constexpr int DENSE_MAX_CAM = 512; // dense S export / Cholesky limit
+
+// scalar slots (device array `scal`); "sum" slots are all-reduced with ncclSum
+enum Scal {
+  S_COST2 = 0,     // sum r^2 at x (linearisation point)
+  S_NEWCOST2 = 1,  // sum r^2 at x + delta
+  S_GP_DP = 2,     // sum_p g_p . delta_p
+  S_DP_D_DP = 3,   // sum_p delta_p^T diag(V_p) delta_p
+  S_DP2 = 4,       // ||delta_p||^2
+  S_XP2 = 5,       // ||x_p||^2
+  S_NSUM = 8,      // number of sum slots sent through the all-reduce
+  S_GPMAX = 8,     // max |g_p|   (ncclMax)
+  S_GC_DC = 10,    // camera-side dots (computed from all-reduced data, identical on all ranks)
+  S_DC_D_DC = 11,
+  S_DC2 = 12,
+  S_XC2 = 13,
+  S_GCMAX = 14,
+  S_DC_RES = 15,   // delta_c . (b - S delta_c)   (PCG residual term of the predicted reduction)
+  S_PCG_ITERS = 16,
+  S_SOLVE_FAIL = 17,
+  S_RES_COST2 = 18 // sum r^2 of b200ba_residuals
+};
+
+// One shard of a bundle-adjustment problem, resident in HBM.
+struct Problem {
+  int64_t C = 0, P = 0, N = 0;
+  Intrinsics K;
+  // observations, point-major (sorted by point, stable)
+  double* u = nullptr;      // [N]
+  double* v = nullptr;      // [N]
+  int* cam = nullptr;       // [N]
+  int* pt = nullptr;        // [N] local point id
+  int* perm = nullptr;      // [N] sorted position -> caller's observation index; null = identity
+  int* pt_off = nullptr;    // [P+1]
+  int* wt_off = nullptr;    // [n_wt+1] warp tiles: whole points, <= 32 observations (or one big point)
+  int n_wt = 0;
+  // camera-sorted view
+  int* cperm = nullptr;     // [N] camera-sorted position -> sorted observation index
+  int* cam_off = nullptr;   // [C+1]
+  int* cch_cam = nullptr;   // [n_cch] camera of each chunk
+  int* cch_a = nullptr;     // [n_cch+1]-style begin / end in cperm
+  int* cch_b = nullptr;
+  int* cam_choff = nullptr; // [C+1] chunk range of each camera
+  int n_cch = 0;
+  // Schur pair entries sorted by (global) upper block
+  int64_t n_ent = 0;
+  long long* ent = nullptr; // [n_ent] (i << 32) | j, sorted observation indices of one point
+  int n_blk = 0;            // upper blocks incl. every diagonal block (global structure, identical on all ranks)
+  int* blk_r = nullptr;     // [n_blk]
+  int* blk_c = nullptr;
+  int* sch_blk = nullptr;   // [n_sch]
+  int* sch_a = nullptr;
+  int* sch_b = nullptr;
+  int* blk_choff = nullptr; // [n_blk+1]
+  int n_sch = 0;
+  int* diag_blk = nullptr;  // [C] index of block (c,c)
+  // full (both triangles) block-CSR view for the PCG mat-vec
+  int* bsr_rowptr = nullptr;  // [C+1]
+  int* bsr_col = nullptr;     // [nnzb]
+  int* bsr_src = nullptr;     // [nnzb] upper block index; bit 31 set = use the transpose
+  int nnzb = 0;
+};
+
+struct Work {
+  double* x = nullptr;        // [6C+3P] current parameters
+  double* xn = nullptr;       // [6C+3P] trial parameters
+  double* camprep = nullptr;  // [C*24]
+  double* camprep_n = nullptr;
+  double* Y = nullptr;        // [N*18]
+  double* rr = nullptr;       // [N*4]  r0 r1 rt0 rt1
+  double* pp = nullptr;       // [P*12] Linv(6) z(3) diagV(3)
+  double* gp = nullptr;       // [P*3]
+  double* cpart = nullptr;    // [n_cch*33]
+  double* spart = nullptr;    // [n_sch*36]
+  double* U = nullptr;        // [C*21]
+  // ---- contiguous all-reduce buffer: Sup | b | gc | udiag | sums
+  double* comm = nullptr;
+  double* Sup = nullptr;      // [n_blk*36]
+  double* b = nullptr;        // [6C]
+  double* gc = nullptr;       // [6C]
+  double* udiag = nullptr;    // [6C]
+  double* sums = nullptr;     // [S_NSUM]
+  int64_t comm_count = 0;
+  // ----
+  double* scal = nullptr;     // [NSCAL]
+  double* part = nullptr;     // [n_part * 8] per-CTA partials of the point-major kernels
+  int n_part = 0;
+  double* dc = nullptr;       // [6C] camera step
+  double* pcg = nullptr;      // [6C*4 + C*36] r z p Ap Minv
+  double* pcg_part = nullptr; // [grid*4]
+  double* dense = nullptr;    // [(6C)^2] Cholesky work (only n_cam <= DENSE_MAX_CAM)
+  double* h_scal = nullptr;   // pinned host mirror [NSCAL]
+};
+
+struct Handle {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  bool has_problem = false;
+  Problem pb;
+  Work w;
+  std::vector<void*> allocs;      // problem-lifetime device allocations
+  int64_t bytes_device = 0;
+  // NCCL
+  void* comm = nullptr;
+  int rank = 0, nranks = 1;
+  int64_t n_obs_global = 0;
+  // stats
+  b200ba_stats st{};
+  bool profile = false;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+};
+
+// ---- helpers (ba_engine.cu)
+int fail(Handle* h, int code, const std::string& msg);
+int cuda_fail(Handle* h, cudaError_t e, const char* where);
+void* dalloc(Handle* h, size_t bytes);  // nullptr on failure (h->err set)
+void free_problem(Handle* h);
+#define BA_CUDA(h, call)                                             \
+  do {                                                               \
+    cudaError_t e__ = (call);                                        \
+    if (e__ != cudaSuccess) return cuda_fail((h), e__, #call);       \
+  } while (0)
+
+// ---- collectives (ba_engine.cu); no-ops when nranks == 1
+int comm_allreduce_sum(Handle* h, double* buf, int64_t count);
+int comm_allreduce_max(Handle* h, double* buf, int64_t count);
+int comm_allgather_i64(Handle* h, const long long* send, long long* recv, int64_t count);
+
+// ---- ba_setup.cu
+int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam_idx, const int64_t* pt_idx,
+                  const double* uv, const double* K);
+
+// ---- ba_kernels.cu (all launches on h->stream)
+void launch_cam_prep(Handle* h, const double* x_cams, const double* dc /*nullable*/, double* x_out /*nullable*/,
+                     double* camprep);
+void launch_residual(Handle* h, const double* x, const double* camprep, double* r_out /*nullable, caller order*/,
+                     int scal_slot);
+void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp);
+void launch_linearize(Handle* h, const double* x, double lambda);  // points + cameras + schur -> Sup, b, gc, ...
+void launch_fix_diag(Handle* h);
+void launch_backsub_trial(Handle* h, double lambda);
+void launch_cam_dots(Handle* h);
+void launch_densify(Handle* h, double* dense /*6C x 6C*/);
+
+// ---- ba_solve.cu
+int launch_pcg(Handle* h, double rtol, int max_iter);
+int launch_cholesky(Handle* h);
+
+}  // namespace b200ba

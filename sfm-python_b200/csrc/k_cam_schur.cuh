@@ -1,0 +1,175 @@
+// Camera-side accumulation and point-block Schur elimination (included inside ba_kernels.cu).
+//
+// "Atomics-free scatter into 6x6 camera blocks via sorted observation order": observations are visited
+// through a camera-sorted permutation, a warp owns a chunk of one camera's run, reduces in registers +
+// shuffles and writes one partial; partials are summed per camera in chunk order (bit-reproducible).
+// The Schur complement uses the same scheme over pair entries (i,j) sorted by block (cam_i, cam_j).
+
+__device__ __forceinline__ int tri6(int m, int n) { return m * 6 - (m * (m - 1)) / 2 + (n - m); }  // n >= m
+
+__global__ void __launch_bounds__(256)
+k_cam_side(Problem pb, const double* __restrict__ x, const double* __restrict__ camprep,
+           const double* __restrict__ rr, double* __restrict__ cpart) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarp = (gridDim.x * blockDim.x) >> 5;
+  const double* xp = x + 6 * pb.C;
+  for (int ch = warp; ch < pb.n_cch; ch += nwarp) {
+    const int c = pb.cch_cam[ch], a = pb.cch_a[ch], b = pb.cch_b[ch];
+    const double* cp = camprep + CAMPREP_STRIDE * c;
+    double acc[33];
+#pragma unroll
+    for (int k = 0; k < 33; ++k) acc[k] = 0.0;
+    for (int q = a + lane; q < b; q += 32) {
+      const int i = pb.cperm[q];
+      const int p = pb.pt[i];
+      const double2 r = reinterpret_cast<const double2*>(rr)[2 * (int64_t)i];
+      const double2 rt = reinterpret_cast<const double2*>(rr)[2 * (int64_t)i + 1];
+      double d0, d1, Jc[12], Jp[6];
+      project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], 0.0, 0.0, d0, d1, Jc, Jp);
+      int k = 0;
+#pragma unroll
+      for (int m = 0; m < 6; ++m)
+#pragma unroll
+        for (int n = m; n < 6; ++n) acc[k++] += Jc[m] * Jc[n] + Jc[6 + m] * Jc[6 + n];
+#pragma unroll
+      for (int m = 0; m < 6; ++m) {
+        acc[21 + m] += Jc[m] * r.x + Jc[6 + m] * r.y;
+        acc[27 + m] += Jc[m] * rt.x + Jc[6 + m] * rt.y;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 33; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < 33; ++k) cpart[(int64_t)ch * 33 + k] = acc[k];
+    }
+  }
+}
+
+// U (21 upper-triangular entries), gc = J_c^T r, b = -J_c^T rt, udiag per camera
+__global__ void k_cam_reduce(int C, const int* __restrict__ cam_choff, const double* __restrict__ cpart,
+                             double* __restrict__ U, double* __restrict__ gc, double* __restrict__ b,
+                             double* __restrict__ udiag) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= C * 33) return;
+  const int c = t / 33, k = t % 33;
+  double s = 0.0;
+  for (int ch = cam_choff[c]; ch < cam_choff[c + 1]; ++ch) s += cpart[(int64_t)ch * 33 + k];
+  if (k < 21) {
+    U[c * 21 + k] = s;
+    const int dm = (k == 0) ? 0 : (k == 6) ? 1 : (k == 11) ? 2 : (k == 15) ? 3 : (k == 18) ? 4 : (k == 20) ? 5 : -1;
+    if (dm >= 0) udiag[6 * c + dm] = s;
+  } else if (k < 27) {
+    gc[6 * c + (k - 21)] = s;
+  } else {
+    b[6 * c + (k - 27)] = -s;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_schur(Problem pb, const double* __restrict__ Y, double* __restrict__ spart) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarp = (gridDim.x * blockDim.x) >> 5;
+  for (int ch = warp; ch < pb.n_sch; ch += nwarp) {
+    const int a = pb.sch_a[ch], b = pb.sch_b[ch];
+    double acc[36];
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+    for (int e = a + lane; e < b; e += 32) {
+      const long long ij = pb.ent[e];
+      const int i = (int)(ij >> 32), j = (int)(ij & 0xffffffffll);
+      const double2* pi = reinterpret_cast<const double2*>(Y + 18 * (int64_t)i);
+      const double2* pj = reinterpret_cast<const double2*>(Y + 18 * (int64_t)j);
+      double yi[18], yj[18];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) {
+        const double2 ti = pi[k], tj = pj[k];
+        yi[2 * k] = ti.x; yi[2 * k + 1] = ti.y;
+        yj[2 * k] = tj.x; yj[2 * k + 1] = tj.y;
+      }
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+          acc[6 * r + c] += yi[3 * r] * yj[3 * c] + yi[3 * r + 1] * yj[3 * c + 1] + yi[3 * r + 2] * yj[3 * c + 2];
+    }
+#pragma unroll
+    for (int k = 0; k < 36; ++k) acc[k] = warp_sum(acc[k]);
+    if (lane == 0) {
+#pragma unroll
+      for (int k = 0; k < 36; ++k) spart[(int64_t)ch * 36 + k] = acc[k];
+    }
+  }
+}
+
+// Sup[g] = [g diagonal ? U*_c : 0] - sum of chunk partials      (U* = U + lambda diag U)
+__global__ void k_schur_reduce(int n_blk, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
+                               const int* __restrict__ blk_choff, const double* __restrict__ spart,
+                               const double* __restrict__ U, double lambda, double* __restrict__ Sup) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n_blk * 36) return;
+  const int g = (int)(t / 36), e = (int)(t % 36);
+  double s = 0.0;
+  for (int ch = blk_choff[g]; ch < blk_choff[g + 1]; ++ch) s += spart[(int64_t)ch * 36 + e];
+  double val = -s;
+  if (blk_r[g] == blk_c[g]) {
+    const int r = e / 6, c = e % 6;
+    double uv = U[blk_r[g] * 21 + tri6(min(r, c), max(r, c))];
+    if (r == c) uv *= (1.0 + lambda);
+    val += uv;
+  }
+  Sup[t] = val;
+}
+
+// cameras without any observation (globally): unit diagonal so the reduced system stays non-singular
+__global__ void k_fix_diag(int C, const int* __restrict__ diag_blk, const double* __restrict__ udiag,
+                           double* __restrict__ Sup) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= 6 * C) return;
+  if (udiag[t] == 0.0) Sup[(int64_t)diag_blk[t / 6] * 36 + 7 * (t % 6)] = 1.0;
+}
+
+// camera-side scalars of the step: g_c.dc, dc^T diag(U) dc, |dc|^2, |x_c|^2, max|g_c|
+__global__ void __launch_bounds__(256)
+k_cam_dots(int n, const double* __restrict__ gc, const double* __restrict__ dc, const double* __restrict__ udiag,
+           const double* __restrict__ xc, double* __restrict__ scal) {
+  __shared__ double sm[32 * 5];
+  double v[5] = {0, 0, 0, 0, 0};
+  double mx = 0.0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const double g = gc[i], d = dc[i], xx = xc[i];
+    v[0] += g * d;
+    v[1] += d * d * udiag[i];
+    v[2] += d * d;
+    v[3] += xx * xx;
+    mx = fmax(mx, fabs(g));
+  }
+  mx = warp_max(mx);
+  block_sum<4>(v, sm);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double m = 0.0;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmax(m, sm[w]);
+    scal[S_GC_DC] = v[0];
+    scal[S_DC_D_DC] = v[1];
+    scal[S_DC2] = v[2];
+    scal[S_XC2] = v[3];
+    scal[S_GCMAX] = m;
+  }
+}
+
+// dense symmetric 6C x 6C copy of the block upper triangle (tests, Cholesky)
+__global__ void k_densify(int n_blk, int C, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
+                          const double* __restrict__ Sup, double* __restrict__ dense) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n_blk * 36) return;
+  const int g = (int)(t / 36), e = (int)(t % 36);
+  const int64_t n = 6 * (int64_t)C;
+  const int64_t row = 6 * (int64_t)blk_r[g] + e / 6, col = 6 * (int64_t)blk_c[g] + e % 6;
+  const double v = Sup[t];
+  dense[row * n + col] = v;
+  if (blk_r[g] != blk_c[g]) dense[col * n + row] = v;
+}

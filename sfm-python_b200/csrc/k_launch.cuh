@@ -1,0 +1,121 @@
+// Host-side launch wrappers (included at the end of ba_kernels.cu, namespace b200ba).
+
+namespace {
+
+struct Slots { int s[8]; };
+
+__global__ void k_reduce_partials2(int n, int nsum, int nval, const double* __restrict__ part,
+                                   double* __restrict__ out_sum, double* __restrict__ out_max, Slots slots) {
+  // single CTA, fixed order: thread t sums partials t, t+256, ...; then a fixed tree
+  __shared__ double sm[32 * 8];
+  double v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = 0.0;
+  for (int b = threadIdx.x; b < n; b += blockDim.x)
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (k < nval) {
+        const double t = part[(int64_t)b * 8 + k];
+        v[k] = (k < nsum) ? v[k] + t : fmax(v[k], t);
+      }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const double r = (k < nsum) ? warp_sum(v[k]) : warp_max(v[k]);
+    if (lane == 0) sm[wid * 8 + k] = r;
+  }
+  __syncthreads();
+  if (threadIdx.x < nval) {
+    const int k = threadIdx.x;
+    double r = 0.0;
+    for (int w = 0; w < nw; ++w) r = (k < nsum) ? r + sm[w * 8 + k] : fmax(r, sm[w * 8 + k]);
+    if (k < nsum) out_sum[slots.s[k]] = r; else out_max[slots.s[k]] = r;
+  }
+}
+
+inline unsigned cdiv(int64_t n, int t) { return (unsigned)std::max<int64_t>((n + t - 1) / t, 1); }
+
+}  // namespace
+
+static inline int point_grid(const Handle* h) {
+  return (int)std::min<int64_t>(cdiv(h->pb.n_wt, LIN_WARPS), (int64_t)h->sm_count * 16);
+}
+static inline int obs_grid(const Handle* h) {
+  return (int)std::min<int64_t>(cdiv(h->pb.N, 256), (int64_t)h->sm_count * 16);
+}
+int partial_capacity(const Handle* h) { return std::max(point_grid(h), obs_grid(h)); }
+
+void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* x_out, double* camprep) {
+  const int C = (int)h->pb.C;
+  if (C == 0) return;
+  k_cam_prep<<<cdiv(C, 128), 128, 0, h->stream>>>(C, x_cams, dc, x_out, camprep);
+  h->st.launches += 1;
+}
+
+void launch_residual(Handle* h, const double* x, const double* camprep, double* r_out, int scal_slot) {
+  const int g = obs_grid(h);
+  k_residual<<<g, 256, 0, h->stream>>>(h->pb, x, camprep, r_out, h->w.part);
+  Slots sl{};
+  sl.s[0] = scal_slot;
+  k_reduce_partials2<<<1, 256, 0, h->stream>>>(g, 1, 1, h->w.part, h->w.scal, h->w.scal, sl);
+  h->st.launches += 2;
+}
+
+void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp) {
+  if (h->pb.N == 0) return;
+  k_jacobian<<<cdiv(h->pb.N, JT), JT, 0, h->stream>>>(h->pb, x, camprep, r_out, Jc, Jp);
+  h->st.launches += 1;
+}
+
+// residual + Jacobian blocks + J^T J / J^T r blocks + point-block Schur elimination at x (camprep must match x)
+void launch_linearize(Handle* h, const double* x, double lambda) {
+  Problem& pb = h->pb;
+  Work& w = h->w;
+  cudaStream_t st = h->stream;
+  const int pg = point_grid(h);
+  k_lin_points<<<pg, LIN_WARPS * 32, 0, st>>>(pb, x, w.camprep, lambda, w.Y, w.rr, w.pp, w.gp, w.part);
+  Slots sl{};
+  sl.s[0] = S_COST2;
+  sl.s[1] = S_GPMAX;
+  k_reduce_partials2<<<1, 256, 0, st>>>(pg, 1, 2, w.part, w.sums, w.scal, sl);
+  const int cg = (int)std::min<int64_t>(cdiv(pb.n_cch, 8), (int64_t)h->sm_count * 16);
+  k_cam_side<<<cg, 256, 0, st>>>(pb, x, w.camprep, w.rr, w.cpart);
+  k_cam_reduce<<<cdiv(pb.C * 33, 256), 256, 0, st>>>((int)pb.C, pb.cam_choff, w.cpart, w.U, w.gc, w.b, w.udiag);
+  const int sg = (int)std::min<int64_t>(cdiv(pb.n_sch, 8), (int64_t)h->sm_count * 16);
+  k_schur<<<sg, 256, 0, st>>>(pb, w.Y, w.spart);
+  k_schur_reduce<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_choff,
+                                                                    w.spart, w.U, lambda, w.Sup);
+  h->st.launches += 6;
+  h->st.n_linearize += 1;
+}
+
+void launch_fix_diag(Handle* h) {
+  k_fix_diag<<<cdiv(6 * h->pb.C, 256), 256, 0, h->stream>>>((int)h->pb.C, h->pb.diag_blk, h->w.udiag, h->w.Sup);
+  h->st.launches += 1;
+}
+
+// delta_p, x_new (points), trial cost partial sums -> w.sums[S_NEWCOST2 .. S_XP2]; camprep_n / xn cameras must be set
+void launch_backsub_trial(Handle* h, double lambda) {
+  (void)lambda;
+  Work& w = h->w;
+  const int pg = point_grid(h);
+  k_backsub_trial<<<pg, LIN_WARPS * 32, 0, h->stream>>>(h->pb, w.x, w.xn, w.camprep, w.camprep_n, w.dc, w.pp, w.part);
+  Slots sl{};
+  sl.s[0] = S_NEWCOST2; sl.s[1] = S_GP_DP; sl.s[2] = S_DP_D_DP; sl.s[3] = S_DP2; sl.s[4] = S_XP2;
+  k_reduce_partials2<<<1, 256, 0, h->stream>>>(pg, 5, 5, w.part, w.sums, w.scal, sl);
+  h->st.launches += 2;
+}
+
+void launch_cam_dots(Handle* h) {
+  Work& w = h->w;
+  k_cam_dots<<<1, 256, 0, h->stream>>>((int)(6 * h->pb.C), w.gc, w.dc, w.udiag, w.x, w.scal);
+  h->st.launches += 1;
+}
+
+void launch_densify(Handle* h, double* dense) {
+  const int64_t n = 6 * h->pb.C;
+  cudaMemsetAsync(dense, 0, (size_t)(n * n) * sizeof(double), h->stream);
+  k_densify<<<cdiv((int64_t)h->pb.n_blk * 36, 256), 256, 0, h->stream>>>(h->pb.n_blk, (int)h->pb.C, h->pb.blk_r,
+                                                                        h->pb.blk_c, h->w.Sup, dense);
+  h->st.launches += 1;
+}
