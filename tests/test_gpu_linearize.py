@@ -1,0 +1,88 @@
+"""GPU parity, stage 2: J^T J / J^T r blocks, point-block Schur complement, one LM step, vs the numpy oracle."""
+import numpy as np
+import pytest
+
+import ba_oracle as O
+from conftest import golden_args, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _small():
+    import b200ba
+    return b200ba.synthetic.make_problem(7, 120, 480, seed=5, window=6)
+
+
+@pytest.mark.parametrize("lam", [0.0, 1e-4, 3.0])
+def test_schur_system_vs_oracle(engine, lam):
+    pb = _small()
+    engine.set_problem(*pb.args())
+    out = engine.normal_equations(pb.x0, lam)
+    ref = O.schur_system(pb.x0, *pb.args(), lam)
+    g_ref = np.concatenate([ref["gc"].ravel(), ref["gp"].ravel()])
+    assert abs(out["cost"] - ref["cost"]) <= 1e-12 * ref["cost"]
+    assert np.abs(out["grad"] - g_ref).max() <= 1e-10 * np.abs(g_ref).max()
+    assert np.abs(out["b"] - ref["b"]).max() <= 1e-9 * np.abs(ref["b"]).max()
+    S, Sr = out["S"], ref["S"]
+    assert np.abs(S - S.T).max() <= 1e-9 * np.abs(Sr).max()
+    assert np.abs(S - Sr).max() <= 1e-9 * np.abs(Sr).max()
+
+
+def test_schur_system_unsorted_and_duplicate_camera(engine):
+    """Unsorted observation order, a point seen twice by one camera, a point with one observation, an unobserved point
+    and an unobserved camera."""
+    pb = _small()
+    rng = np.random.default_rng(0)
+    ci = pb.camera_indices.copy()
+    pi = pb.point_indices.copy()
+    uv = pb.points_2d.copy()
+    ci[1] = ci[0]                       # point 0 seen twice by the same camera
+    keep = np.ones(len(ci), bool)
+    p5 = np.flatnonzero(pi == 5)
+    keep[p5[1:]] = False                # point 5: single observation
+    keep[pi == 9] = False               # point 9: no observation
+    keep[ci == 3] = False               # camera 3: no observation
+    ci, pi, uv = ci[keep], pi[keep], uv[keep]
+    perm = rng.permutation(len(ci))
+    ci, pi, uv = ci[perm], pi[perm], uv[perm]
+    args = (pb.n_cam, pb.n_pts, ci, pi, uv, pb.K)
+    engine.set_problem(*args)
+    r = engine.residuals(pb.x0)
+    r_ref = O.residuals(pb.x0, *args)
+    assert np.abs(r - r_ref).max() <= 1e-9 * np.abs(r_ref).max()
+    lam = 1e-3
+    out = engine.normal_equations(pb.x0, lam)
+    ref = O.schur_system(pb.x0, *args, lam)
+    Sr = ref["S"].copy()
+    live = np.ones(6 * pb.n_cam, bool)
+    live[18:24] = False
+    assert np.abs(out["S"][np.ix_(live, live)] - Sr[np.ix_(live, live)]).max() <= 1e-9 * np.abs(Sr).max()
+    assert np.allclose(out["S"][18:24, 18:24], np.eye(6))           # unobserved camera: unit block
+    assert np.abs(out["b"] - ref["b"]).max() <= 1e-9 * np.abs(ref["b"]).max()
+
+
+@pytest.mark.parametrize("solver", ["cholesky", "pcg"])
+def test_lm_step_vs_oracle(engine, solver):
+    pb = _small()
+    engine.set_problem(*pb.args())
+    lam = 1e-3
+    d, pred, newc = engine.lm_step(pb.x0, lam, solver=solver)
+    d_ref, pred_ref, _ = O.lm_step(pb.x0, *pb.args(), lam)
+    assert np.abs(d - d_ref).max() <= 1e-6 * np.abs(d_ref).max()
+    assert abs(pred - pred_ref) <= 1e-8 * abs(pred_ref)
+    r_new = O.residuals(pb.x0 + d, *pb.args())
+    assert abs(newc - 0.5 * float(r_new @ r_new)) <= 1e-9 * newc
+
+
+def test_big_point_path(engine):
+    """A point observed by more than 32 cameras takes the multi-pass tile path."""
+    import b200ba
+    pb = b200ba.synthetic.make_problem(40, 30, 30 * 36, seed=2, window=40)
+    engine.set_problem(*pb.args())
+    lam = 1e-4
+    out = engine.normal_equations(pb.x0, lam)
+    ref = O.schur_system(pb.x0, *pb.args(), lam)
+    assert np.abs(out["S"] - ref["S"]).max() <= 1e-9 * np.abs(ref["S"]).max()
+    d, pred, newc = engine.lm_step(pb.x0, lam, solver="cholesky")
+    d_ref, pred_ref, _ = O.lm_step(pb.x0, *pb.args(), lam)
+    assert np.abs(d - d_ref).max() <= 1e-6 * np.abs(d_ref).max()
