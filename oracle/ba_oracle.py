@@ -243,7 +243,10 @@ def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2
     i3 = np.arange(3)
     Us[:, i6, i6] *= (1.0 + lam)
     Vs[:, i3, i3] *= (1.0 + lam)
-    Vinv = np.linalg.inv(Vs) if n_points else Vs
+    Vinv = np.zeros_like(Vs)
+    ok = np.einsum("pii->p", Vs) > 0                          # points without observations stay frozen
+    if ok.any():
+        Vinv[ok] = np.linalg.inv(Vs[ok])
     W = np.einsum("nri,nrj->nij", Jc, Jp)                    # (N,6,3)
     n = 6 * n_cameras
     S = np.zeros((n, n))
