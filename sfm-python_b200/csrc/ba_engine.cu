@@ -178,13 +178,7 @@ struct PhaseTimer {
 // linearise at w.x (camprep must match) and reduce across ranks; leaves Sup, b, gc, udiag, sums ready
 int linearize_all(Handle* h, double lambda) {
   Work& w = h->w;
-  if (h->profile) {
-    // split timing of the three kernel families needs separate launches; re-use launch_linearize as a whole
-    PhaseTimer t(h, &h->st.ms_linearize_points);
-    launch_linearize(h, w.x, lambda);
-  } else {
-    launch_linearize(h, w.x, lambda);
-  }
+  launch_linearize(h, w.x, lambda);
   {
     PhaseTimer t(h, &h->st.ms_allreduce);
     if (int rc = comm_allreduce_sum(h, w.comm, w.comm_count)) return rc;

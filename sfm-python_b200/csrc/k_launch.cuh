@@ -68,21 +68,43 @@ void launch_jacobian(Handle* h, const double* x, const double* camprep, double* 
 }
 
 // residual + Jacobian blocks + J^T J / J^T r blocks + point-block Schur elimination at x (camprep must match x)
+// profiling helper: time the launches between begin() and end() with CUDA events on the library stream
+struct KernelTimer {
+  Handle* h; bool on;
+  explicit KernelTimer(Handle* h_) : h(h_), on(h_->profile) {}
+  void begin() { if (on) cudaEventRecord(h->ev0, h->stream); }
+  void end(double* acc) {
+    if (!on) return;
+    cudaEventRecord(h->ev1, h->stream);
+    cudaEventSynchronize(h->ev1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    *acc += ms;
+  }
+};
+
 void launch_linearize(Handle* h, const double* x, double lambda) {
   Problem& pb = h->pb;
   Work& w = h->w;
   cudaStream_t st = h->stream;
+  KernelTimer t(h);
   const int pg = point_grid(h);
+  t.begin();
   k_lin_points<<<pg, LIN_WARPS * 32, 0, st>>>(pb, x, w.camprep, lambda, w.Y, w.rr, w.pp, w.gp, w.part);
+  t.end(&h->st.ms_linearize_points);
   Slots sl{};
   sl.s[0] = S_COST2;
   sl.s[1] = S_GPMAX;
   k_reduce_partials2<<<1, 256, 0, st>>>(pg, 1, 2, w.part, w.sums, w.scal, sl);
   const int cg = (int)std::min<int64_t>(cdiv(pb.n_cch, 8), (int64_t)h->sm_count * 16);
+  t.begin();
   k_cam_side<<<cg, 256, 0, st>>>(pb, x, w.camprep, w.rr, w.cpart);
   k_cam_reduce<<<cdiv(pb.C * 33, 256), 256, 0, st>>>((int)pb.C, pb.cam_choff, w.cpart, w.U, w.gc, w.b, w.udiag);
+  t.end(&h->st.ms_camera_blocks);
   const int sg = (int)std::min<int64_t>(cdiv(pb.n_sch, 8), (int64_t)h->sm_count * 16);
+  t.begin();
   k_schur<<<sg, 256, 0, st>>>(pb, w.Y, w.spart);
+  t.end(&h->st.ms_schur);
   k_schur_reduce<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_choff,
                                                                     w.spart, w.U, lambda, w.Sup);
   h->st.launches += 6;
