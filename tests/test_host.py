@@ -1,0 +1,80 @@
+"""CPU: host-side logic -- the C-ABI library loads and exports every declared symbol, generator and shard planner."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def test_library_exports_every_header_symbol():
+    import b200ba
+    lib = b200ba.bundle_adjustment._lib.load()
+    hdr = open(os.path.join(ROOT, "include", "b200ba.h")).read()
+    names = set(re.findall(r"\b(b200ba_[a-z0-9_]+)\s*\(", hdr))
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), n
+    assert names <= set(b200ba.bundle_adjustment._lib.SIGNATURES)
+    assert lib.b200ba_version() >= 100
+
+
+def test_struct_layouts_match_header():
+    import b200ba
+    L = b200ba.bundle_adjustment._lib
+    assert ctypes.sizeof(L.Options) == 64 and ctypes.sizeof(L.Result) == 80 and ctypes.sizeof(L.Stats) == 112
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    import b200ba
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(b200ba.BAError):
+        b200ba.Engine(0)
+    with pytest.raises(TypeError):
+        b200ba.least_squares(lambda x: x, np.zeros(3))
+
+
+def test_synthetic_generator_contract():
+    import b200ba
+    syn = b200ba.synthetic
+    pb = syn.make_config("B")
+    assert (pb.n_cam, pb.n_pts, pb.n_obs) == (49, 7776, 31843)
+    assert np.all(np.diff(pb.point_indices) >= 0)
+    assert np.bincount(pb.point_indices, minlength=pb.n_pts).min() >= 2
+    assert np.all(pb.x0[:6] == 0.0)                                  # camera 0 exactly identity (sfm.py:176)
+    # no duplicated (camera, point) pair
+    key = pb.point_indices * pb.n_cam + pb.camera_indices
+    assert len(np.unique(key)) == len(key)
+    # shard == slice of the full problem, bit for bit
+    sh = syn.make_config("B", point_range=(1000, 3000))
+    m = (pb.point_indices >= 1000) & (pb.point_indices < 3000)
+    assert np.array_equal(sh.camera_indices, pb.camera_indices[m]) and np.array_equal(sh.points_2d, pb.points_2d[m])
+    assert np.array_equal(sh.x0[6 * 49:], pb.x0[6 * 49 + 3000:6 * 49 + 9000])
+    ip = syn.make_problem(5, 60, 200, seed=4, window=5, int_pixels=True)
+    assert ip.points_2d.dtype == np.int64
+
+
+def test_shard_plan_balanced_and_covering():
+    import b200ba
+    deg = b200ba.synthetic.point_degrees(4000, 20000, 16, 0)
+    for world in (1, 2, 4, 8):
+        ranges = b200ba.dist.plan_shards_from_degrees(deg, world)
+        assert ranges[0][0] == 0 and ranges[-1][1] == 4000
+        assert all(ranges[i][1] == ranges[i + 1][0] for i in range(world - 1))
+        loads = [int(deg[a:b].sum()) for a, b in ranges]
+        assert max(loads) - min(loads) <= int(deg.max()) * 2
+    pi = np.repeat(np.arange(4000), deg)
+    assert b200ba.dist.plan_shards(pi, 4000, 4) == b200ba.dist.plan_shards_from_degrees(deg, 4)
+
+
+def test_local_problem_and_split_x():
+    import b200ba
+    pb = b200ba.synthetic.make_problem(6, 80, 300, seed=3, window=6)
+    ci, pil, uv, sel = b200ba.dist.local_problem(pb.camera_indices, pb.point_indices, pb.points_2d, 20, 50)
+    assert pil.min() == 0 and pil.max() == 29 and np.array_equal(pb.point_indices[sel] - 20, pil)
+    xl = b200ba.dist.split_x(pb.x0, 6, 20, 50)
+    assert len(xl) == 36 + 90 and np.array_equal(xl[36:], pb.x0[36 + 60:36 + 150])

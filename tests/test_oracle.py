@@ -1,0 +1,96 @@
+"""CPU: the numpy oracle pinned to outputs of the REAL reference (tests/golden, made by oracle/make_golden.py)."""
+import numpy as np
+import pytest
+
+import ba_oracle as O
+from conftest import golden_args, load_golden
+
+FIX = ["ref_residual_small.npz", "ref_residual_int_unsorted.npz", "ref_residual_pnp9.npz", "ref_residual_B2000.npz",
+       "ref_residual_angles_skewK.npz"]
+
+
+@pytest.mark.parametrize("name", FIX)
+def test_vectorised_residual_vs_reference(name):
+    d = load_golden(name)
+    r = O.residuals(d["x"], *golden_args(d))
+    ref = d["r_ref"]
+    assert np.abs(r - ref).max() <= 1e-11 * np.abs(ref).max()
+
+
+@pytest.mark.parametrize("name", ["ref_residual_small.npz", "ref_residual_pnp9.npz", "ref_residual_int_unsorted.npz"])
+def test_loop_port_vs_reference_bit_exact(name):
+    """The per-observation port follows bundle_adjustment.py:20-42 operation by operation."""
+    d = load_golden(name)
+    r = O.residuals_loop(d["x"], *golden_args(d))
+    assert np.array_equal(r, d["r_ref"])
+
+
+@pytest.mark.parametrize("k", range(9))
+def test_residual_on_sceaux_dumps(k):
+    d = load_golden(f"sceaux_ba_{k}.npz")
+    r = O.residuals(d["x0"], *golden_args(d))
+    assert np.abs(r - d["r0_ref"]).max() <= 1e-11 * np.abs(d["r0_ref"]).max()
+    assert d["uv"].dtype == np.int64 and np.all(np.diff(d["pi"]) >= 0)
+
+
+@pytest.mark.parametrize("name", ["ref_residual_small.npz", "ref_residual_pnp9.npz"])
+def test_sparsity_vs_reference(name):
+    """create_sparsity_matrix (bundle_adjustment.py:6-17): same non-zero pattern, from the oracle and from the product's
+    lazy mask."""
+    import b200ba
+    d = load_golden(name)
+    n_cam, n_pts, ci, pi = int(d["n_cam"]), int(d["n_pts"]), d["ci"], d["pi"]
+    for S in (O.sparsity(n_cam, n_pts, len(ci), ci, pi),
+              b200ba.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi).tocsr()):
+        S = S.tocoo()
+        order = np.lexsort((S.col, S.row))
+        assert tuple(S.shape) == tuple(d["sp_shape"])
+        assert np.array_equal(S.row[order], d["sp_row"]) and np.array_equal(S.col[order], d["sp_col"])
+    assert b200ba.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi).nnz == len(d["sp_row"])
+
+
+def test_analytic_jacobian_vs_central_differences_of_reference_residual_model():
+    d = load_golden("ref_residual_angles_skewK.npz")
+    n_cam, n_pts, ci, pi, uv, K = golden_args(d)
+    x = d["x"]
+    J = O.dense_jacobian(x, n_cam, n_pts, ci, pi, K)
+    r0 = O.residuals(x, n_cam, n_pts, ci, pi, uv, K)
+    ok = np.abs(r0) < 1e4                       # skip rows whose depth is ~0 (ill-conditioned projection)
+    rng = np.random.default_rng(0)
+    for col in rng.choice(J.shape[1], 40, replace=False):
+        h = 1e-6
+        e = np.zeros_like(x)
+        e[col] = h
+        fd = (O.residuals(x + e, n_cam, n_pts, ci, pi, uv, K) - O.residuals(x - e, n_cam, n_pts, ci, pi, uv, K)) / (2 * h)
+        scale = max(1.0, np.abs(J[ok, col]).max())
+        assert np.abs(fd[ok] - J[ok, col]).max() <= 2e-5 * scale
+
+
+def test_schur_step_equals_dense_normal_equations():
+    import b200ba
+    pb = b200ba.synthetic.make_problem(5, 40, 150, seed=1, window=5)
+    lam = 1e-3
+    delta, pred, s = O.lm_step(pb.x0, *pb.args(), lam)
+    J = O.dense_jacobian(pb.x0, pb.n_cam, pb.n_pts, pb.camera_indices, pb.point_indices, pb.K)
+    r = O.residuals(pb.x0, *pb.args())
+    H = J.T @ J
+    Hd = H + lam * np.diag(np.diag(H))
+    ref = np.linalg.solve(Hd, -J.T @ r)
+    assert np.abs(delta - ref).max() <= 1e-8 * np.abs(ref).max()
+    assert abs(pred - (0.5 * r @ r - 0.5 * np.sum((r + J @ ref) ** 2))) <= 1e-8 * abs(pred)
+
+
+@pytest.mark.parametrize("k", [0, 3])
+def test_oracle_lm_reaches_scipy_cost_on_dumps(k):
+    d = load_golden(f"sceaux_ba_{k}.npz")
+    res = O.lm_solve(d["x0"], *golden_args(d), ftol=1e-10)
+    assert abs(res["cost"] - float(d["scipy_cost"])) <= 1e-6 * float(d["scipy_cost"])
+    assert abs(res["cost"] - float(d["lm_cost"])) <= 1e-9 * float(d["lm_cost"])
+
+
+def test_true_reference_scipy_golden_consistent():
+    """scipy + the real reference residual (calls 0-2) agrees with scipy + the vectorised twin to 1e-7."""
+    ref = load_golden("sceaux_scipy_ref.npz")
+    for k in (0, 1, 2):
+        d = load_golden(f"sceaux_ba_{k}.npz")
+        assert abs(float(ref[f"cost_{k}"]) - float(d["scipy_cost"])) <= 1e-7 * float(d["scipy_cost"])
