@@ -67,41 +67,115 @@ __global__ void k_cam_reduce(int C, const int* __restrict__ cam_choff, const dou
   }
 }
 
-__global__ void __launch_bounds__(256)
+// ---- Schur pair kernel: S_{c_i c_j} -= Y_i Y_j^T summed over the pair entries of a chunk (one block of S).
+// A warp streams its chunks through a 3-stage cp.async pipeline: the two 144-byte records of 32 entries are
+// gathered global -> shared memory by LDGSTS with 9 consecutive lanes per record (each request touches ~7 lines
+// instead of 32), without passing through registers, while the previous group is multiplied out of shared memory.
+// Entry slots are padded to 304 B so that the per-lane 16-byte reads are bank-conflict free.
+constexpr int SCH_WARPS = 7;
+constexpr int SCH_STAGES = 3;
+constexpr int SCH_ESTRIDE = 304;
+constexpr int SCH_STAGE_BYTES = 32 * SCH_ESTRIDE;
+constexpr int SCH_SMEM = SCH_WARPS * SCH_STAGES * SCH_STAGE_BYTES;  // 204288 B
+
+__device__ __forceinline__ void cp_async16(void* dst_smem, const void* src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+struct ChunkCursor {
+  int ch, g, a, b;  // chunk id, 32-entry group inside it, entry range of the chunk
+};
+__device__ __forceinline__ void cursor_load(const Problem& pb, ChunkCursor& c) {
+  c.g = 0;
+  if (c.ch < pb.n_sch) { c.a = pb.sch_a[c.ch]; c.b = pb.sch_b[c.ch]; } else { c.a = 0; c.b = 0; }
+}
+__device__ __forceinline__ bool cursor_advance(const Problem& pb, ChunkCursor& c, int stride) {  // true: chunk finished
+  ++c.g;
+  if (c.a + 32 * c.g >= c.b) { c.ch += stride; cursor_load(pb, c); return true; }
+  return false;
+}
+
+template <int MODE>  // 0 = production; 1 = fetch only; 2 = multiply only (diagnostic builds of the same pipeline)
+__global__ void __launch_bounds__(SCH_WARPS * 32)
 k_schur(Problem pb, const double* __restrict__ Y, double* __restrict__ spart) {
-  const int lane = threadIdx.x & 31;
-  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int nwarp = (gridDim.x * blockDim.x) >> 5;
-  for (int ch = warp; ch < pb.n_sch; ch += nwarp) {
-    const int a = pb.sch_a[ch], b = pb.sch_b[ch];
-    double acc[36];
+  extern __shared__ __align__(16) unsigned char sch_smem[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int nwarp = gridDim.x * SCH_WARPS;
+  unsigned char* wbase = sch_smem + wid * (SCH_STAGES * SCH_STAGE_BYTES);
+
+  ChunkCursor F, Cc;  // fetch / compute cursors over the same (chunk, group) sequence
+  F.ch = blockIdx.x * SCH_WARPS + wid;
+  cursor_load(pb, F);
+  Cc = F;
+  long long ij_pend = 0;
+  if (F.ch < pb.n_sch) ij_pend = pb.ent[min(F.a + lane, F.b - 1)];
+
+  auto fetch = [&](int stage) {
+    if (F.ch < pb.n_sch) {
+      const int i = (int)(ij_pend >> 32), j = (int)(ij_pend & 0xffffffffll);
+      unsigned char* st = wbase + stage * SCH_STAGE_BYTES;
 #pragma unroll
-    for (int k = 0; k < 36; ++k) acc[k] = 0.0;
-    for (int e = a + lane; e < b; e += 32) {
-      const long long ij = pb.ent[e];
-      const int i = (int)(ij >> 32), j = (int)(ij & 0xffffffffll);
-      const double2* pi = reinterpret_cast<const double2*>(Y + 18 * (int64_t)i);
-      const double2* pj = reinterpret_cast<const double2*>(Y + 18 * (int64_t)j);
-      double yi[18], yj[18];
+      for (int t = 0; t < (MODE == 2 ? 0 : 9); ++t) {
+        const int id = t * 32 + lane;
+        const int rec = id / 9, q = id - rec * 9;
+        const int ri = __shfl_sync(FULL, i, rec), rj = __shfl_sync(FULL, j, rec);
+        cp_async16(st + rec * SCH_ESTRIDE + q * 16, Y + 18 * (int64_t)ri + 2 * q);
+        cp_async16(st + rec * SCH_ESTRIDE + 144 + q * 16, Y + 18 * (int64_t)rj + 2 * q);
+      }
+      cursor_advance(pb, F, nwarp);
+      if (F.ch < pb.n_sch) ij_pend = pb.ent[min(F.a + 32 * F.g + lane, F.b - 1)];  // consumed by the NEXT fetch
+    }
+    cp_async_commit();
+  };
+
 #pragma unroll
-      for (int k = 0; k < 9; ++k) {
-        const double2 ti = pi[k], tj = pj[k];
-        yi[2 * k] = ti.x; yi[2 * k + 1] = ti.y;
-        yj[2 * k] = tj.x; yj[2 * k + 1] = tj.y;
+  for (int s = 0; s < SCH_STAGES - 1; ++s) fetch(s);
+  int stage_c = 0, stage_f = SCH_STAGES - 1;
+  double acc[36];
+#pragma unroll
+  for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+
+  while (Cc.ch < pb.n_sch) {
+    fetch(stage_f);
+    cp_async_wait<SCH_STAGES - 1>();
+    __syncwarp();
+    if (MODE != 1 && Cc.a + 32 * Cc.g + lane < Cc.b) {
+      const double2* sl = reinterpret_cast<const double2*>(wbase + stage_c * SCH_STAGE_BYTES + lane * SCH_ESTRIDE);
+      double yj[18];
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { const double2 t = sl[9 + k]; yj[2 * k] = t.x; yj[2 * k + 1] = t.y; }
+#pragma unroll
+      for (int h = 0; h < 3; ++h) {  // rows 2h, 2h+1 of Y_i
+        const double2 t0 = sl[3 * h], t1 = sl[3 * h + 1], t2 = sl[3 * h + 2];
+        const double yi[6] = {t0.x, t0.y, t1.x, t1.y, t2.x, t2.y};
+#pragma unroll
+        for (int rr2 = 0; rr2 < 2; ++rr2)
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+            acc[6 * (2 * h + rr2) + c] += yi[3 * rr2] * yj[3 * c] + yi[3 * rr2 + 1] * yj[3 * c + 1] +
+                                          yi[3 * rr2 + 2] * yj[3 * c + 2];
+      }
+    }
+    __syncwarp();
+    const int ch_done = Cc.ch;
+    if (cursor_advance(pb, Cc, nwarp)) {
+#pragma unroll
+      for (int k = 0; k < 36; ++k) acc[k] = warp_sum(acc[k]);
+      if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 36; ++k) spart[(int64_t)ch_done * 36 + k] = acc[k];
       }
 #pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int c = 0; c < 6; ++c)
-          acc[6 * r + c] += yi[3 * r] * yj[3 * c] + yi[3 * r + 1] * yj[3 * c + 1] + yi[3 * r + 2] * yj[3 * c + 2];
+      for (int k = 0; k < 36; ++k) acc[k] = 0.0;
     }
-#pragma unroll
-    for (int k = 0; k < 36; ++k) acc[k] = warp_sum(acc[k]);
-    if (lane == 0) {
-#pragma unroll
-      for (int k = 0; k < 36; ++k) spart[(int64_t)ch * 36 + k] = acc[k];
-    }
+    stage_c = (stage_c + 1 == SCH_STAGES) ? 0 : stage_c + 1;
+    stage_f = (stage_f + 1 == SCH_STAGES) ? 0 : stage_f + 1;
   }
+  cp_async_wait<0>();
 }
 
 // Sup[g] = [g diagonal ? U*_c : 0] - sum of chunk partials      (U* = U + lambda diag U)

@@ -101,9 +101,19 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
   k_cam_side<<<cg, 256, 0, st>>>(pb, x, w.camprep, w.rr, w.cpart);
   k_cam_reduce<<<cdiv(pb.C * 33, 256), 256, 0, st>>>((int)pb.C, pb.cam_choff, w.cpart, w.U, w.gc, w.b, w.udiag);
   t.end(&h->st.ms_camera_blocks);
-  const int sg = (int)std::min<int64_t>(cdiv(pb.n_sch, 8), (int64_t)h->sm_count * 16);
+  static int schur_mode = -1;
+  if (schur_mode < 0) {
+    cudaFuncSetAttribute(k_schur<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
+    cudaFuncSetAttribute(k_schur<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
+    cudaFuncSetAttribute(k_schur<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
+    const char* e = getenv("B200BA_SCHUR_DIAG");  // diagnostic only (wrong results): 1 = fetch only, 2 = multiply only
+    schur_mode = e ? atoi(e) : 0;
+  }
+  const int sg = (int)std::min<int64_t>(cdiv(pb.n_sch, SCH_WARPS), (int64_t)h->sm_count);
   t.begin();
-  k_schur<<<sg, 256, 0, st>>>(pb, w.Y, w.spart);
+  if (schur_mode == 1) k_schur<1><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
+  else if (schur_mode == 2) k_schur<2><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
+  else k_schur<0><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
   t.end(&h->st.ms_schur);
   k_schur_reduce<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_choff,
                                                                     w.spart, w.U, lambda, w.Sup);
