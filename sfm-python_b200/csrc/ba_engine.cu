@@ -132,7 +132,7 @@ static int alloc_work(Handle* h) {
   WALLOC(w.pp, P * 12);
   WALLOC(w.gp, P * 3);
   WALLOC(w.cpart, (int64_t)pb.n_cch * 33);
-  WALLOC(w.spart, (int64_t)pb.n_sch * 36);
+  WALLOC(w.spart, (int64_t)std::max(pb.n_sch, pb.n_slot) * 36);
   WALLOC(w.U, C * 21);
   w.comm_count = (int64_t)pb.n_blk * 36 + 18 * C + S_NSUM;
   WALLOC(w.comm, w.comm_count);

@@ -14,7 +14,8 @@ namespace b200ba {
 
 constexpr int LIN_WARPS = 8;       // warps per CTA in the point-major kernels
 constexpr int CCHUNK = 256;        // observations per camera-side chunk (one warp)
-constexpr int SCHUNK = 512;        // pair entries per Schur chunk (one warp)
+constexpr int SCHUNK = 512;
+constexpr int SCHUR_TILE_MAX = 1344;  // observations per Schur tile: 1344 * 144 B = 193.5 KB of shared memory        // pair entries per Schur chunk (one warp)
 constexpr int NSCAL = 32;          // device scalar slots
 constexpr int DENSE_MAX_CAM = 512; // dense S export / Cholesky limit
 
@@ -72,6 +73,20 @@ struct Problem {
   int* blk_choff = nullptr; // [n_blk+1]
   int n_sch = 0;
   int* diag_blk = nullptr;  // [C] index of block (c,c)
+  // tile mode of the Schur kernel (default): observations cut into tiles of whole points that fit shared memory;
+  // a "slot" = all pair entries of one (tile, block); slots of a tile are ordered by decreasing entry count
+  bool schur_tiles = false;
+  int tile_obs = 0;           // observations per tile (<= SCHUR_TILE_MAX)
+  int n_st = 0;
+  int* st_off = nullptr;      // [n_st+1] observation offsets of the tiles
+  unsigned* tent = nullptr;   // [n_ent] (i_local << 16) | j_local, grouped by (tile, block)
+  int n_slot = 0;
+  int* slot_a = nullptr;      // [n_slot] first entry
+  int* slot_n = nullptr;      // [n_slot] entry count
+  int* tile_slot_off = nullptr;  // [n_st+1]
+  int* tile_ent_off = nullptr;   // [n_st+1] entry range of each tile
+  int* blk_slot_off = nullptr;   // [n_blk+1] reduce lists: slots of each block
+  int* blk_slots = nullptr;      // [n_slot]
   // full (both triangles) block-CSR view for the PCG mat-vec
   int* bsr_rowptr = nullptr;  // [C+1]
   int* bsr_col = nullptr;     // [nnzb]

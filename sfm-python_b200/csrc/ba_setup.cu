@@ -12,6 +12,8 @@ namespace b200ba {
 
 namespace {
 
+constexpr int SLOT_CAP = 32;  // pair entries per Schur slot (tile mode)
+
 __global__ void k_check_convert(int64_t N, int64_t C, int64_t P, const int64_t* __restrict__ cam64,
                                 const int64_t* __restrict__ pt64, int* __restrict__ cam32, int* __restrict__ pt32,
                                 int* __restrict__ iota, int* __restrict__ flags) {
@@ -69,18 +71,19 @@ __global__ void k_pair_count(int P, const int* __restrict__ pt_off, const int* _
 }
 
 __global__ void k_pair_fill(int P, long long C, const int* __restrict__ pt_off, const int* __restrict__ cam,
-                            const long long* __restrict__ ent_off, long long* __restrict__ keys,
-                            long long* __restrict__ vals) {
+                            const long long* __restrict__ ent_off, const int* __restrict__ pt_tile,
+                            long long* __restrict__ keys, long long* __restrict__ vals) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   int a = pt_off[p], b = pt_off[p + 1];
   long long e = ent_off[p];
+  const long long tbase = pt_tile ? (long long)pt_tile[p] * C * C : 0;
   for (int i = a; i < b; ++i) {
     int ci = cam[i];
     for (int j = a; j < b; ++j) {
       int cj = cam[j];
       if (ci <= cj) {
-        keys[e] = (long long)ci * C + cj;
+        keys[e] = tbase + (long long)ci * C + cj;
         vals[e] = ((long long)i << 32) | (unsigned int)j;
         ++e;
       }
@@ -100,6 +103,97 @@ __global__ void k_lower_bound(int n_blk, const long long* __restrict__ gkeys, lo
     if (keys_sorted[mid] < key) lo = mid + 1; else hi = mid;
   }
   blk_off[g] = lo;
+}
+
+__global__ void k_mod_keys(int n, const long long* __restrict__ keys, long long CC, long long* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = keys[i] % CC;
+}
+
+// per (tile, block) cell: global block id and the ordering key (tile asc, entry count desc)
+__global__ void k_cell_meta(int n, const long long* __restrict__ cellkey, const int* __restrict__ cnt, long long CC,
+                            const long long* __restrict__ gkeys, int n_blk, int* __restrict__ cell_blk,
+                            int* __restrict__ cell_tile, int* __restrict__ nsub) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  const long long key = cellkey[c];
+  const long long tile = key / CC, bk = key - tile * CC;
+  int lo = 0, hi = n_blk;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (gkeys[mid] < bk) lo = mid + 1; else hi = mid;
+  }
+  cell_blk[c] = lo;
+  cell_tile[c] = (int)tile;
+  nsub[c] = (cnt[c] + SLOT_CAP - 1) / SLOT_CAP;
+}
+
+// split every cell into sub-slots of at most SLOT_CAP entries (bounded, balanced work per lane group)
+__global__ void k_sub_fill(int n_cell, const int* __restrict__ sub_off, const int* __restrict__ cell_off,
+                           const int* __restrict__ cnt, const int* __restrict__ cell_blk,
+                           const int* __restrict__ cell_tile, int* __restrict__ sub_a, int* __restrict__ sub_n,
+                           int* __restrict__ sub_blk, long long* __restrict__ key2) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= n_cell) return;
+  const int q0 = sub_off[c], nq = sub_off[c + 1] - q0, a = cell_off[c], n = cnt[c];
+  for (int k = 0; k < nq; ++k) {
+    const int m = min(SLOT_CAP, n - SLOT_CAP * k);
+    sub_a[q0 + k] = a + SLOT_CAP * k;
+    sub_n[q0 + k] = m;
+    sub_blk[q0 + k] = cell_blk[c];
+    key2[q0 + k] = ((long long)cell_tile[c] << 32) | (long long)(0x7fffffff - m);
+  }
+}
+
+__global__ void k_slot_fill(int n, const int* __restrict__ order, const int* __restrict__ sub_a,
+                            const int* __restrict__ sub_n, const int* __restrict__ sub_blk, int* __restrict__ slot_a,
+                            int* __restrict__ slot_n, int* __restrict__ slot_blk) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  const int q = order[s];
+  slot_a[s] = sub_a[q];
+  slot_n[s] = sub_n[q];
+  slot_blk[s] = sub_blk[q];
+}
+
+__global__ void k_tile_slot_off(int n_st, int n_slot, const long long* __restrict__ key2s, int* __restrict__ off) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t > n_st) return;
+  const long long key = (long long)t << 32;
+  int lo = 0, hi = n_slot;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (key2s[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  off[t] = lo;
+}
+
+__global__ void k_tile_ent_off(int n_st, int n_ent, const long long* __restrict__ keys_sorted, long long CC,
+                               int* __restrict__ off) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t > n_st) return;
+  const long long key = (long long)t * CC;
+  int lo = 0, hi = n_ent;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (keys_sorted[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  off[t] = lo;
+}
+
+__global__ void k_pack_entries(long long n, const long long* __restrict__ ent64, const int* __restrict__ st_off,
+                               int n_st, unsigned* __restrict__ tent) {
+  long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const long long ij = ent64[e];
+  const int i = (int)(ij >> 32), j = (int)(ij & 0xffffffffll);
+  int lo = 0, hi = n_st;  // last tile with st_off[t] <= i
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (st_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  const int base = st_off[lo];
+  tent[e] = ((unsigned)(i - base) << 16) | (unsigned)(j - base);
 }
 
 inline unsigned nblk(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
@@ -189,7 +283,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
 
   // ---- 3. warp tiles (host greedy packing of whole points into <= 32 observations)
-  std::vector<int> h_pt_off(P + 1, 0);
+  std::vector<int> h_pt_off(P + 1, 0), h_pt_tile;
   BA_CUDA(h, cudaMemcpyAsync(h_pt_off.data(), pb.pt_off, (P + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
   BA_CUDA(h, cudaStreamSynchronize(st));
   {
@@ -208,6 +302,32 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if ((int)N > start) wt.push_back((int)N);
     pb.n_wt = (int)wt.size() - 1;
     if (int rc = upload(h, &pb.wt_off, wt)) return rc;
+    // Schur tiles: runs of warp tiles (whole points) with at most tile_obs observations
+    int max_deg = 0;
+    for (int64_t p = 0; p < P; ++p) max_deg = std::max(max_deg, h_pt_off[p + 1] - h_pt_off[p]);
+    int tile_obs = (int)std::min<int64_t>(SCHUR_TILE_MAX, std::max<int64_t>(256, (N / (4 * (int64_t)h->sm_count) + 31) / 32 * 32));
+    const char* force_stream = getenv("B200BA_SCHUR_STREAM");
+    pb.schur_tiles = max_deg <= tile_obs && !(force_stream && atoi(force_stream));
+    if (pb.schur_tiles) {
+      std::vector<int> stv;
+      stv.push_back(0);
+      int ts = 0;
+      for (size_t k = 1; k < wt.size(); ++k)
+        if (wt[k] - ts > tile_obs) { stv.push_back(wt[k - 1]); ts = wt[k - 1]; }
+      if ((int)N > ts) stv.push_back((int)N);
+      pb.n_st = (int)stv.size() - 1;
+      pb.tile_obs = tile_obs;
+      if ((double)(pb.n_st + 1) * (double)C * (double)C >= 4.0e18) pb.schur_tiles = false;  // key would overflow
+      else {
+        if (int rc = upload(h, &pb.st_off, stv)) return rc;
+        h_pt_tile.assign(P, 0);
+        int t = 0;
+        for (int64_t p = 0; p < P; ++p) {
+          while (t + 1 < pb.n_st && h_pt_off[p] >= stv[t + 1]) ++t;
+          h_pt_tile[p] = t;
+        }
+      }
+    }
   }
 
   // ---- 4. camera-sorted permutation and chunks
@@ -245,7 +365,14 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.cam_choff, coff)) return rc;
   }
 
-  // ---- 5. Schur pair entries, sorted by block key = cam_i * C + cam_j (cam_i <= cam_j)
+  // ---- 5. Schur pair entries sorted by key: [tile *] C*C + cam_i * C + cam_j  (cam_i <= cam_j)
+  const long long CC = (long long)C * C;
+  int* d_pt_tile = nullptr;
+  if (pb.schur_tiles) {
+    d_pt_tile = (int*)tmp.get(std::max<size_t>(P, 1) * sizeof(int));
+    if (!d_pt_tile) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+    if (P > 0) BA_CUDA(h, cudaMemcpyAsync(d_pt_tile, h_pt_tile.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
   TMP_ALLOC(d_cnt, long long, P + 1);
   TMP_ALLOC(d_ent_off, long long, P + 1);
   BA_CUDA(h, cudaMemsetAsync(d_cnt, 0, (P + 1) * sizeof(long long), st));
@@ -261,33 +388,66 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   BA_CUDA(h, cudaStreamSynchronize(st));
   if (n_ent >= ((long long)1 << 31)) return fail(h, B200BA_BAD_ARG, "too many Schur pair entries for one shard (>= 2^31)");
   pb.n_ent = n_ent;
-  DEV_ALLOC(pb.ent, long long, n_ent);
+  long long* d_ent64 = nullptr;  // sorted (i << 32) | j : kept in stream mode, scratch in tile mode
+  if (pb.schur_tiles) {
+    d_ent64 = (long long*)tmp.get(std::max<size_t>(n_ent, 1) * sizeof(long long));
+    if (!d_ent64) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+  } else {
+    DEV_ALLOC(pb.ent, long long, n_ent);
+    d_ent64 = pb.ent;
+  }
   TMP_ALLOC(d_keys_sorted, long long, n_ent);
-  std::vector<long long> keys_host;  // unique local keys
+  TMP_ALLOC(d_uniq, long long, n_ent + 1);   // run keys: blocks (stream mode) or (tile, block) cells (tile mode)
+  TMP_ALLOC(d_runs, int, n_ent + 1);         // run lengths
+  int nruns = 0;
+  std::vector<long long> keys_host;  // unique local block keys
   {
     TMP_ALLOC(d_keys, long long, n_ent);
     TMP_ALLOC(d_vals, long long, n_ent);
-    if (P > 0) k_pair_fill<<<nblk(P, T), T, 0, st>>>((int)P, (long long)C, pb.pt_off, pb.cam, d_ent_off, d_keys, d_vals);
+    if (P > 0)
+      k_pair_fill<<<nblk(P, T), T, 0, st>>>((int)P, (long long)C, pb.pt_off, pb.cam, d_ent_off, d_pt_tile, d_keys, d_vals);
     if (n_ent > 0) {
+      const double kmax = (double)CC * (double)(pb.schur_tiles ? pb.n_st : 1);
       int end_bit = 1;
-      while (end_bit < 63 && ((long long)1 << end_bit) < (long long)C * C) ++end_bit;
+      while (end_bit < 63 && (double)((long long)1 << end_bit) < kmax) ++end_bit;
       size_t bytes = 0;
-      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_keys, d_keys_sorted, d_vals, pb.ent, (int)n_ent, 0, end_bit, st);
+      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_keys, d_keys_sorted, d_vals, d_ent64, (int)n_ent, 0, end_bit, st);
       TMP_ALLOC(d_sort, char, bytes);
-      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort, bytes, d_keys, d_keys_sorted, d_vals, pb.ent, (int)n_ent, 0,
+      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort, bytes, d_keys, d_keys_sorted, d_vals, d_ent64, (int)n_ent, 0,
                                                  end_bit, st));
-      TMP_ALLOC(d_uniq, long long, n_ent);
-      TMP_ALLOC(d_runs, int, n_ent);
       TMP_ALLOC(d_nruns, int, 1);
       bytes = 0;
       cub::DeviceRunLengthEncode::Encode(nullptr, bytes, d_keys_sorted, d_uniq, d_runs, d_nruns, (int)n_ent, st);
       TMP_ALLOC(d_rle, char, bytes);
       BA_CUDA(h, cub::DeviceRunLengthEncode::Encode(d_rle, bytes, d_keys_sorted, d_uniq, d_runs, d_nruns, (int)n_ent, st));
-      int nruns = 0;
       BA_CUDA(h, cudaMemcpyAsync(&nruns, d_nruns, sizeof(int), cudaMemcpyDeviceToHost, st));
       BA_CUDA(h, cudaStreamSynchronize(st));
-      keys_host.resize(nruns);
-      BA_CUDA(h, cudaMemcpy(keys_host.data(), d_uniq, (size_t)nruns * sizeof(long long), cudaMemcpyDeviceToHost));
+      if (!pb.schur_tiles) {
+        keys_host.resize(nruns);
+        BA_CUDA(h, cudaMemcpy(keys_host.data(), d_uniq, (size_t)nruns * sizeof(long long), cudaMemcpyDeviceToHost));
+      } else {
+        // block keys of the cells -> sort -> unique
+        TMP_ALLOC(d_bk, long long, nruns);
+        TMP_ALLOC(d_bk_sorted, long long, nruns);
+        TMP_ALLOC(d_bk_uniq, long long, nruns);
+        TMP_ALLOC(d_bk_cnt, int, nruns);
+        k_mod_keys<<<nblk(nruns, T), T, 0, st>>>(nruns, d_uniq, CC, d_bk);
+        int eb = 1;
+        while (eb < 63 && (double)((long long)1 << eb) < (double)CC) ++eb;
+        bytes = 0;
+        cub::DeviceRadixSort::SortKeys(nullptr, bytes, d_bk, d_bk_sorted, nruns, 0, eb, st);
+        TMP_ALLOC(d_sort2, char, bytes);
+        BA_CUDA(h, cub::DeviceRadixSort::SortKeys(d_sort2, bytes, d_bk, d_bk_sorted, nruns, 0, eb, st));
+        bytes = 0;
+        cub::DeviceRunLengthEncode::Encode(nullptr, bytes, d_bk_sorted, d_bk_uniq, d_bk_cnt, d_nruns, nruns, st);
+        TMP_ALLOC(d_rle2, char, bytes);
+        BA_CUDA(h, cub::DeviceRunLengthEncode::Encode(d_rle2, bytes, d_bk_sorted, d_bk_uniq, d_bk_cnt, d_nruns, nruns, st));
+        int nb = 0;
+        BA_CUDA(h, cudaMemcpyAsync(&nb, d_nruns, sizeof(int), cudaMemcpyDeviceToHost, st));
+        BA_CUDA(h, cudaStreamSynchronize(st));
+        keys_host.resize(nb);
+        BA_CUDA(h, cudaMemcpy(keys_host.data(), d_bk_uniq, (size_t)nb * sizeof(long long), cudaMemcpyDeviceToHost));
+      }
     }
   }
 
@@ -321,12 +481,12 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   const int n_blk = (int)keys_host.size();
   pb.n_blk = n_blk;
 
-  // entry range of every global block in the local sorted entry list
+  // entry range of every global block in the local sorted entry list (stream mode only)
   std::vector<long long> h_blk_off(n_blk + 1, 0);
-  {
-    TMP_ALLOC(d_gkeys, long long, n_blk);
+  TMP_ALLOC(d_gkeys, long long, n_blk);
+  BA_CUDA(h, cudaMemcpyAsync(d_gkeys, keys_host.data(), (size_t)n_blk * sizeof(long long), cudaMemcpyHostToDevice, st));
+  if (!pb.schur_tiles) {
     TMP_ALLOC(d_blk_off, long long, n_blk + 1);
-    BA_CUDA(h, cudaMemcpyAsync(d_gkeys, keys_host.data(), (size_t)n_blk * sizeof(long long), cudaMemcpyHostToDevice, st));
     k_lower_bound<<<nblk(n_blk + 1, T), T, 0, st>>>(n_blk, d_gkeys, n_ent, d_keys_sorted, d_blk_off);
     BA_CUDA(h, cudaMemcpyAsync(h_blk_off.data(), d_blk_off, (size_t)(n_blk + 1) * sizeof(long long),
                                cudaMemcpyDeviceToHost, st));
@@ -370,6 +530,76 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.bsr_rowptr, rowptr)) return rc;
     if (int rc = upload(h, &pb.bsr_col, col)) return rc;
     if (int rc = upload(h, &pb.bsr_src, src)) return rc;
+  }
+  // ---- 8. tile mode: slots = (tile, block) cells ordered inside each tile by decreasing entry count,
+  //         per-block reduce lists, entries packed to tile-local 16-bit indices
+  if (pb.schur_tiles) {
+    const int n_cell = nruns;
+    DEV_ALLOC(pb.tent, unsigned, n_ent);
+    DEV_ALLOC(pb.tile_slot_off, int, pb.n_st + 1);
+    DEV_ALLOC(pb.tile_ent_off, int, pb.n_st + 1);
+    DEV_ALLOC(pb.blk_slot_off, int, n_blk + 1);
+    BA_CUDA(h, cudaMemsetAsync(pb.tile_slot_off, 0, (pb.n_st + 1) * sizeof(int), st));
+    BA_CUDA(h, cudaMemsetAsync(pb.tile_ent_off, 0, (pb.n_st + 1) * sizeof(int), st));
+    BA_CUDA(h, cudaMemsetAsync(pb.blk_slot_off, 0, (n_blk + 1) * sizeof(int), st));
+    int n_slot = 0;
+    struct { int *sub_off = nullptr, *cell_off = nullptr, *cell_blk = nullptr, *cell_tile = nullptr; } tile_scratch;
+    if (n_cell > 0) {
+      TMP_ALLOC(d_cell_off, int, n_cell + 1);
+      TMP_ALLOC(d_cell_blk, int, n_cell);
+      TMP_ALLOC(d_cell_tile, int, n_cell);
+      TMP_ALLOC(d_nsub, int, n_cell + 1);
+      TMP_ALLOC(d_sub_off, int, n_cell + 1);
+      tile_scratch.sub_off = d_sub_off; tile_scratch.cell_off = d_cell_off;
+      tile_scratch.cell_blk = d_cell_blk; tile_scratch.cell_tile = d_cell_tile;
+      BA_CUDA(h, cudaMemsetAsync(d_runs + n_cell, 0, sizeof(int), st));
+      BA_CUDA(h, cudaMemsetAsync(d_nsub + n_cell, 0, sizeof(int), st));
+      size_t bytes = 0;
+      cub::DeviceScan::ExclusiveSum(nullptr, bytes, d_runs, d_cell_off, n_cell + 1, st);
+      TMP_ALLOC(d_scan2, char, bytes);
+      BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan2, bytes, d_runs, d_cell_off, n_cell + 1, st));
+      k_cell_meta<<<nblk(n_cell, T), T, 0, st>>>(n_cell, d_uniq, d_runs, CC, d_gkeys, n_blk, d_cell_blk, d_cell_tile, d_nsub);
+      BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan2, bytes, d_nsub, d_sub_off, n_cell + 1, st));
+      BA_CUDA(h, cudaMemcpyAsync(&n_slot, d_sub_off + n_cell, sizeof(int), cudaMemcpyDeviceToHost, st));
+      BA_CUDA(h, cudaStreamSynchronize(st));
+    }
+    pb.n_slot = n_slot;
+    DEV_ALLOC(pb.slot_a, int, n_slot);
+    DEV_ALLOC(pb.slot_n, int, n_slot);
+    DEV_ALLOC(pb.blk_slots, int, n_slot);
+    if (n_slot > 0) {
+      // (re-use of the scratch names above is scoped to the previous block; fetch them again)
+      TMP_ALLOC(d_sub_a, int, n_slot);
+      TMP_ALLOC(d_sub_n, int, n_slot);
+      TMP_ALLOC(d_sub_blk, int, n_slot);
+      TMP_ALLOC(d_key2, long long, n_slot);
+      TMP_ALLOC(d_key2s, long long, n_slot);
+      TMP_ALLOC(d_si, int, n_slot);
+      TMP_ALLOC(d_order, int, n_slot);
+      TMP_ALLOC(d_slot_blk, int, n_slot);
+      TMP_ALLOC(d_blk_sorted, int, n_slot);
+      k_sub_fill<<<nblk(n_cell, T), T, 0, st>>>(n_cell, tile_scratch.sub_off, tile_scratch.cell_off, d_runs,
+                                                tile_scratch.cell_blk, tile_scratch.cell_tile, d_sub_a, d_sub_n, d_sub_blk,
+                                                d_key2);
+      k_iota<<<nblk(n_slot, T), T, 0, st>>>(n_slot, d_si);
+      size_t bytes = 0;
+      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_key2, d_key2s, d_si, d_order, n_slot, 0, 63, st);
+      TMP_ALLOC(d_sort3, char, bytes);
+      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort3, bytes, d_key2, d_key2s, d_si, d_order, n_slot, 0, 63, st));
+      k_slot_fill<<<nblk(n_slot, T), T, 0, st>>>(n_slot, d_order, d_sub_a, d_sub_n, d_sub_blk, pb.slot_a, pb.slot_n,
+                                                 d_slot_blk);
+      k_tile_slot_off<<<nblk(pb.n_st + 1, T), T, 0, st>>>(pb.n_st, n_slot, d_key2s, pb.tile_slot_off);
+      int eb = 1;
+      while (eb < 31 && (1 << eb) < n_blk) ++eb;
+      bytes = 0;
+      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_slot_blk, d_blk_sorted, d_si, pb.blk_slots, n_slot, 0, eb, st);
+      TMP_ALLOC(d_sort4, char, bytes);
+      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort4, bytes, d_slot_blk, d_blk_sorted, d_si, pb.blk_slots, n_slot, 0,
+                                                 eb, st));
+      k_offsets<<<nblk(n_slot, T), T, 0, st>>>(n_slot, n_blk, d_blk_sorted, pb.blk_slot_off);
+      k_pack_entries<<<nblk(n_ent, T), T, 0, st>>>(n_ent, d_ent64, pb.st_off, pb.n_st, pb.tent);
+      k_tile_ent_off<<<nblk(pb.n_st + 1, T), T, 0, st>>>(pb.n_st, (int)n_ent, d_keys_sorted, CC, pb.tile_ent_off);
+    }
   }
   BA_CUDA(h, cudaStreamSynchronize(st));
   BA_CUDA(h, cudaGetLastError());

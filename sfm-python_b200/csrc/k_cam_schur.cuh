@@ -178,6 +178,102 @@ k_schur(Problem pb, const double* __restrict__ Y, double* __restrict__ spart) {
   cp_async_wait<0>();
 }
 
+// ---- Schur tile kernel (default path).  A CTA stages the Y records of one tile of observations (whole points,
+// <= 1344 observations = 193.5 KB) into shared memory ONCE with fully coalesced 16-byte LDGSTS copies, then every
+// lane owns one "slot" = all pair entries of one (tile, block) cell and accumulates its 6x6 partial in registers,
+// reading both records of an entry from shared memory.  Compared with the streaming kernel this cuts the L2->SM
+// traffic from 288 B per pair entry to 144 B per observation (6x less at 5 observations per point); no cross-lane
+// reduction is needed, slots of a tile are sorted by entry count so the lanes of a warp finish together.
+constexpr int SCHT_THREADS = 512;
+constexpr int SCHT_G = 4;                                   // lanes cooperating on one slot
+constexpr int SCHT_ENT_CAP = 9216;                          // tile entries staged in shared memory (36 KB)
+constexpr int SCHT_SMEM_MAX = SCHUR_TILE_MAX * 144 + SCHT_ENT_CAP * 4;   // 230400 B
+
+__device__ __forceinline__ void cp_async4(void* dst_smem, const void* src) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d), "l"(src) : "memory");
+}
+
+__global__ void __launch_bounds__(SCHT_THREADS)
+k_schur_tiles(Problem pb, const double* __restrict__ Y, double* __restrict__ spart) {
+  extern __shared__ __align__(16) unsigned char sY_raw[];
+  const double* sY = reinterpret_cast<const double*>(sY_raw);
+  unsigned* sE = reinterpret_cast<unsigned*>(sY_raw + (size_t)pb.tile_obs * 144);
+  const int g = threadIdx.x % SCHT_G, sub = threadIdx.x / SCHT_G;
+  for (int t = blockIdx.x; t < pb.n_st; t += gridDim.x) {
+    const int a = pb.st_off[t], n = pb.st_off[t + 1] - a;
+    const int te0 = pb.tile_ent_off[t], nte = pb.tile_ent_off[t + 1] - te0;
+    const bool ent_in_smem = nte <= SCHT_ENT_CAP;
+    const char* src = reinterpret_cast<const char*>(Y + 18 * (int64_t)a);
+    for (int q = threadIdx.x; q < n * 9; q += SCHT_THREADS) cp_async16(sY_raw + 16 * q, src + 16 * (int64_t)q);
+    if (ent_in_smem)
+      for (int q = threadIdx.x; q < nte; q += SCHT_THREADS) cp_async4(sE + q, pb.tent + te0 + q);
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncthreads();
+    const int s_lo = pb.tile_slot_off[t], s_hi = pb.tile_slot_off[t + 1];
+    for (int s0 = s_lo; s0 < s_hi; s0 += SCHT_THREADS / SCHT_G) {
+      const int s = s0 + sub;
+      const bool active = s < s_hi;
+      const int ea = active ? pb.slot_a[s] : 0, en = active ? pb.slot_n[s] : 0;
+      const unsigned* ent = ent_in_smem ? (sE + (ea - te0)) : (pb.tent + ea);
+      double acc[36];
+#pragma unroll
+      for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+      for (int e = g; e < en; e += SCHT_G) {
+        const unsigned ij = ent[e];
+        const double2* pi = reinterpret_cast<const double2*>(sY + 18 * (ij >> 16));
+        const double2* pj = reinterpret_cast<const double2*>(sY + 18 * (ij & 0xffffu));
+        double yj[18];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) { const double2 v = pj[k]; yj[2 * k] = v.x; yj[2 * k + 1] = v.y; }
+#pragma unroll
+        for (int h = 0; h < 3; ++h) {
+          const double2 t0 = pi[3 * h], t1 = pi[3 * h + 1], t2 = pi[3 * h + 2];
+          const double yi[6] = {t0.x, t0.y, t1.x, t1.y, t2.x, t2.y};
+#pragma unroll
+          for (int r2 = 0; r2 < 2; ++r2)
+#pragma unroll
+            for (int c = 0; c < 6; ++c)
+              acc[6 * (2 * h + r2) + c] += yi[3 * r2] * yj[3 * c] + yi[3 * r2 + 1] * yj[3 * c + 1] +
+                                           yi[3 * r2 + 2] * yj[3 * c + 2];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < 36; ++k) {
+        acc[k] += __shfl_xor_sync(FULL, acc[k], 1);
+        acc[k] += __shfl_xor_sync(FULL, acc[k], 2);
+      }
+      if (active && g == 0) {
+        double2* o = reinterpret_cast<double2*>(spart + 36 * (int64_t)s);
+#pragma unroll
+        for (int k = 0; k < 18; ++k) o[k] = make_double2(acc[2 * k], acc[2 * k + 1]);
+      }
+    }
+    __syncthreads();  // the next tile overwrites the staged records
+  }
+}
+
+// tile mode: Sup[g] = [g diagonal ? U*_c : 0] - sum over the slots of block g (fixed order => reproducible)
+__global__ void k_schur_reduce_tiles(int n_blk, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
+                                     const int* __restrict__ blk_slot_off, const int* __restrict__ blk_slots,
+                                     const double* __restrict__ spart, const double* __restrict__ U, double lambda,
+                                     double* __restrict__ Sup) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n_blk * 36) return;
+  const int g = (int)(t / 36), e = (int)(t % 36);
+  double s = 0.0;
+  for (int q = blk_slot_off[g]; q < blk_slot_off[g + 1]; ++q) s += spart[(int64_t)blk_slots[q] * 36 + e];
+  double val = -s;
+  if (blk_r[g] == blk_c[g]) {
+    const int r = e / 6, c = e % 6;
+    double uv = U[blk_r[g] * 21 + tri6(min(r, c), max(r, c))];
+    if (r == c) uv *= (1.0 + lambda);
+    val += uv;
+  }
+  Sup[t] = val;
+}
+
 // Sup[g] = [g diagonal ? U*_c : 0] - sum of chunk partials      (U* = U + lambda diag U)
 __global__ void k_schur_reduce(int n_blk, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
                                const int* __restrict__ blk_choff, const double* __restrict__ spart,

@@ -106,17 +106,29 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
     cudaFuncSetAttribute(k_schur<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
     cudaFuncSetAttribute(k_schur<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
     cudaFuncSetAttribute(k_schur<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
+    cudaFuncSetAttribute(k_schur_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, SCHT_SMEM_MAX);
     const char* e = getenv("B200BA_SCHUR_DIAG");  // diagnostic only (wrong results): 1 = fetch only, 2 = multiply only
     schur_mode = e ? atoi(e) : 0;
   }
-  const int sg = (int)std::min<int64_t>(cdiv(pb.n_sch, SCH_WARPS), (int64_t)h->sm_count);
-  t.begin();
-  if (schur_mode == 1) k_schur<1><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
-  else if (schur_mode == 2) k_schur<2><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
-  else k_schur<0><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
-  t.end(&h->st.ms_schur);
-  k_schur_reduce<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_choff,
-                                                                    w.spart, w.U, lambda, w.Sup);
+  if (pb.schur_tiles) {
+    const int smem = pb.tile_obs * 144 + SCHT_ENT_CAP * 4;
+    const int per_sm = std::max(1, std::min(4, (220 * 1024) / std::max(smem, 1)));
+    const int tg = (int)std::min<int64_t>(std::max(pb.n_st, 1), (int64_t)h->sm_count * per_sm);
+    t.begin();
+    k_schur_tiles<<<tg, SCHT_THREADS, smem, st>>>(pb, w.Y, w.spart);
+    t.end(&h->st.ms_schur);
+    k_schur_reduce_tiles<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(
+        pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_slot_off, pb.blk_slots, w.spart, w.U, lambda, w.Sup);
+  } else {
+    const int sg = (int)std::min<int64_t>(cdiv(pb.n_sch, SCH_WARPS), (int64_t)h->sm_count);
+    t.begin();
+    if (schur_mode == 1) k_schur<1><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
+    else if (schur_mode == 2) k_schur<2><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
+    else k_schur<0><<<sg, SCH_WARPS * 32, SCH_SMEM, st>>>(pb, w.Y, w.spart);
+    t.end(&h->st.ms_schur);
+    k_schur_reduce<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_choff,
+                                                                      w.spart, w.U, lambda, w.Sup);
+  }
   h->st.launches += 6;
   h->st.n_linearize += 1;
 }
