@@ -63,7 +63,14 @@ __global__ void k_cam_prep(int C, const double* __restrict__ xc, const double* _
   double out[CAMPREP_STRIDE];
   cam_prep(cam, out);
 #pragma unroll
-  for (int k = 0; k < CAMPREP_STRIDE; ++k) camprep[CAMPREP_STRIDE * c + k] = out[k];
+  for (int k = 0; k < CAMPREP_FIELDS; ++k) camprep[(int64_t)k * C + c] = out[k];  // field-major: see load_cam
+}
+
+// camprep is stored field-major ([21][C]): the lanes of a warp look at a handful of neighbouring cameras, so one
+// load instruction touches 1-2 cache lines instead of one line per distinct camera.
+__device__ __forceinline__ void load_cam(const double* __restrict__ camprep, int64_t C, int c, double* __restrict__ cp) {
+#pragma unroll
+  for (int k = 0; k < CAMPREP_FIELDS; ++k) cp[k] = camprep[(int64_t)k * C + c];
 }
 
 // ------------------------------------------------------------------ residual
@@ -75,8 +82,9 @@ __global__ void __launch_bounds__(256) k_residual(Problem pb, const double* __re
   double acc = 0.0;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pb.N; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = pb.cam[i], p = pb.pt[i];
-    double r0, r1;
-    project_residual(camprep + CAMPREP_STRIDE * c, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i],
+    double r0, r1, cp[CAMPREP_FIELDS];
+    load_cam(camprep, pb.C, c, cp);
+    project_residual(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i],
                      r0, r1);
     acc += r0 * r0 + r1 * r1;
     if (r_out) {
@@ -103,8 +111,9 @@ __global__ void __launch_bounds__(JT) k_jacobian(Problem pb, const double* __res
   double r0 = 0, r1 = 0, Jc[12], Jp[6];
   if (i < pb.N) {
     const int c = pb.cam[i], p = pb.pt[i];
-    project_jac(camprep + CAMPREP_STRIDE * c, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0,
-                r1, Jc, Jp);
+    double cp[CAMPREP_FIELDS];
+    load_cam(camprep, pb.C, c, cp);
+    project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp);
   }
   if (pb.perm) {
     if (i < pb.N) {

@@ -22,7 +22,8 @@
 
 namespace b200ba {
 
-constexpr int CAMPREP_STRIDE = 24;  // R[9] Jr[9] T[3] pad[3]  -> 192 B = 6 sectors
+constexpr int CAMPREP_STRIDE = 24;  // scratch size of cam_prep's output: R[9] Jr[9] T[3] pad[3]
+constexpr int CAMPREP_FIELDS = 21;  // stored fields per camera (device layout is field-major [21][C])
 constexpr double SMALL_ANGLE = 1e-4;
 
 struct Intrinsics {

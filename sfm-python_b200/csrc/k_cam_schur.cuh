@@ -16,7 +16,8 @@ k_cam_side(Problem pb, const double* __restrict__ x, const double* __restrict__ 
   const double* xp = x + 6 * pb.C;
   for (int ch = warp; ch < pb.n_cch; ch += nwarp) {
     const int c = pb.cch_cam[ch], a = pb.cch_a[ch], b = pb.cch_b[ch];
-    const double* cp = camprep + CAMPREP_STRIDE * c;
+    double cp[CAMPREP_FIELDS];
+    load_cam(camprep, pb.C, c, cp);
     double acc[33];
 #pragma unroll
     for (int k = 0; k < 33; ++k) acc[k] = 0.0;
