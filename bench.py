@@ -218,7 +218,11 @@ def run_b200(a, rank, world, local_rank):
         lin()
     sp = eng.stats()
     eng.set_profiling(False)
-    kern_ms = {k: sp[k] / reps for k in ("ms_linearize_points", "ms_camera_blocks", "ms_schur", "ms_allreduce")}
+    fused = int(st["n_self_slots"]) > 0
+    kkeys = ("ms_lin_fused", "ms_slot_reduce", "ms_allreduce") if fused else \
+            ("ms_linearize_points", "ms_camera_blocks", "ms_schur", "ms_allreduce")
+    kern_ms = {k: sp[k] / reps for k in kkeys}
+    fp64_peak = eng.fp64_peak_tflops()
 
     # ---- LM iterations/s: device-resident solve, exactly K iterations (tolerances off)
     solver = "cholesky" if n_cam <= 64 else "pcg"
@@ -259,7 +263,7 @@ def run_b200(a, rank, world, local_rank):
 
     if rank != 0:
         return
-    # ---- roofline of the dominant kernel of the step
+    # ---- roofline of the dominant kernel of the step (SURVEY.md 8d family L)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -268,20 +272,39 @@ def run_b200(a, rank, world, local_rank):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     n_loc, p_loc = len(ci), hi - lo
     n_ent, n_blk = int(st["schur_entries"]), int(st["schur_blocks"])
-    alg = {  # compulsory bytes per launch of each kernel family on this rank
-        "ms_linearize_points": 24 * n_loc + 24 * p_loc + 192 * n_cam + (144 + 32) * n_loc + (96 + 24) * p_loc,
-        "ms_camera_blocks": (8 + 32 + 24) * n_loc + 192 * n_cam + 33 * 8 * (n_loc // 256 + n_cam),
-        "ms_schur": 144 * n_loc + 8 * n_ent + 288 * (n_ent // 512 + n_blk),
-    }
-    dom = max(alg, key=lambda k: kern_ms[k])
-    ach = alg[dom] / (kern_ms[dom] * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": {"ms_linearize_points": "k_lin_points", "ms_camera_blocks": "k_cam_side",
-                                       "ms_schur": "k_schur"}[dom],
-            "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+    kdeg = deg[lo:hi].astype(np.float64)
+    # compulsory bytes of the linearisation contract: observations in, points in, cameras in, per-point factor + gradient
+    # out (72 B), reduced system out (block-sparse upper triangle, b, g_c)
+    lin_bytes = 24 * n_loc + 24 * p_loc + 48 * n_cam + 72 * p_loc + 288 * n_blk + 96 * n_cam
+    # algorithmic flops: 350 per observation + per point [3x3 factor 40 + 120 k + 216 k (k + 1) / 2]
+    lin_flops = 350.0 * n_loc + float(np.sum(40.0 + 120.0 * kdeg + 108.0 * kdeg * (kdeg + 1.0)))
+    if fused:
+        dom, dom_name = "ms_lin_fused", "k_lin_fused"
+        alg = {"ms_lin_fused": lin_bytes}
+    else:
+        alg = {"ms_linearize_points": 24 * n_loc + 24 * p_loc + 192 * n_cam + (144 + 32) * n_loc + (96 + 24) * p_loc,
+               "ms_camera_blocks": (8 + 32 + 24) * n_loc + 192 * n_cam + 33 * 8 * (n_loc // 256 + n_cam),
+               "ms_schur": 144 * n_loc + 8 * n_ent + 288 * (n_ent // 512 + n_blk)}
+        dom = max(alg, key=lambda k: kern_ms[k])
+        dom_name = {"ms_linearize_points": "k_lin_points", "ms_camera_blocks": "k_cam_side", "ms_schur": "k_schur_tiles"}[dom]
+    t_dom = max(kern_ms[dom], 1e-9) * 1e-3
+    ach = alg[dom] / t_dom / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(f"{dom_name}:{a.workload}")
+    except Exception:
+        pass
+    roof = {"bound": "hbm", "kernel": dom_name, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+            "traffic": traffic,
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
             "algorithmic_bytes_per_launch": alg[dom], "kernel_ms": kern_ms[dom],
-            "all_kernels": {k: {"ms": kern_ms[k], "GB/s": alg[k] / (kern_ms[k] * 1e-3) / 1e9 if kern_ms[k] > 0 else None}
-                            for k in alg}}
+            "note": "compulsory bytes of the linearisation contract; the kernel is FP64-pipe-bound, see roofline_fp64"}
+    tf = lin_flops / (max(kern_ms.get("ms_lin_fused", ms_step), 1e-9) * 1e-3) / 1e12
+    roof64 = {"bound": "fp64", "kernel": dom_name if fused else "linearisation (all kernels)", "achieved": tf,
+              "peak": fp64_peak, "unit": "TFLOP/s", "frac": tf / fp64_peak if fp64_peak > 0 else None,
+              "peak_source": "b200ba_fp64_peak: unrolled DFMA chains over all SMs, measured in this run",
+              "algorithmic_flops_per_launch": lin_flops,
+              "flops_per_compulsory_byte": lin_flops / lin_bytes}
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3),
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic", "impl": "b200",
@@ -290,7 +313,9 @@ def run_b200(a, rank, world, local_rank):
                       "cache": "inputs exceed L2 (>= 3.5 GB touched per step)" if n_obs >= 2_000_000 else
                                "working set fits L2 (latency-bound config)", "lambda": lam,
                       "schur_blocks": n_blk, "schur_pair_entries_rank0": n_ent},
-           "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "kernel_ms": kern_ms}
+           "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "roofline_fp64": roof64, "kernel_ms": kern_ms,
+           "tiles": {"n_tiles": int(st["n_tiles"]), "pair_slots": int(st["n_pair_slots"]),
+                     "self_slots": int(st["n_self_slots"])}}
     out.update(lm)
     if not a.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(a.workload, a.seed, a.cpu_sample_obs)

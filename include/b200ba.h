@@ -86,6 +86,8 @@ typedef struct b200ba_stats {
   int64_t n_linearize, n_pcg_iters;
   int64_t schur_entries, schur_blocks;
   int64_t bytes_device;   /* device memory held by the handle */
+  double ms_lin_fused, ms_slot_reduce;   /* fused linearisation + Schur kernel and its fixed-order partial reduction */
+  int64_t n_tiles, n_pair_slots, n_self_slots;
 } b200ba_stats;
 
 int b200ba_version(void);
@@ -139,6 +141,9 @@ int b200ba_get_stats(b200ba_handle* h, b200ba_stats* out);
 int b200ba_reset_stats(b200ba_handle* h);
 /* on != 0: bracket every kernel family with CUDA events and accumulate b200ba_stats.ms_* (adds syncs) */
 int b200ba_set_profiling(b200ba_handle* h, int on);
+/* Roofline denominator: FP64 FMA throughput of this device in TFLOP/s, measured by an unrolled DFMA-chain kernel
+ * (no reference counterpart; MEASURED_PEAKS.json has no FP64 figure). Needs a problem (uses its scratch). */
+int b200ba_fp64_peak(b200ba_handle* h, double* tflops_out);
 /* stream the library launches on (so callers can record CUDA events around its kernels) */
 void* b200ba_stream(b200ba_handle* h);
 

@@ -33,7 +33,9 @@ class Stats(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("ms_cam_prep", "ms_linearize_points", "ms_camera_blocks", "ms_schur",
                                           "ms_allreduce", "ms_camera_solve", "ms_backsub_trial", "ms_residual")] + \
                [(n, C.c_int64) for n in ("launches", "n_linearize", "n_pcg_iters", "schur_entries", "schur_blocks",
-                                         "bytes_device")]
+                                         "bytes_device")] + \
+               [(n, C.c_double) for n in ("ms_lin_fused", "ms_slot_reduce")] + \
+               [(n, C.c_int64) for n in ("n_tiles", "n_pair_slots", "n_self_slots")]
 
 
 _P = C.c_void_p
@@ -61,6 +63,7 @@ SIGNATURES = {
     "b200ba_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "b200ba_reset_stats": (C.c_int, [_P]),
     "b200ba_set_profiling": (C.c_int, [_P, C.c_int]),
+    "b200ba_fp64_peak": (C.c_int, [_P, _D]),
     "b200ba_stream": (_P, [_P]),
     "b200ba_debug_fetch": (C.c_int64, [_P, C.c_char_p, _P, C.c_int64]),
 }

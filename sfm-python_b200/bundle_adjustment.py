@@ -208,6 +208,11 @@ class Engine:
     def reset_stats(self):
         self._check(self.lib.b200ba_reset_stats(self.h))
 
+    def fp64_peak_tflops(self):
+        v = C.c_double(0.0)
+        self._check(self.lib.b200ba_fp64_peak(self.h, C.byref(v)))
+        return v.value
+
     def set_profiling(self, on):
         self._check(self.lib.b200ba_set_profiling(self.h, int(bool(on))))
 

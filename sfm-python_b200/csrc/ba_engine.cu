@@ -123,10 +123,10 @@ static int alloc_work(Handle* h) {
 #define WALLOC(ptr, count)                                                                    \
   ptr = (double*)dalloc(h, (size_t)std::max<int64_t>((count), 1) * sizeof(double));           \
   if (!ptr) return B200BA_OOM
-  WALLOC(w.x, nx);
-  WALLOC(w.xn, nx);
-  WALLOC(w.camprep, C * CAMPREP_STRIDE);
-  WALLOC(w.camprep_n, C * CAMPREP_STRIDE);
+  WALLOC(w.x, nx + 2);
+  WALLOC(w.xn, nx + 2);
+  WALLOC(w.camprep, (C + 2) * CAMPREP_STRIDE);   // field-major [21][Cs], Cs <= C + 1
+  WALLOC(w.camprep_n, (C + 2) * CAMPREP_STRIDE);
   WALLOC(w.Y, N * 18);
   WALLOC(w.rr, N * 4);
   WALLOC(w.pp, P * 12);
@@ -134,6 +134,7 @@ static int alloc_work(Handle* h) {
   WALLOC(w.cpart, (int64_t)pb.n_cch * 33);
   WALLOC(w.spart, (int64_t)std::max(pb.n_sch, pb.n_slot) * 36);
   WALLOC(w.U, C * 21);
+  WALLOC(w.dpart, (int64_t)pb.n_dslot * 40);
   w.comm_count = (int64_t)pb.n_blk * 36 + 18 * C + S_NSUM;
   WALLOC(w.comm, w.comm_count);
   w.Sup = w.comm;
@@ -211,6 +212,19 @@ int fetch_scalars(Handle* h) {
   BA_CUDA(h, cudaMemcpyAsync(w.h_scal, w.scal, NSCAL * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   BA_CUDA(h, cudaMemcpyAsync(w.h_scal + NSCAL, w.sums, S_NSUM * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   BA_CUDA(h, cudaStreamSynchronize(h->stream));
+  int flow_err = 0;
+  memcpy(&flow_err, w.h_scal + S_FLOW_ERR, sizeof(int));
+  if (flow_err) return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
+  return 0;
+}
+
+// test hooks and stats: the error word of the dataflow kernel (set instead of hanging the device)
+int check_flow_error(Handle* h) {
+  if (!h->has_problem || !h->pb.flow) return 0;
+  int flow_err = 0;
+  BA_CUDA(h, cudaMemcpyAsync(&flow_err, h->w.scal + S_FLOW_ERR, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+  BA_CUDA(h, cudaStreamSynchronize(h->stream));
+  if (flow_err) return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
   return 0;
 }
 

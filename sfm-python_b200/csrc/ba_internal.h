@@ -15,7 +15,15 @@ namespace b200ba {
 constexpr int LIN_WARPS = 8;       // warps per CTA in the point-major kernels
 constexpr int CCHUNK = 256;        // observations per camera-side chunk (one warp)
 constexpr int SCHUNK = 512;
-constexpr int SCHUR_TILE_MAX = 1344;  // observations per Schur tile: 1344 * 144 B = 193.5 KB of shared memory        // pair entries per Schur chunk (one warp)
+constexpr int SCHUR_TILE_MAX = 1344;  // observations per Schur tile (unfused path): 1344 * 144 B = 193.5 KB of shared memory
+constexpr int FUSED_REC_BYTES = 176;  // per-observation record of k_lin_fused (22 doubles)
+constexpr int FUSED_TILE_2CTA = 640;  // 640 * 176 B = 110 KB: two CTAs of 256 threads per SM
+constexpr int FUSED_TILE_1CTA = 1312; // 1312 * 176 B = 225.5 KB: one CTA of 512 threads per SM
+// dataflow kernel (k_lin_flow): one persistent CTA of 512 threads per SM, two record buffers, bulk-copy staging
+constexpr int FLOW_TILE = 512;        // observations per tile: 2 * 512 * 176 B = 176 KB of records
+constexpr int FLOW_CAM_SPAN = 64;     // staged camera window per tile (21 x 64 doubles)
+constexpr int FLOW_META_CAP = 8192;   // staged tile metadata (slot descriptors + entries), bytes
+constexpr int FLOW_IDX_BYTES = (FLOW_TILE + 8) * 4;  // staged cam[] / pt[] window incl. alignment slack
 constexpr int NSCAL = 32;          // device scalar slots
 constexpr int DENSE_MAX_CAM = 512; // dense S export / Cholesky limit
 
@@ -37,12 +45,14 @@ enum Scal {
   S_DC_RES = 15,   // delta_c . (b - S delta_c)   (PCG residual term of the predicted reduction)
   S_PCG_ITERS = 16,
   S_SOLVE_FAIL = 17,
-  S_RES_COST2 = 18 // sum r^2 of b200ba_residuals
+  S_RES_COST2 = 18, // sum r^2 of b200ba_residuals
+  S_FLOW_ERR = 31   // (int) set by k_lin_flow when a dependency wait timed out
 };
 
 // One shard of a bundle-adjustment problem, resident in HBM.
 struct Problem {
   int64_t C = 0, P = 0, N = 0;
+  int64_t Cs = 0;           // row stride of the field-major camera prep table (C rounded up to even: 16-byte rows)
   Intrinsics K;
   // observations, point-major (sorted by point, stable)
   double* u = nullptr;      // [N]
@@ -87,6 +97,21 @@ struct Problem {
   int* tile_ent_off = nullptr;   // [n_st+1] entry range of each tile
   int* blk_slot_off = nullptr;   // [n_blk+1] reduce lists: slots of each block
   int* blk_slots = nullptr;      // [n_slot]
+  // fused kernel (k_lin_fused): pair entries exclude i == j; the tile's observations grouped by camera form "self" slots
+  bool fused = false;
+  int* st_wt_off = nullptr;      // [n_st+1] warp-tile range of each CTA tile
+  unsigned short* dent = nullptr;  // [N] tile-local observation index, grouped by (tile, camera)
+  int n_dslot = 0;
+  int* dslot_a = nullptr;        // [n_dslot] first entry in dent
+  int* dslot_n = nullptr;        // [n_dslot]
+  int* tile_dslot_off = nullptr; // [n_st+1]
+  int* cam_dslot_off = nullptr;  // [C+1] reduce lists: self slots of each camera
+  int* cam_dslots = nullptr;     // [n_dslot]
+  // dataflow kernel: per-tile info (4 x int4) and one contiguous metadata blob per tile (16-byte units)
+  bool flow = false;
+  int4* tile_info = nullptr;     // [n_st*4] {nA, n_pslot, n_dslot, flags} {blob_off16, blob_units16, cmin, cspan}
+                                 //           {obs0, n_obs, wt0, n_pent} {pslot_base, dslot_base, pt0, n_pts}
+  uint4* blob = nullptr;         // header(32 B) | pair slots (a, n) | self slots (a, n) | pair entries u32 | self entries u16
   // full (both triangles) block-CSR view for the PCG mat-vec
   int* bsr_rowptr = nullptr;  // [C+1]
   int* bsr_col = nullptr;     // [nnzb]
@@ -106,6 +131,7 @@ struct Work {
   double* cpart = nullptr;    // [n_cch*33]
   double* spart = nullptr;    // [n_sch*36]
   double* U = nullptr;        // [C*21]
+  double* dpart = nullptr;    // [n_dslot*40] self-slot partials of the fused kernel
   // ---- contiguous all-reduce buffer: Sup | b | gc | udiag | sums
   double* comm = nullptr;
   double* Sup = nullptr;      // [n_blk*36]
@@ -176,6 +202,7 @@ void launch_fix_diag(Handle* h);
 void launch_backsub_trial(Handle* h, double lambda);
 void launch_cam_dots(Handle* h);
 void launch_densify(Handle* h, double* dense /*6C x 6C*/);
+double measure_fp64_peak(Handle* h);
 
 // ---- ba_solve.cu
 int launch_pcg(Handle* h, double rtol, int max_iter);

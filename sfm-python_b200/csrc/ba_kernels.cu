@@ -9,6 +9,8 @@
 //   k_cam_side        camera-sorted accumulation of U_c, g_c, b_c without atomics
 //   k_schur           S -= sum Y_i Y_j^T over pair entries sorted by block, without atomics
 //   k_backsub_trial   delta_p back-substitution fused with the trial residual at x + delta
+//   k_lin_fused       (default) k_lin_points + k_cam_side + k_schur in one kernel: per-observation records live only in
+//                     shared memory (k_fused.cuh); the three kernels above remain as the fallback / A-B path
 #include "ba_internal.h"
 
 namespace b200ba {
@@ -50,7 +52,7 @@ __device__ __forceinline__ void block_sum(double* vals, double* smem /*[32*NV]*/
 }
 
 // ------------------------------------------------------------------ camera prep
-__global__ void k_cam_prep(int C, const double* __restrict__ xc, const double* __restrict__ dc,
+__global__ void k_cam_prep(int C, int64_t Cs, const double* __restrict__ xc, const double* __restrict__ dc,
                            double* __restrict__ x_out, double* __restrict__ camprep) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -63,10 +65,10 @@ __global__ void k_cam_prep(int C, const double* __restrict__ xc, const double* _
   double out[CAMPREP_STRIDE];
   cam_prep(cam, out);
 #pragma unroll
-  for (int k = 0; k < CAMPREP_FIELDS; ++k) camprep[(int64_t)k * C + c] = out[k];  // field-major: see load_cam
+  for (int k = 0; k < CAMPREP_FIELDS; ++k) camprep[(int64_t)k * Cs + c] = out[k];  // field-major: see load_cam
 }
 
-// camprep is stored field-major ([21][C]): the lanes of a warp look at a handful of neighbouring cameras, so one
+// camprep is stored field-major ([21][Cs], Cs = C rounded up to even): the lanes of a warp look at a handful of neighbouring cameras, so one
 // load instruction touches 1-2 cache lines instead of one line per distinct camera.
 __device__ __forceinline__ void load_cam(const double* __restrict__ camprep, int64_t C, int c, double* __restrict__ cp) {
 #pragma unroll
@@ -83,7 +85,7 @@ __global__ void __launch_bounds__(256) k_residual(Problem pb, const double* __re
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pb.N; i += (int64_t)gridDim.x * blockDim.x) {
     const int c = pb.cam[i], p = pb.pt[i];
     double r0, r1, cp[CAMPREP_FIELDS];
-    load_cam(camprep, pb.C, c, cp);
+    load_cam(camprep, pb.Cs, c, cp);
     project_residual(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i],
                      r0, r1);
     acc += r0 * r0 + r1 * r1;
@@ -112,7 +114,7 @@ __global__ void __launch_bounds__(JT) k_jacobian(Problem pb, const double* __res
   if (i < pb.N) {
     const int c = pb.cam[i], p = pb.pt[i];
     double cp[CAMPREP_FIELDS];
-    load_cam(camprep, pb.C, c, cp);
+    load_cam(camprep, pb.Cs, c, cp);
     project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp);
   }
   if (pb.perm) {
@@ -140,6 +142,8 @@ __global__ void __launch_bounds__(JT) k_jacobian(Problem pb, const double* __res
 #include "k_lin.cuh"
 #include "k_cam_schur.cuh"
 #include "k_backsub.cuh"
+#include "k_fused.cuh"
+#include "k_flow.cuh"
 
 }  // namespace
 

@@ -57,7 +57,7 @@ __global__ void k_iota(int64_t N, int* __restrict__ a) {
 }
 
 // ordered pairs (i,j) of one point's observations that land in the upper triangle (cam_i <= cam_j)
-__global__ void k_pair_count(int P, const int* __restrict__ pt_off, const int* __restrict__ cam,
+__global__ void k_pair_count(int P, const int* __restrict__ pt_off, const int* __restrict__ cam, bool skip_self,
                              long long* __restrict__ cnt) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
@@ -65,13 +65,13 @@ __global__ void k_pair_count(int P, const int* __restrict__ pt_off, const int* _
   long long n = 0;
   for (int i = a; i < b; ++i) {
     int ci = cam[i];
-    for (int j = a; j < b; ++j) n += (ci <= cam[j]);
+    for (int j = a; j < b; ++j) n += (ci <= cam[j]) && !(skip_self && i == j);
   }
   cnt[p] = n;
 }
 
 __global__ void k_pair_fill(int P, long long C, const int* __restrict__ pt_off, const int* __restrict__ cam,
-                            const long long* __restrict__ ent_off, const int* __restrict__ pt_tile,
+                            bool skip_self, const long long* __restrict__ ent_off, const int* __restrict__ pt_tile,
                             long long* __restrict__ keys, long long* __restrict__ vals) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
@@ -82,7 +82,7 @@ __global__ void k_pair_fill(int P, long long C, const int* __restrict__ pt_off, 
     int ci = cam[i];
     for (int j = a; j < b; ++j) {
       int cj = cam[j];
-      if (ci <= cj) {
+      if (ci <= cj && !(skip_self && i == j)) {
         keys[e] = tbase + (long long)ci * C + cj;
         vals[e] = ((long long)i << 32) | (unsigned int)j;
         ++e;
@@ -119,10 +119,12 @@ __global__ void k_cell_meta(int n, const long long* __restrict__ cellkey, const 
   const long long key = cellkey[c];
   const long long tile = key / CC, bk = key - tile * CC;
   int lo = 0, hi = n_blk;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (gkeys[mid] < bk) lo = mid + 1; else hi = mid;
-  }
+  if (!gkeys) lo = (int)bk;  // identity: the id is the group index
+  else
+    while (lo < hi) {
+      int mid = (lo + hi) >> 1;
+      if (gkeys[mid] < bk) lo = mid + 1; else hi = mid;
+    }
   cell_blk[c] = lo;
   cell_tile[c] = (int)tile;
   nsub[c] = (cnt[c] + SLOT_CAP - 1) / SLOT_CAP;
@@ -196,6 +198,98 @@ __global__ void k_pack_entries(long long n, const long long* __restrict__ ent64,
   tent[e] = ((unsigned)(i - base) << 16) | (unsigned)(j - base);
 }
 
+// fused kernel: key (tile, camera) of every observation; tile-local 16-bit index of the camera-grouped list
+__global__ void k_self_keys(int64_t N, long long C, const int* __restrict__ cam, const int* __restrict__ st_off, int n_st,
+                            long long* __restrict__ key) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  int lo = 0, hi = n_st;  // last tile with st_off[t] <= i
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (st_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  key[i] = (long long)lo * C + cam[i];
+}
+
+__global__ void k_pack_self(int64_t N, const int* __restrict__ val, const int* __restrict__ st_off, int n_st,
+                            unsigned short* __restrict__ dent) {
+  int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= N) return;
+  const int i = val[e];
+  int lo = 0, hi = n_st;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (st_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  dent[e] = (unsigned short)(i - st_off[lo]);
+}
+
+// ---- dataflow kernel metadata -------------------------------------------------------------------------------
+// per tile: counts, camera window, blob size (16-byte units)
+__global__ void k_tile_info(int n_st, long long C, const int* __restrict__ st_off, const int* __restrict__ st_wt_off,
+                            const int* __restrict__ tile_slot_off, const int* __restrict__ tile_dslot_off,
+                            const int* __restrict__ tile_ent_off, const int* __restrict__ pt, int n_cell,
+                            const long long* __restrict__ dcell, int4* __restrict__ info, int* __restrict__ units) {
+  int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= n_st) return;
+  const int nobs = st_off[t + 1] - st_off[t];
+  const int np = tile_slot_off[t + 1] - tile_slot_off[t], nd = tile_dslot_off[t + 1] - tile_dslot_off[t];
+  const int npent = tile_ent_off[t + 1] - tile_ent_off[t];
+  // first / last (tile, camera) cell of the tile in the sorted cell list
+  int lo = 0, hi = n_cell;
+  const long long k0 = (long long)t * C, k1 = (long long)(t + 1) * C;
+  while (lo < hi) { int mid = (lo + hi) >> 1; if (dcell[mid] < k0) lo = mid + 1; else hi = mid; }
+  const int first = lo;
+  hi = n_cell;
+  while (lo < hi) { int mid = (lo + hi) >> 1; if (dcell[mid] < k1) lo = mid + 1; else hi = mid; }
+  const int last = lo - 1;
+  int cmin = 0, cspan = 0;
+  if (last >= first) {
+    cmin = (int)(dcell[first] - k0) & ~1;
+    const int cmax = (int)(dcell[last] - k0);
+    cspan = (cmax - cmin + 2) & ~1;
+  }
+  const int bytes = 32 + 8 * (np + nd) + 4 * npent + 2 * nobs;
+  const int u = (bytes + 15) / 16;
+  int flags = 0;
+  if (u * 16 <= FLOW_META_CAP) flags |= 1;
+  if (cspan <= FLOW_CAM_SPAN) flags |= 2;
+  info[4 * t + 0] = make_int4(st_wt_off[t + 1] - st_wt_off[t], np, nd, flags);
+  info[4 * t + 1] = make_int4(0, u, cmin, cspan);
+  info[4 * t + 2] = make_int4(st_off[t], nobs, st_wt_off[t], npent);
+  const int p0 = nobs > 0 ? pt[st_off[t]] : 0, p1 = nobs > 0 ? pt[st_off[t + 1] - 1] : -1;
+  info[4 * t + 3] = make_int4(tile_slot_off[t], tile_dslot_off[t], p0, p1 - p0 + 1);
+  units[t] = u;
+}
+
+// one CTA per tile: pack the tile's slot descriptors and entries into its blob
+__global__ void k_blob_fill(int n_st, const int* __restrict__ blob_off, int4* __restrict__ info,
+                            const int* __restrict__ slot_a, const int* __restrict__ slot_n,
+                            const int* __restrict__ dslot_a, const int* __restrict__ dslot_n,
+                            const int* __restrict__ tile_ent_off, const unsigned* __restrict__ tent,
+                            const unsigned short* __restrict__ dent, uint4* __restrict__ blob) {
+  for (int t = blockIdx.x; t < n_st; t += gridDim.x) {
+    const int4 i0 = info[4 * t], i2 = info[4 * t + 2], i3 = info[4 * t + 3];
+    const int np = i0.y, nd = i0.z, obs0 = i2.x, nobs = i2.y, npent = i2.w, ps = i3.x, ds = i3.y;
+    const int off = blob_off[t];
+    if (threadIdx.x == 0) info[4 * t + 1].x = off;
+    int* w = reinterpret_cast<int*>(blob + off);
+    if (threadIdx.x < 8) {
+      const int hdr[8] = {np, nd, npent, nobs, 0, 0, 0, 0};
+      w[threadIdx.x] = hdr[threadIdx.x];
+    }
+    int* pd = w + 8;
+    const int e0 = tile_ent_off[t];
+    for (int q = threadIdx.x; q < np; q += blockDim.x) { pd[2 * q] = slot_a[ps + q] - e0; pd[2 * q + 1] = slot_n[ps + q]; }
+    int* dd = pd + 2 * np;
+    for (int q = threadIdx.x; q < nd; q += blockDim.x) { dd[2 * q] = dslot_a[ds + q] - obs0; dd[2 * q + 1] = dslot_n[ds + q]; }
+    unsigned* pe = reinterpret_cast<unsigned*>(dd + 2 * nd);
+    for (int q = threadIdx.x; q < npent; q += blockDim.x) pe[q] = tent[e0 + q];
+    unsigned short* de = reinterpret_cast<unsigned short*>(pe + npent);
+    for (int q = threadIdx.x; q < nobs; q += blockDim.x) de[q] = dent[obs0 + q];
+  }
+}
+
 inline unsigned nblk(int64_t n, int t) { return (unsigned)((n + t - 1) / t); }
 
 template <class T>
@@ -220,8 +314,6 @@ struct Tmp {  // scratch freed at the end of setup
   }
 };
 
-}  // namespace
-
 #define TMP_ALLOC(var, type, count)                                          \
   type* var = (type*)tmp.get((size_t)(count) * sizeof(type));                \
   if (!var) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)")
@@ -229,12 +321,95 @@ struct Tmp {  // scratch freed at the end of setup
   var = (type*)dalloc(h, (size_t)std::max<int64_t>((count), 1) * sizeof(type)); \
   if (!var) return B200BA_OOM
 
+
+// Slots of a tile-grouped entry list.  Input: the (tile, id) cells of the list in sorted order (cellkey = tile * M + id,
+// cnt = entries per cell; both with room for n_cell + 1 elements).  Every cell is cut into slots of <= SLOT_CAP entries;
+// the slots of a tile are ordered by decreasing entry count (lanes of a warp finish together); grp_* lists the slots
+// of every group (block of S / camera) in slot order for the fixed-order reduction.  gkeys maps id -> group (binary
+// search in the sorted global key list) or is null when the id is the group index.
+struct SlotList {
+  int n_slot = 0;
+  int* slot_a = nullptr;
+  int* slot_n = nullptr;
+  int* tile_off = nullptr;   // [n_st+1]
+  int* grp_off = nullptr;    // [n_grp+1]
+  int* grp_slots = nullptr;  // [n_slot]
+};
+
+int build_slots(Handle* h, Tmp& tmp, int n_cell, const long long* d_cellkey, int* d_cnt, long long M,
+                const long long* d_gkeys, int n_grp, int n_st, SlotList* out) {
+  cudaStream_t st = h->stream;
+  const int T = 256;
+  DEV_ALLOC(out->tile_off, int, n_st + 1);
+  DEV_ALLOC(out->grp_off, int, n_grp + 1);
+  BA_CUDA(h, cudaMemsetAsync(out->tile_off, 0, (n_st + 1) * sizeof(int), st));
+  BA_CUDA(h, cudaMemsetAsync(out->grp_off, 0, (n_grp + 1) * sizeof(int), st));
+  int n_slot = 0;
+  int *d_sub_off = nullptr, *d_cell_off = nullptr, *d_cell_blk = nullptr, *d_cell_tile = nullptr;
+  if (n_cell > 0) {
+    TMP_ALLOC(a_cell_off, int, n_cell + 1);
+    TMP_ALLOC(a_cell_blk, int, n_cell);
+    TMP_ALLOC(a_cell_tile, int, n_cell);
+    TMP_ALLOC(d_nsub, int, n_cell + 1);
+    TMP_ALLOC(a_sub_off, int, n_cell + 1);
+    d_sub_off = a_sub_off; d_cell_off = a_cell_off; d_cell_blk = a_cell_blk; d_cell_tile = a_cell_tile;
+    BA_CUDA(h, cudaMemsetAsync(d_cnt + n_cell, 0, sizeof(int), st));
+    BA_CUDA(h, cudaMemsetAsync(d_nsub + n_cell, 0, sizeof(int), st));
+    size_t bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, bytes, d_cnt, d_cell_off, n_cell + 1, st);
+    TMP_ALLOC(d_scan2, char, bytes);
+    BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan2, bytes, d_cnt, d_cell_off, n_cell + 1, st));
+    k_cell_meta<<<nblk(n_cell, T), T, 0, st>>>(n_cell, d_cellkey, d_cnt, M, d_gkeys, n_grp, d_cell_blk, d_cell_tile, d_nsub);
+    BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan2, bytes, d_nsub, d_sub_off, n_cell + 1, st));
+    BA_CUDA(h, cudaMemcpyAsync(&n_slot, d_sub_off + n_cell, sizeof(int), cudaMemcpyDeviceToHost, st));
+    BA_CUDA(h, cudaStreamSynchronize(st));
+  }
+  out->n_slot = n_slot;
+  DEV_ALLOC(out->slot_a, int, n_slot);
+  DEV_ALLOC(out->slot_n, int, n_slot);
+  DEV_ALLOC(out->grp_slots, int, n_slot);
+  if (n_slot > 0) {
+    TMP_ALLOC(d_sub_a, int, n_slot);
+    TMP_ALLOC(d_sub_n, int, n_slot);
+    TMP_ALLOC(d_sub_blk, int, n_slot);
+    TMP_ALLOC(d_key2, long long, n_slot);
+    TMP_ALLOC(d_key2s, long long, n_slot);
+    TMP_ALLOC(d_si, int, n_slot);
+    TMP_ALLOC(d_order, int, n_slot);
+    TMP_ALLOC(d_slot_blk, int, n_slot);
+    TMP_ALLOC(d_blk_sorted, int, n_slot);
+    k_sub_fill<<<nblk(n_cell, T), T, 0, st>>>(n_cell, d_sub_off, d_cell_off, d_cnt, d_cell_blk, d_cell_tile, d_sub_a, d_sub_n,
+                                              d_sub_blk, d_key2);
+    k_iota<<<nblk(n_slot, T), T, 0, st>>>(n_slot, d_si);
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_key2, d_key2s, d_si, d_order, n_slot, 0, 63, st);
+    TMP_ALLOC(d_sort3, char, bytes);
+    BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort3, bytes, d_key2, d_key2s, d_si, d_order, n_slot, 0, 63, st));
+    k_slot_fill<<<nblk(n_slot, T), T, 0, st>>>(n_slot, d_order, d_sub_a, d_sub_n, d_sub_blk, out->slot_a, out->slot_n,
+                                               d_slot_blk);
+    k_tile_slot_off<<<nblk(n_st + 1, T), T, 0, st>>>(n_st, n_slot, d_key2s, out->tile_off);
+    int eb = 1;
+    while (eb < 31 && (1 << eb) < n_grp) ++eb;
+    bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_slot_blk, d_blk_sorted, d_si, out->grp_slots, n_slot, 0, eb, st);
+    TMP_ALLOC(d_sort4, char, bytes);
+    BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort4, bytes, d_slot_blk, d_blk_sorted, d_si, out->grp_slots, n_slot, 0, eb,
+                                               st));
+    k_offsets<<<nblk(n_slot, T), T, 0, st>>>(n_slot, n_grp, d_blk_sorted, out->grp_off);
+  }
+  BA_CUDA(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+}  // namespace
+
 int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam_idx, const int64_t* pt_idx,
                   const double* uv, const double* K) {
   Problem& pb = h->pb;
   cudaStream_t st = h->stream;
   pb = Problem();
   pb.C = C; pb.P = P; pb.N = N;
+  pb.Cs = (C + 1) & ~(int64_t)1;
   for (int i = 0; i < 9; ++i) pb.K.k[i] = K[i];
   Tmp tmp;
   const int T = 256;
@@ -260,10 +435,10 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   if (flags & 1) return fail(h, B200BA_INDEX_RANGE, "camera or point index out of range");
 
   // ---- 2. point-major order (stable); identity when the input is already sorted (graph.py:186-191)
-  DEV_ALLOC(pb.u, double, N);
-  DEV_ALLOC(pb.v, double, N);
-  DEV_ALLOC(pb.cam, int, N);
-  DEV_ALLOC(pb.pt, int, N);
+  DEV_ALLOC(pb.u, double, N + 2);  // + slack for 16-byte aligned prefetch windows
+  DEV_ALLOC(pb.v, double, N + 2);
+  DEV_ALLOC(pb.cam, int, N + 16);  // + slack: the dataflow kernel bulk-copies 16-byte aligned windows
+  DEV_ALLOC(pb.pt, int, N + 16);
   DEV_ALLOC(pb.pt_off, int, P + 1);
   BA_CUDA(h, cudaMemsetAsync(pb.pt_off, 0, (P + 1) * sizeof(int), st));
   if (flags & 2) {
@@ -302,24 +477,35 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if ((int)N > start) wt.push_back((int)N);
     pb.n_wt = (int)wt.size() - 1;
     if (int rc = upload(h, &pb.wt_off, wt)) return rc;
-    // Schur tiles: runs of warp tiles (whole points) with at most tile_obs observations
+    // CTA tiles: runs of warp tiles (whole points) with at most tile_obs observations (records fit shared memory)
     int max_deg = 0;
     for (int64_t p = 0; p < P; ++p) max_deg = std::max(max_deg, h_pt_off[p + 1] - h_pt_off[p]);
-    int tile_obs = (int)std::min<int64_t>(SCHUR_TILE_MAX, std::max<int64_t>(256, (N / (4 * (int64_t)h->sm_count) + 31) / 32 * 32));
+    const char* e_fused = getenv("B200BA_FUSED");        // 0: unfused A/B path (k_lin_points + k_cam_side + k_schur_tiles)
+    const char* e_tile = getenv("B200BA_TILE_OBS");      // tuning sweeps
+    const bool want_fused = !(e_fused && atoi(e_fused) == 0);
+    const int cap = want_fused ? FUSED_TILE_1CTA : SCHUR_TILE_MAX;
+    const char* e_flow0 = getenv("B200BA_FLOW");
+    const bool want_flow = want_fused && !(e_flow0 && atoi(e_flow0) == 0);
+    const int tile_max = want_flow ? FLOW_TILE : want_fused ? FUSED_TILE_2CTA : SCHUR_TILE_MAX;
+    int tile_obs = (int)std::min<int64_t>(tile_max, std::max<int64_t>(256, (N / (4 * (int64_t)h->sm_count) + 31) / 32 * 32));
+    if (e_tile && atoi(e_tile) >= 32) tile_obs = std::min(cap, atoi(e_tile) / 32 * 32);  // exact override (tests, sweeps)
+    if (max_deg > tile_obs) tile_obs = std::min(cap, (max_deg + 31) / 32 * 32);  // one big point must fit a tile
     const char* force_stream = getenv("B200BA_SCHUR_STREAM");
     pb.schur_tiles = max_deg <= tile_obs && !(force_stream && atoi(force_stream));
     if (pb.schur_tiles) {
-      std::vector<int> stv;
-      stv.push_back(0);
+      std::vector<int> stv, stw;
+      stv.push_back(0); stw.push_back(0);
       int ts = 0;
       for (size_t k = 1; k < wt.size(); ++k)
-        if (wt[k] - ts > tile_obs) { stv.push_back(wt[k - 1]); ts = wt[k - 1]; }
-      if ((int)N > ts) stv.push_back((int)N);
+        if (wt[k] - ts > tile_obs) { stv.push_back(wt[k - 1]); stw.push_back((int)k - 1); ts = wt[k - 1]; }
+      if ((int)N > ts) { stv.push_back((int)N); stw.push_back((int)wt.size() - 1); }
       pb.n_st = (int)stv.size() - 1;
       pb.tile_obs = tile_obs;
       if ((double)(pb.n_st + 1) * (double)C * (double)C >= 4.0e18) pb.schur_tiles = false;  // key would overflow
       else {
+        pb.fused = want_fused;
         if (int rc = upload(h, &pb.st_off, stv)) return rc;
+        if (int rc = upload(h, &pb.st_wt_off, stw)) return rc;
         h_pt_tile.assign(P, 0);
         int t = 0;
         for (int64_t p = 0; p < P; ++p) {
@@ -376,7 +562,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   TMP_ALLOC(d_cnt, long long, P + 1);
   TMP_ALLOC(d_ent_off, long long, P + 1);
   BA_CUDA(h, cudaMemsetAsync(d_cnt, 0, (P + 1) * sizeof(long long), st));
-  if (P > 0) k_pair_count<<<nblk(P, T), T, 0, st>>>((int)P, pb.pt_off, pb.cam, d_cnt);
+  if (P > 0) k_pair_count<<<nblk(P, T), T, 0, st>>>((int)P, pb.pt_off, pb.cam, pb.fused, d_cnt);
   {
     size_t bytes = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, bytes, d_cnt, d_ent_off, (int)(P + 1), st);
@@ -405,7 +591,8 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     TMP_ALLOC(d_keys, long long, n_ent);
     TMP_ALLOC(d_vals, long long, n_ent);
     if (P > 0)
-      k_pair_fill<<<nblk(P, T), T, 0, st>>>((int)P, (long long)C, pb.pt_off, pb.cam, d_ent_off, d_pt_tile, d_keys, d_vals);
+      k_pair_fill<<<nblk(P, T), T, 0, st>>>((int)P, (long long)C, pb.pt_off, pb.cam, pb.fused, d_ent_off, d_pt_tile, d_keys,
+                                            d_vals);
     if (n_ent > 0) {
       const double kmax = (double)CC * (double)(pb.schur_tiles ? pb.n_st : 1);
       int end_bit = 1;
@@ -531,79 +718,81 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.bsr_col, col)) return rc;
     if (int rc = upload(h, &pb.bsr_src, src)) return rc;
   }
-  // ---- 8. tile mode: slots = (tile, block) cells ordered inside each tile by decreasing entry count,
+  // ---- 8. tile mode: pair slots = (tile, block) cells ordered inside each tile by decreasing entry count,
   //         per-block reduce lists, entries packed to tile-local 16-bit indices
   if (pb.schur_tiles) {
-    const int n_cell = nruns;
     DEV_ALLOC(pb.tent, unsigned, n_ent);
-    DEV_ALLOC(pb.tile_slot_off, int, pb.n_st + 1);
     DEV_ALLOC(pb.tile_ent_off, int, pb.n_st + 1);
-    DEV_ALLOC(pb.blk_slot_off, int, n_blk + 1);
-    BA_CUDA(h, cudaMemsetAsync(pb.tile_slot_off, 0, (pb.n_st + 1) * sizeof(int), st));
     BA_CUDA(h, cudaMemsetAsync(pb.tile_ent_off, 0, (pb.n_st + 1) * sizeof(int), st));
-    BA_CUDA(h, cudaMemsetAsync(pb.blk_slot_off, 0, (n_blk + 1) * sizeof(int), st));
-    int n_slot = 0;
-    struct { int *sub_off = nullptr, *cell_off = nullptr, *cell_blk = nullptr, *cell_tile = nullptr; } tile_scratch;
-    if (n_cell > 0) {
-      TMP_ALLOC(d_cell_off, int, n_cell + 1);
-      TMP_ALLOC(d_cell_blk, int, n_cell);
-      TMP_ALLOC(d_cell_tile, int, n_cell);
-      TMP_ALLOC(d_nsub, int, n_cell + 1);
-      TMP_ALLOC(d_sub_off, int, n_cell + 1);
-      tile_scratch.sub_off = d_sub_off; tile_scratch.cell_off = d_cell_off;
-      tile_scratch.cell_blk = d_cell_blk; tile_scratch.cell_tile = d_cell_tile;
-      BA_CUDA(h, cudaMemsetAsync(d_runs + n_cell, 0, sizeof(int), st));
-      BA_CUDA(h, cudaMemsetAsync(d_nsub + n_cell, 0, sizeof(int), st));
-      size_t bytes = 0;
-      cub::DeviceScan::ExclusiveSum(nullptr, bytes, d_runs, d_cell_off, n_cell + 1, st);
-      TMP_ALLOC(d_scan2, char, bytes);
-      BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan2, bytes, d_runs, d_cell_off, n_cell + 1, st));
-      k_cell_meta<<<nblk(n_cell, T), T, 0, st>>>(n_cell, d_uniq, d_runs, CC, d_gkeys, n_blk, d_cell_blk, d_cell_tile, d_nsub);
-      BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan2, bytes, d_nsub, d_sub_off, n_cell + 1, st));
-      BA_CUDA(h, cudaMemcpyAsync(&n_slot, d_sub_off + n_cell, sizeof(int), cudaMemcpyDeviceToHost, st));
-      BA_CUDA(h, cudaStreamSynchronize(st));
-    }
-    pb.n_slot = n_slot;
-    DEV_ALLOC(pb.slot_a, int, n_slot);
-    DEV_ALLOC(pb.slot_n, int, n_slot);
-    DEV_ALLOC(pb.blk_slots, int, n_slot);
-    if (n_slot > 0) {
-      // (re-use of the scratch names above is scoped to the previous block; fetch them again)
-      TMP_ALLOC(d_sub_a, int, n_slot);
-      TMP_ALLOC(d_sub_n, int, n_slot);
-      TMP_ALLOC(d_sub_blk, int, n_slot);
-      TMP_ALLOC(d_key2, long long, n_slot);
-      TMP_ALLOC(d_key2s, long long, n_slot);
-      TMP_ALLOC(d_si, int, n_slot);
-      TMP_ALLOC(d_order, int, n_slot);
-      TMP_ALLOC(d_slot_blk, int, n_slot);
-      TMP_ALLOC(d_blk_sorted, int, n_slot);
-      k_sub_fill<<<nblk(n_cell, T), T, 0, st>>>(n_cell, tile_scratch.sub_off, tile_scratch.cell_off, d_runs,
-                                                tile_scratch.cell_blk, tile_scratch.cell_tile, d_sub_a, d_sub_n, d_sub_blk,
-                                                d_key2);
-      k_iota<<<nblk(n_slot, T), T, 0, st>>>(n_slot, d_si);
-      size_t bytes = 0;
-      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_key2, d_key2s, d_si, d_order, n_slot, 0, 63, st);
-      TMP_ALLOC(d_sort3, char, bytes);
-      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort3, bytes, d_key2, d_key2s, d_si, d_order, n_slot, 0, 63, st));
-      k_slot_fill<<<nblk(n_slot, T), T, 0, st>>>(n_slot, d_order, d_sub_a, d_sub_n, d_sub_blk, pb.slot_a, pb.slot_n,
-                                                 d_slot_blk);
-      k_tile_slot_off<<<nblk(pb.n_st + 1, T), T, 0, st>>>(pb.n_st, n_slot, d_key2s, pb.tile_slot_off);
-      int eb = 1;
-      while (eb < 31 && (1 << eb) < n_blk) ++eb;
-      bytes = 0;
-      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_slot_blk, d_blk_sorted, d_si, pb.blk_slots, n_slot, 0, eb, st);
-      TMP_ALLOC(d_sort4, char, bytes);
-      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort4, bytes, d_slot_blk, d_blk_sorted, d_si, pb.blk_slots, n_slot, 0,
-                                                 eb, st));
-      k_offsets<<<nblk(n_slot, T), T, 0, st>>>(n_slot, n_blk, d_blk_sorted, pb.blk_slot_off);
+    SlotList sl;
+    if (int rc = build_slots(h, tmp, nruns, d_uniq, d_runs, CC, d_gkeys, n_blk, pb.n_st, &sl)) return rc;
+    pb.n_slot = sl.n_slot; pb.slot_a = sl.slot_a; pb.slot_n = sl.slot_n;
+    pb.tile_slot_off = sl.tile_off; pb.blk_slot_off = sl.grp_off; pb.blk_slots = sl.grp_slots;
+    if (n_ent > 0) {
       k_pack_entries<<<nblk(n_ent, T), T, 0, st>>>(n_ent, d_ent64, pb.st_off, pb.n_st, pb.tent);
       k_tile_ent_off<<<nblk(pb.n_st + 1, T), T, 0, st>>>(pb.n_st, (int)n_ent, d_keys_sorted, CC, pb.tile_ent_off);
+    }
+  }
+  // ---- 9. fused kernel: self slots = the observations of one camera inside one tile
+  if (pb.fused) {
+    DEV_ALLOC(pb.dent, unsigned short, N);
+    int n_cell = 0;
+    TMP_ALLOC(d_dkey, long long, N);
+    TMP_ALLOC(d_dkey_sorted, long long, N);
+    TMP_ALLOC(d_dval, int, N);
+    TMP_ALLOC(d_dcell, long long, N + 1);
+    TMP_ALLOC(d_dcnt, int, N + 1);
+    if (N > 0) {
+      k_self_keys<<<nblk(N, T), T, 0, st>>>(N, (long long)C, pb.cam, pb.st_off, pb.n_st, d_dkey);
+      k_iota<<<nblk(N, T), T, 0, st>>>(N, d_iota);
+      const double kmax = (double)C * (double)pb.n_st;
+      int end_bit = 1;
+      while (end_bit < 63 && (double)((long long)1 << end_bit) < kmax) ++end_bit;
+      size_t bytes = 0;
+      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_dkey, d_dkey_sorted, d_iota, d_dval, (int)N, 0, end_bit, st);
+      TMP_ALLOC(d_sort5, char, bytes);
+      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort5, bytes, d_dkey, d_dkey_sorted, d_iota, d_dval, (int)N, 0, end_bit, st));
+      TMP_ALLOC(d_nruns2, int, 1);
+      bytes = 0;
+      cub::DeviceRunLengthEncode::Encode(nullptr, bytes, d_dkey_sorted, d_dcell, d_dcnt, d_nruns2, (int)N, st);
+      TMP_ALLOC(d_rle3, char, bytes);
+      BA_CUDA(h, cub::DeviceRunLengthEncode::Encode(d_rle3, bytes, d_dkey_sorted, d_dcell, d_dcnt, d_nruns2, (int)N, st));
+      BA_CUDA(h, cudaMemcpyAsync(&n_cell, d_nruns2, sizeof(int), cudaMemcpyDeviceToHost, st));
+      BA_CUDA(h, cudaStreamSynchronize(st));
+      k_pack_self<<<nblk(N, T), T, 0, st>>>(N, d_dval, pb.st_off, pb.n_st, pb.dent);
+    }
+    SlotList sl;
+    if (int rc = build_slots(h, tmp, n_cell, d_dcell, d_dcnt, (long long)C, nullptr, (int)C, pb.n_st, &sl)) return rc;
+    pb.n_dslot = sl.n_slot; pb.dslot_a = sl.slot_a; pb.dslot_n = sl.slot_n;
+    pb.tile_dslot_off = sl.tile_off; pb.cam_dslot_off = sl.grp_off; pb.cam_dslots = sl.grp_slots;
+    // ---- 10. dataflow kernel: per-tile info + contiguous metadata blobs (bulk-copied to shared memory per tile)
+    const char* e_flow = getenv("B200BA_FLOW");
+    if (pb.tile_obs <= FLOW_TILE && !(e_flow && atoi(e_flow) == 0) && pb.n_st > 0) {
+      DEV_ALLOC(pb.tile_info, int4, 4 * (int64_t)pb.n_st);
+      TMP_ALLOC(d_units, int, pb.n_st + 1);
+      TMP_ALLOC(d_boff, int, pb.n_st + 1);
+      BA_CUDA(h, cudaMemsetAsync(d_units, 0, (pb.n_st + 1) * sizeof(int), st));
+      k_tile_info<<<nblk(pb.n_st, T), T, 0, st>>>(pb.n_st, (long long)C, pb.st_off, pb.st_wt_off, pb.tile_slot_off,
+                                                  pb.tile_dslot_off, pb.tile_ent_off, pb.pt, n_cell, d_dcell, pb.tile_info, d_units);
+      size_t bytes = 0;
+      cub::DeviceScan::ExclusiveSum(nullptr, bytes, d_units, d_boff, pb.n_st + 1, st);
+      TMP_ALLOC(d_scan6, char, bytes);
+      BA_CUDA(h, cub::DeviceScan::ExclusiveSum(d_scan6, bytes, d_units, d_boff, pb.n_st + 1, st));
+      int total_units = 0;
+      BA_CUDA(h, cudaMemcpyAsync(&total_units, d_boff + pb.n_st, sizeof(int), cudaMemcpyDeviceToHost, st));
+      BA_CUDA(h, cudaStreamSynchronize(st));
+      DEV_ALLOC(pb.blob, uint4, (int64_t)total_units + 1);
+      k_blob_fill<<<std::min(pb.n_st, 4096), 128, 0, st>>>(pb.n_st, d_boff, pb.tile_info, pb.slot_a, pb.slot_n, pb.dslot_a,
+                                                         pb.dslot_n, pb.tile_ent_off, pb.tent, pb.dent, pb.blob);
+      pb.flow = true;
     }
   }
   BA_CUDA(h, cudaStreamSynchronize(st));
   BA_CUDA(h, cudaGetLastError());
   h->st.schur_entries = pb.n_ent;
+  h->st.n_tiles = pb.n_st;
+  h->st.n_pair_slots = pb.n_slot;
+  h->st.n_self_slots = pb.n_dslot;
   h->st.schur_blocks = pb.n_blk;
   return 0;
 }

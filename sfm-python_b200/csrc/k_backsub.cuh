@@ -47,7 +47,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       const double X0 = xp[3 * p], X1 = xp[3 * p + 1], X2 = xp[3 * p + 2];
       const double uo = pb.u[i], vo = pb.v[i];
       double r0, r1, Jc[12], Jp[6], s3[3], cp[CAMPREP_FIELDS];
-      load_cam(camprep, pb.C, c, cp);
+      load_cam(camprep, pb.Cs, c, cp);
       project_jac(cp, pb.K, X0, X1, X2, uo, vo, r0, r1, Jc, Jp);
       jc_dc_jp(Jc, Jp, dc + 6 * c, s3);
       if (!valid) s3[0] = s3[1] = s3[2] = 0.0;
@@ -56,7 +56,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       double dp[3], sums[3];
       point_step(pp + 12 * (int64_t)p, s3, dp, sums);
       const double N0 = X0 + dp[0], N1 = X1 + dp[1], N2 = X2 + dp[2];
-      load_cam(camprep_n, pb.C, c, cp);
+      load_cam(camprep_n, pb.Cs, c, cp);
       project_residual(cp, pb.K, N0, N1, N2, uo, vo, r0, r1);
       if (valid) {
         acc[0] += r0 * r0 + r1 * r1;
@@ -73,7 +73,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       for (int i = a + lane; i < b; i += 32) {
         const int c = pb.cam[i];
         double r0, r1, Jc[12], Jp[6], t3[3], cp[CAMPREP_FIELDS];
-        load_cam(camprep, pb.C, c, cp);
+        load_cam(camprep, pb.Cs, c, cp);
         project_jac(cp, pb.K, X0, X1, X2, 0.0, 0.0, r0, r1, Jc, Jp);
         jc_dc_jp(Jc, Jp, dc + 6 * c, t3);
         s3[0] += t3[0]; s3[1] += t3[1]; s3[2] += t3[2];
@@ -84,7 +84,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       const double N0 = X0 + dp[0], N1 = X1 + dp[1], N2 = X2 + dp[2];
       for (int i = a + lane; i < b; i += 32) {
         double r0, r1, cp[CAMPREP_FIELDS];
-        load_cam(camprep_n, pb.C, pb.cam[i], cp);
+        load_cam(camprep_n, pb.Cs, pb.cam[i], cp);
         project_residual(cp, pb.K, N0, N1, N2, pb.u[i], pb.v[i], r0, r1);
         acc[0] += r0 * r0 + r1 * r1;
       }

@@ -17,7 +17,7 @@ k_cam_side(Problem pb, const double* __restrict__ x, const double* __restrict__ 
   for (int ch = warp; ch < pb.n_cch; ch += nwarp) {
     const int c = pb.cch_cam[ch], a = pb.cch_a[ch], b = pb.cch_b[ch];
     double cp[CAMPREP_FIELDS];
-    load_cam(camprep, pb.C, c, cp);
+    load_cam(camprep, pb.Cs, c, cp);
     double acc[33];
 #pragma unroll
     for (int k = 0; k < 33; ++k) acc[k] = 0.0;

@@ -1,0 +1,302 @@
+// Fused linearisation + point-block Schur elimination (included inside ba_kernels.cu's anonymous namespace).
+//
+// One CTA owns a tile = a run of whole points whose per-observation records fit shared memory.  The records
+//     rec_i = [ Jc_i (2x6) | A_i = Jp_i L^-T (2x3) | r_i (2) | rt_i = r_i - A_i z_p (2) ]        22 doubles
+// are produced in phase 1 and consumed in phases 2 and 3 without ever touching HBM:
+//   phase 1  one lane per observation (warp tiles of whole points, as k_lin_points): residual, analytic blocks,
+//            V_p / g_p by a segmented shuffle scan, damped 3x3 Cholesky; pp / gp go to HBM for the back-substitution.
+//   phase 2  "self" slots = the tile's observations of one camera: 4 lanes per slot accumulate in registers
+//                N_c  += Jc^T (A A^T - I) Jc   (21 unique)      => S_cc = -N_c - pairs + lambda diag U
+//                dU_c += diag(Jc^T Jc),  g_c += Jc^T r,  b_c -= Jc^T rt
+//   phase 3  "pair" slots = the ordered pairs (i, j), i != j, cam_i <= cam_j of one point that fall into one block of
+//            S: 4 lanes per slot accumulate  Jc_i^T (A_i A_j^T) Jc_j  in registers.
+// Every slot partial is written exactly once; k_slot_reduce_* sum them in list order: no atomics, bit-reproducible.
+// Replaces the J^T J / J^T r products and the LSMR operator inside scipy's TRF (sfm_lite/sfm.py:266-268).
+
+constexpr int FREC = 22;    // doubles per observation record
+constexpr int FG = 4;       // lanes cooperating on one slot
+constexpr int DPART = 40;   // doubles per self-slot partial: N (21) | diag U (6) | g_c (6) | b_c (6) | pad
+
+__device__ __forceinline__ void store_record(double* __restrict__ rec, const double* Jc, const double* Jp,
+                                             const double* Li, const double* z, double r0, double r1) {
+  double A[6];
+#pragma unroll
+  for (int r = 0; r < 2; ++r) {
+    A[3 * r + 0] = Jp[3 * r] * Li[0];
+    A[3 * r + 1] = Jp[3 * r] * Li[1] + Jp[3 * r + 1] * Li[2];
+    A[3 * r + 2] = Jp[3 * r] * Li[3] + Jp[3 * r + 1] * Li[4] + Jp[3 * r + 2] * Li[5];
+  }
+  const double rt0 = r0 - (A[0] * z[0] + A[1] * z[1] + A[2] * z[2]);
+  const double rt1 = r1 - (A[3] * z[0] + A[4] * z[1] + A[5] * z[2]);
+  double2* o = reinterpret_cast<double2*>(rec);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) o[k] = make_double2(Jc[2 * k], Jc[2 * k + 1]);
+  o[6] = make_double2(A[0], A[1]);
+  o[7] = make_double2(A[2], A[3]);
+  o[8] = make_double2(A[4], A[5]);
+  o[9] = make_double2(r0, r1);
+  o[10] = make_double2(rt0, rt1);
+}
+
+// Sum `acc[2*H]` over the 4 lanes of a slot group so that every lane ends with H/2 of the sums (two exchange steps,
+// 3H/2 additions instead of the 4H of an all-reduce butterfly).  Lane g receives entries [(H/2) * g', (H/2) * (g' + 1))
+// with g' = 2 * (g & 1) + (g >> 1).
+template <int H>
+__device__ __forceinline__ void group_reduce_scatter(const double* acc, double* out, int g) {
+  const bool odd = g & 1, hi = g & 2;
+  double h[H];
+#pragma unroll
+  for (int k = 0; k < H; ++k) {
+    const double mine = odd ? acc[H + k] : acc[k];
+    const double give = odd ? acc[k] : acc[H + k];
+    h[k] = mine + __shfl_xor_sync(FULL, give, 1);
+  }
+#pragma unroll
+  for (int k = 0; k < H / 2; ++k) {
+    const double mine = hi ? h[H / 2 + k] : h[k];
+    const double give = hi ? h[k] : h[H / 2 + k];
+    out[k] = mine + __shfl_xor_sync(FULL, give, 2);
+  }
+}
+
+// ---- slot bodies shared by k_lin_fused and k_lin_flow (pure FMA chains: 2 DFMA per accumulator and entry) ----------
+// pair slot: acc(6x6) += Jc_i^T (A_i A_j^T) Jc_j over the entries e = g, g + FG, ... of the slot
+__device__ __forceinline__ void pair_slot_body(const double* __restrict__ rec, const unsigned* __restrict__ ent, int en,
+                                               int g, double* __restrict__ acc /*[36]*/) {
+  for (int e = g; e < en; e += FG) {
+    const unsigned cur = ent[e];
+    const double2* ri = reinterpret_cast<const double2*>(rec + FREC * (cur >> 16));
+    const double2* rj = reinterpret_cast<const double2*>(rec + FREC * (cur & 0xffffu));
+    const double2 a01 = ri[6], a23 = ri[7], a45 = ri[8];
+    const double2 b01 = rj[6], b23 = rj[7], b45 = rj[8];
+    // M = A_i A_j^T (2x2)
+    const double m00 = fma(a23.x, b23.x, fma(a01.y, b01.y, a01.x * b01.x));
+    const double m01 = fma(a23.x, b45.y, fma(a01.y, b45.x, a01.x * b23.y));
+    const double m10 = fma(a45.y, b23.x, fma(a45.x, b01.y, a23.y * b01.x));
+    const double m11 = fma(a45.y, b45.y, fma(a45.x, b45.x, a23.y * b23.y));
+    double G0[6], G1[6];  // G = M Jc_j (2x6)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double2 j0 = rj[k], j1 = rj[3 + k];
+      G0[2 * k] = fma(m01, j1.x, m00 * j0.x);     G0[2 * k + 1] = fma(m01, j1.y, m00 * j0.y);
+      G1[2 * k] = fma(m11, j1.x, m10 * j0.x);     G1[2 * k + 1] = fma(m11, j1.y, m10 * j0.y);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const double2 i0 = ri[k], i1 = ri[3 + k];
+#pragma unroll
+      for (int n = 0; n < 6; ++n) {
+        acc[6 * (2 * k) + n] = fma(i1.x, G1[n], fma(i0.x, G0[n], acc[6 * (2 * k) + n]));
+        acc[6 * (2 * k + 1) + n] = fma(i1.y, G1[n], fma(i0.y, G0[n], acc[6 * (2 * k + 1) + n]));
+      }
+    }
+  }
+}
+
+// self slot: acc[0..20] += Jc^T (A A^T - I) Jc (upper triangle), acc[21..26] += diag(Jc^T Jc), acc[27..32] += Jc^T r,
+// acc[33..38] += Jc^T rt over the entries of the slot
+__device__ __forceinline__ void self_slot_body(const double* __restrict__ rec, const unsigned short* __restrict__ ent,
+                                               int en, int g, double* __restrict__ acc /*[40]*/) {
+  for (int e = g; e < en; e += FG) {
+    const double2* rc = reinterpret_cast<const double2*>(rec + FREC * (int)ent[e]);
+    double J[12];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) { const double2 v = rc[k]; J[2 * k] = v.x; J[2 * k + 1] = v.y; }
+    const double2 A01 = rc[6], A23 = rc[7], A45 = rc[8], rv = rc[9], rtv = rc[10];
+    const double m00 = fma(A23.x, A23.x, fma(A01.y, A01.y, fma(A01.x, A01.x, -1.0)));
+    const double m01 = fma(A23.x, A45.y, fma(A01.y, A45.x, A01.x * A23.y));
+    const double m11 = fma(A45.y, A45.y, fma(A45.x, A45.x, fma(A23.y, A23.y, -1.0)));
+    int k = 0;
+#pragma unroll
+    for (int m = 0; m < 6; ++m) {
+      const double h0 = fma(J[6 + m], m01, J[m] * m00);  // row m of Jc^T M
+      const double h1 = fma(J[6 + m], m11, J[m] * m01);
+#pragma unroll
+      for (int n = m; n < 6; ++n, ++k) acc[k] = fma(h1, J[6 + n], fma(h0, J[n], acc[k]));
+    }
+#pragma unroll
+    for (int m = 0; m < 6; ++m) {
+      acc[21 + m] = fma(J[6 + m], J[6 + m], fma(J[m], J[m], acc[21 + m]));
+      acc[27 + m] = fma(J[6 + m], rv.y, fma(J[m], rv.x, acc[27 + m]));
+      acc[33 + m] = fma(J[6 + m], rtv.y, fma(J[m], rtv.x, acc[33 + m]));
+    }
+  }
+}
+
+template <int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__ camprep, double lambda,
+            double* __restrict__ pp, double* __restrict__ gp, double* __restrict__ spart, double* __restrict__ dpart,
+            double* __restrict__ part) {
+  extern __shared__ __align__(16) double srec[];
+  constexpr int NW = THREADS / 32;
+  __shared__ double sred[2 * NW];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int g = threadIdx.x % FG, sub = threadIdx.x / FG;
+  const double* xp = x + 6 * pb.C;
+  double cost2 = 0.0, gmax = 0.0;
+
+  for (int t = blockIdx.x; t < pb.n_st; t += gridDim.x) {
+    const int a0 = pb.st_off[t];
+    // ------------------------------------------------ phase 1: records
+    for (int wt = pb.st_wt_off[t] + wid; wt < pb.st_wt_off[t + 1]; wt += NW) {
+      const int a = pb.wt_off[wt], b = pb.wt_off[wt + 1], n = b - a;
+      if (n <= 32) {
+        const bool valid = lane < n;
+        const int i = a + (valid ? lane : 0);
+        const int c = pb.cam[i], p = pb.pt[i];
+        double r0, r1, Jc[12], Jp[6], vals[9], cp[CAMPREP_FIELDS];
+        load_cam(camprep, pb.Cs, c, cp);
+        project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+        point_products(Jp, r0, r1, vals);
+        if (!valid) {
+#pragma unroll
+          for (int k = 0; k < 9; ++k) vals[k] = 0.0;
+        }
+        const SegInfo s = seg_info(p, valid, lane);
+        seg_allsum<9>(vals, s, lane);
+        double Li[6], z[3];
+        point_factor(vals, lambda, Li);
+        z[0] = Li[0] * vals[6];
+        z[1] = Li[1] * vals[6] + Li[2] * vals[7];
+        z[2] = Li[3] * vals[6] + Li[4] * vals[7] + Li[5] * vals[8];
+        if (valid) {
+          cost2 += r0 * r0 + r1 * r1;
+          store_record(srec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
+          if (lane == s.first) {
+            store_point(pp, gp, p, Li, z, vals);
+            gmax = fmax(gmax, fmax(fabs(vals[6]), fmax(fabs(vals[7]), fabs(vals[8]))));
+          }
+        }
+      } else {
+        // one point with more than 32 observations: two passes over its run
+        const int p = pb.pt[a];
+        const double X0 = xp[3 * p], X1 = xp[3 * p + 1], X2 = xp[3 * p + 2];
+        double vals[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) vals[k] = 0.0;
+        for (int i = a + lane; i < b; i += 32) {
+          double r0, r1, Jc[12], Jp[6], v9[9], cp[CAMPREP_FIELDS];
+          load_cam(camprep, pb.Cs, pb.cam[i], cp);
+          project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+          point_products(Jp, r0, r1, v9);
+#pragma unroll
+          for (int k = 0; k < 9; ++k) vals[k] += v9[k];
+          cost2 += r0 * r0 + r1 * r1;
+        }
+#pragma unroll
+        for (int k = 0; k < 9; ++k) vals[k] = warp_sum(vals[k]);
+        double Li[6], z[3];
+        point_factor(vals, lambda, Li);
+        z[0] = Li[0] * vals[6];
+        z[1] = Li[1] * vals[6] + Li[2] * vals[7];
+        z[2] = Li[3] * vals[6] + Li[4] * vals[7] + Li[5] * vals[8];
+        if (lane == 0) {
+          store_point(pp, gp, p, Li, z, vals);
+          gmax = fmax(gmax, fmax(fabs(vals[6]), fmax(fabs(vals[7]), fabs(vals[8]))));
+        }
+        for (int i = a + lane; i < b; i += 32) {
+          double r0, r1, Jc[12], Jp[6], cp[CAMPREP_FIELDS];
+          load_cam(camprep, pb.Cs, pb.cam[i], cp);
+          project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+          store_record(srec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
+        }
+      }
+    }
+    __syncthreads();
+
+    // ------------------------------------------------ phase 2: self slots (one camera of the tile each)
+    {
+      const int s_lo = pb.tile_dslot_off[t], s_hi = pb.tile_dslot_off[t + 1];
+      for (int s0 = s_lo; s0 < s_hi; s0 += THREADS / FG) {
+        const int s = s0 + sub;
+        const bool active = s < s_hi;
+        const int ea = active ? pb.dslot_a[s] : 0, en = active ? pb.dslot_n[s] : 0;
+        double acc[40];
+#pragma unroll
+        for (int k = 0; k < 40; ++k) acc[k] = 0.0;
+        self_slot_body(srec, pb.dent + ea, en, g, acc);
+        // reduce-scatter over the 4 lanes of the group: lane g ends with entries [10 g', 10 g' + 10) of the partial
+        double q10[10];
+        group_reduce_scatter<20>(acc, q10, g);
+        if (active) {
+          double* o = dpart + DPART * (int64_t)s + 10 * (((g & 1) << 1) | (g >> 1));
+#pragma unroll
+          for (int k = 0; k < 10; ++k) o[k] = q10[k];
+        }
+      }
+    }
+
+    // ------------------------------------------------ phase 3: pair slots (one block of S each)
+    {
+      const int s_lo = pb.tile_slot_off[t], s_hi = pb.tile_slot_off[t + 1];
+      for (int s0 = s_lo; s0 < s_hi; s0 += THREADS / FG) {
+        const int s = s0 + sub;
+        const bool active = s < s_hi;
+        const int ea = active ? pb.slot_a[s] : 0, en = active ? pb.slot_n[s] : 0;
+        double acc[36];
+#pragma unroll
+        for (int k = 0; k < 36; ++k) acc[k] = 0.0;
+        pair_slot_body(srec, pb.tent + ea, en, g, acc);
+        double q9[9];
+        group_reduce_scatter<18>(acc, q9, g);
+        if (active) {
+          double* o = spart + 36 * (int64_t)s + 9 * (((g & 1) << 1) | (g >> 1));
+#pragma unroll
+          for (int k = 0; k < 9; ++k) o[k] = q9[k];
+        }
+      }
+    }
+    __syncthreads();  // the next tile overwrites the records
+  }
+
+  cost2 = warp_sum(cost2);
+  gmax = warp_max(gmax);
+  if (lane == 0) { sred[wid] = cost2; sred[NW + wid] = gmax; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double s = 0.0, m = 0.0;
+    for (int w = 0; w < NW; ++w) { s += sred[w]; m = fmax(m, sred[NW + w]); }
+    part[blockIdx.x * 8 + 0] = s;
+    part[blockIdx.x * 8 + 1] = m;
+  }
+}
+
+// Sup[g] = -(sum of the pair-slot partials of block g) [- N_c + lambda diag U_c on diagonal blocks]
+__global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
+                                const int* __restrict__ blk_slot_off, const int* __restrict__ blk_slots,
+                                const double* __restrict__ spart, const int* __restrict__ cam_dslot_off,
+                                const int* __restrict__ cam_dslots, const double* __restrict__ dpart, double lambda,
+                                double* __restrict__ Sup) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t >= (int64_t)n_blk * 36) return;
+  const int g = (int)(t / 36), e = (int)(t % 36);
+  double s = 0.0;
+  for (int q = blk_slot_off[g]; q < blk_slot_off[g + 1]; ++q) s += spart[(int64_t)blk_slots[q] * 36 + e];
+  if (blk_r[g] == blk_c[g]) {
+    const int c = blk_r[g], r = e / 6, cc = e % 6;
+    const int k = tri6(min(r, cc), max(r, cc));
+    double nn = 0.0, ud = 0.0;
+    for (int q = cam_dslot_off[c]; q < cam_dslot_off[c + 1]; ++q) {
+      const double* d = dpart + DPART * (int64_t)cam_dslots[q];
+      nn += d[k];
+      if (r == cc) ud += d[21 + r];
+    }
+    s += nn - lambda * ud;
+  }
+  Sup[t] = -s;
+}
+
+// diag U, g_c = J_c^T r, b_c = -J_c^T rt per camera from the self-slot partials
+__global__ void k_slot_reduce_cam(int C, const int* __restrict__ cam_dslot_off, const int* __restrict__ cam_dslots,
+                                  const double* __restrict__ dpart, double* __restrict__ udiag, double* __restrict__ gc,
+                                  double* __restrict__ b) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= C * 18) return;
+  const int c = t / 18, k = t % 18;
+  double s = 0.0;
+  for (int q = cam_dslot_off[c]; q < cam_dslot_off[c + 1]; ++q) s += dpart[DPART * (int64_t)cam_dslots[q] + 21 + k];
+  if (k < 6) udiag[6 * c + k] = s;
+  else if (k < 12) gc[6 * c + (k - 6)] = s;
+  else b[6 * c + (k - 12)] = -s;
+}

@@ -35,6 +35,25 @@ __global__ void k_reduce_partials2(int n, int nsum, int nval, const double* __re
 
 inline unsigned cdiv(int64_t n, int t) { return (unsigned)std::max<int64_t>((n + t - 1) / t, 1); }
 
+// FP64 FMA peak probe: 8 independent DFMA chains per thread (MEASURED_PEAKS.json holds no FP64 figure; bench.py
+// divides the fused kernel's algorithmic flops by this number measured in the same run).
+__global__ void __launch_bounds__(256) k_fp64_peak(int iters, double seed, double* __restrict__ sink) {
+  double a[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) a[k] = seed + k + threadIdx.x * 1e-9;
+  const double m = 1.0 - 1e-12, c = 1e-13;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[k] = a[k] * m + c;
+  }
+  double s = 0.0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s += a[k];
+  if (s == 123.456) sink[0] = s;  // never true: keeps the chains alive
+}
+
 }  // namespace
 
 static inline int point_grid(const Handle* h) {
@@ -43,12 +62,21 @@ static inline int point_grid(const Handle* h) {
 static inline int obs_grid(const Handle* h) {
   return (int)std::min<int64_t>(cdiv(h->pb.N, 256), (int64_t)h->sm_count * 16);
 }
-int partial_capacity(const Handle* h) { return std::max(point_grid(h), obs_grid(h)); }
+static inline int fused_grid(const Handle* h) {
+  if (h->pb.flow) return (int)std::min<int64_t>(std::max(h->pb.n_st, 1), (int64_t)h->sm_count);
+  const int per_sm = h->pb.tile_obs <= FUSED_TILE_2CTA ? std::max(2, std::min(8, (FUSED_TILE_1CTA * FUSED_REC_BYTES) /
+                                                                              std::max(h->pb.tile_obs * FUSED_REC_BYTES, 1)))
+                                                       : 1;
+  return (int)std::min<int64_t>(std::max(h->pb.n_st, 1), (int64_t)h->sm_count * per_sm);
+}
+int partial_capacity(const Handle* h) {
+  return std::max(std::max(std::max(point_grid(h), obs_grid(h)), fused_grid(h)), h->pb.flow ? h->pb.n_st : 0);
+}
 
 void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* x_out, double* camprep) {
   const int C = (int)h->pb.C;
   if (C == 0) return;
-  k_cam_prep<<<cdiv(C, 128), 128, 0, h->stream>>>(C, x_cams, dc, x_out, camprep);
+  k_cam_prep<<<cdiv(C, 128), 128, 0, h->stream>>>(C, h->pb.Cs, x_cams, dc, x_out, camprep);
   h->st.launches += 1;
 }
 
@@ -88,6 +116,44 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
   Work& w = h->w;
   cudaStream_t st = h->stream;
   KernelTimer t(h);
+  if (pb.fused) {
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(k_lin_fused<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_TILE_2CTA * FUSED_REC_BYTES);
+      cudaFuncSetAttribute(k_lin_fused<512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_TILE_1CTA * FUSED_REC_BYTES);
+      attr_set = true;
+    }
+    const int smem = pb.tile_obs * FUSED_REC_BYTES;
+    const int fg = fused_grid(h);
+    t.begin();
+    if (pb.flow) {
+      static bool flow_attr = false;
+      if (!flow_attr) {
+        cudaFuncSetAttribute(k_lin_flow, cudaFuncAttributeMaxDynamicSharedMemorySize, FlowSmem::TOTAL);
+        flow_attr = true;
+      }
+      k_lin_flow<<<fg, FLOW_THREADS, FlowSmem::TOTAL, st>>>(pb, x, w.camprep, lambda, w.pp, w.gp, w.spart, w.dpart, w.part,
+                                                         reinterpret_cast<int*>(w.scal + S_FLOW_ERR));
+    } else if (pb.tile_obs <= FUSED_TILE_2CTA)
+      k_lin_fused<256, 2><<<fg, 256, smem, st>>>(pb, x, w.camprep, lambda, w.pp, w.gp, w.spart, w.dpart, w.part);
+    else
+      k_lin_fused<512, 1><<<fg, 512, smem, st>>>(pb, x, w.camprep, lambda, w.pp, w.gp, w.spart, w.dpart, w.part);
+    t.end(&h->st.ms_lin_fused);
+    Slots sl{};
+    sl.s[0] = S_COST2;
+    sl.s[1] = S_GPMAX;
+    k_reduce_partials2<<<1, 256, 0, st>>>(pb.flow ? pb.n_st : fg, 1, 2, w.part, w.sums, w.scal, sl);
+    t.begin();
+    k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_slot_off,
+                                                                       pb.blk_slots, w.spart, pb.cam_dslot_off,
+                                                                       pb.cam_dslots, w.dpart, lambda, w.Sup);
+    k_slot_reduce_cam<<<cdiv(pb.C * 18, 256), 256, 0, st>>>((int)pb.C, pb.cam_dslot_off, pb.cam_dslots, w.dpart, w.udiag,
+                                                           w.gc, w.b);
+    t.end(&h->st.ms_slot_reduce);
+    h->st.launches += 4;
+    h->st.n_linearize += 1;
+    return;
+  }
   const int pg = point_grid(h);
   t.begin();
   k_lin_points<<<pg, LIN_WARPS * 32, 0, st>>>(pb, x, w.camprep, lambda, w.Y, w.rr, w.pp, w.gp, w.part);
@@ -162,4 +228,22 @@ void launch_densify(Handle* h, double* dense) {
   k_densify<<<cdiv((int64_t)h->pb.n_blk * 36, 256), 256, 0, h->stream>>>(h->pb.n_blk, (int)h->pb.C, h->pb.blk_r,
                                                                         h->pb.blk_c, h->w.Sup, dense);
   h->st.launches += 1;
+}
+
+// measured FP64 FMA throughput of the device in TFLOP/s (best of 5 timed launches after a warm-up)
+double measure_fp64_peak(Handle* h) {
+  const int iters = 4096, blocks = h->sm_count * 8, threads = 256;
+  float best = 1e30f;
+  for (int rep = 0; rep < 6; ++rep) {
+    cudaEventRecord(h->ev0, h->stream);
+    k_fp64_peak<<<blocks, threads, 0, h->stream>>>(iters, 1.0, h->w.scal);
+    cudaEventRecord(h->ev1, h->stream);
+    cudaEventSynchronize(h->ev1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    if (rep > 0 && ms < best) best = ms;
+  }
+  h->st.launches += 6;
+  const double flops = 2.0 * 64.0 * (double)iters * (double)blocks * (double)threads;
+  return flops / ((double)best * 1e-3) / 1e12;
 }

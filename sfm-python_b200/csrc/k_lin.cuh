@@ -108,7 +108,7 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
       const int i = a + (valid ? lane : 0);
       const int c = pb.cam[i], p = pb.pt[i];
       double r0, r1, Jc[12], Jp[6], vals[9], cp[CAMPREP_FIELDS];
-      load_cam(camprep, pb.C, c, cp);
+      load_cam(camprep, pb.Cs, c, cp);
       project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp);
       point_products(Jp, r0, r1, vals);
       if (!valid) {
@@ -143,7 +143,7 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
       for (int k = 0; k < 9; ++k) vals[k] = 0.0;
       for (int i = a + lane; i < b; i += 32) {
         double r0, r1, Jc[12], Jp[6], v9[9], cp[CAMPREP_FIELDS];
-        load_cam(camprep, pb.C, pb.cam[i], cp);
+        load_cam(camprep, pb.Cs, pb.cam[i], cp);
         project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
         point_products(Jp, r0, r1, v9);
 #pragma unroll
@@ -166,7 +166,7 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
         const bool valid = lane < nn;
         const int i = base + (valid ? lane : 0);
         double r0, r1, Jc[12], Jp[6], Yv[18], rt0, rt1, cp[CAMPREP_FIELDS];
-        load_cam(camprep, pb.C, pb.cam[i], cp);
+        load_cam(camprep, pb.Cs, pb.cam[i], cp);
         project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
         obs_outputs(Jc, Jp, Li, z, r0, r1, Yv, rt0, rt1);
         if (valid) {

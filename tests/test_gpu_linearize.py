@@ -86,3 +86,48 @@ def test_big_point_path(engine):
     d, pred, newc = engine.lm_step(pb.x0, lam, solver="cholesky")
     d_ref, pred_ref, _ = O.lm_step(pb.x0, *pb.args(), lam)
     assert np.abs(d - d_ref).max() <= 1e-6 * np.abs(d_ref).max()
+
+
+@pytest.mark.parametrize("tile_obs", [32, 64, 640, 1312])
+def test_fused_matches_unfused_and_oracle(tile_obs, monkeypatch):
+    """k_lin_fused (records in shared memory) against the unfused kernels and the oracle, several tile sizes,
+    including points seen twice by one camera and tiles that cut the camera windows."""
+    import b200ba
+    pb = b200ba.synthetic.make_problem(23, 900, 4000, seed=9, window=7)
+    ci = pb.camera_indices.copy()
+    ci[1] = ci[0]
+    ci[401] = ci[400]
+    args = (pb.n_cam, pb.n_pts, ci, pb.point_indices, pb.points_2d, pb.K)
+    lam = 2e-4
+    ref = O.schur_system(pb.x0, *args, lam)
+    g_ref = np.concatenate([ref["gc"].ravel(), ref["gp"].ravel()])
+    outs = {}
+    for fused, flow in (("1", "1"), ("1", "0"), ("0", "0")):
+        monkeypatch.setenv("B200BA_FUSED", fused)
+        monkeypatch.setenv("B200BA_FLOW", flow)
+        monkeypatch.setenv("B200BA_TILE_OBS", str(tile_obs))
+        eng = b200ba.Engine(0)
+        eng.set_problem(*args)
+        out = eng.normal_equations(pb.x0, lam)
+        st = eng.stats()
+        assert (st["n_self_slots"] > 0) == (fused == "1")
+        outs[fused + flow] = out
+        assert abs(out["cost"] - ref["cost"]) <= 1e-12 * ref["cost"]
+        assert np.abs(out["grad"] - g_ref).max() <= 1e-10 * np.abs(g_ref).max()
+        assert np.abs(out["b"] - ref["b"]).max() <= 1e-9 * np.abs(ref["b"]).max()
+        assert np.abs(out["S"] - ref["S"]).max() <= 1e-9 * np.abs(ref["S"]).max()
+        eng.close()
+    assert np.abs(outs["10"]["S"] - outs["00"]["S"]).max() <= 1e-11 * np.abs(ref["S"]).max()
+    if tile_obs <= 512:   # the dataflow kernel ran: same slot partials as the barrier version, bit for bit
+        assert np.array_equal(outs["11"]["S"], outs["10"]["S"]) and np.array_equal(outs["11"]["b"], outs["10"]["b"])
+
+
+def test_fused_is_bit_reproducible():
+    import b200ba
+    pb = b200ba.synthetic.make_problem(40, 3000, 13000, seed=3, window=9)
+    eng = b200ba.Engine(0)
+    eng.set_problem(*pb.args())
+    a = eng.normal_equations(pb.x0, 1e-4)
+    b = eng.normal_equations(pb.x0, 1e-4)
+    assert np.array_equal(a["S"], b["S"]) and np.array_equal(a["b"], b["b"]) and a["cost"] == b["cost"]
+    eng.close()
