@@ -58,7 +58,8 @@ typedef struct b200ba_options {
   int32_t verbose;        /* 0 silent, 1 termination line, 2 per-iteration table (scipy's columns) */
   int32_t solver;         /* b200ba_solver */
   double lambda0;         /* initial Marquardt damping, <= 0 -> 1e-4 */
-  double pcg_rtol;        /* relative residual of the reduced-camera PCG, <= 0 -> 1e-6 */
+  double pcg_rtol;        /* relative residual of the reduced-camera PCG; <= 0 -> inexact-Newton forcing term chosen by
+                             the LM loop (0.1, tightened to 1e-2 once the relative cost reduction drops below 1e-4) */
   int32_t pcg_max_iter;   /* <= 0 -> 500 */
   int32_t fixed_iters;    /* > 0: run exactly this many LM iterations, ignoring the tolerances (benchmarks) */
 } b200ba_options;

@@ -135,6 +135,7 @@ static int alloc_work(Handle* h) {
   WALLOC(w.spart, (int64_t)std::max(pb.n_sch, pb.n_slot) * 36);
   WALLOC(w.U, C * 21);
   WALLOC(w.dpart, (int64_t)pb.n_dslot * 40);
+  WALLOC(w.camsum, C * 40);
   w.comm_count = (int64_t)pb.n_blk * 36 + 18 * C + S_NSUM;
   WALLOC(w.comm, w.comm_count);
   w.Sup = w.comm;

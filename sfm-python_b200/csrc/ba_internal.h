@@ -132,6 +132,7 @@ struct Work {
   double* spart = nullptr;    // [n_sch*36]
   double* U = nullptr;        // [C*21]
   double* dpart = nullptr;    // [n_dslot*40] self-slot partials of the fused kernel
+  double* camsum = nullptr;   // [C*40] per-camera sums of the self-slot partials
   // ---- contiguous all-reduce buffer: Sup | b | gc | udiag | sums
   double* comm = nullptr;
   double* Sup = nullptr;      // [n_blk*36]

@@ -11,6 +11,8 @@
 //   k_backsub_trial   delta_p back-substitution fused with the trial residual at x + delta
 //   k_lin_fused       (default) k_lin_points + k_cam_side + k_schur in one kernel: per-observation records live only in
 //                     shared memory (k_fused.cuh); the three kernels above remain as the fallback / A-B path
+#include <type_traits>
+
 #include "ba_internal.h"
 
 namespace b200ba {

@@ -275,7 +275,7 @@ __global__ void k_blob_fill(int n_st, const int* __restrict__ blob_off, int4* __
     if (threadIdx.x == 0) info[4 * t + 1].x = off;
     int* w = reinterpret_cast<int*>(blob + off);
     if (threadIdx.x < 8) {
-      const int hdr[8] = {np, nd, npent, nobs, 0, 0, 0, 0};
+      const int hdr[8] = {np, nd, npent, nobs, ps, ds, 0, 0};
       w[threadIdx.x] = hdr[threadIdx.x];
     }
     int* pd = w + 8;

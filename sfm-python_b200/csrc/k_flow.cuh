@@ -30,9 +30,11 @@ struct FlowSmem {
   static constexpr int IDXP = IDXC + 2 * FLOW_IDX_BYTES;                     // [2][FLOW_IDX_BYTES] pt window
   static constexpr int META = IDXP + 2 * FLOW_IDX_BYTES;                     // [2][FLOW_META_CAP]
   static constexpr int BAR = META + 2 * FLOW_META_CAP;                       // 4 mbarriers: inA[2], meta[2]
-  static constexpr int CTR = BAR + 4 * 8;                                    // q_next, doneA[2], doneBC[2], error
+  static constexpr int INFO = BAR + 4 * 8;                                   // [2][4] int4: staged tile_info of the A tile
+  static constexpr int CTR = INFO + 2 * 64;                                  // q_next, doneA[2], doneBC[2], error
   static constexpr int RED = CTR + 8 * 4;                                    // [2][FLOW_MAX_WT][2] doubles: (sum r^2, max |g_p|)
-  static constexpr int TOTAL = RED + 2 * FLOW_MAX_WT * 2 * 8;                // per warp tile, summed in index order
+  static constexpr int TSUM = RED + 2 * FLOW_MAX_WT * 2 * 8;                 // [64][2] doubles: tile sums, ring by k % 64
+  static constexpr int TOTAL = TSUM + 64 * 2 * 8;
 };
 static_assert(FlowSmem::TOTAL <= 232448, "dataflow kernel shared memory exceeds the 227 KB opt-in limit");
 
@@ -71,6 +73,9 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, unsign
                : "memory");
 }
 
+#ifndef FLOW_PROF
+#define FLOW_PROF 0
+#endif
 constexpr int FLOW_SPIN_LIMIT = 1 << 24;  // bail out instead of hanging the GPU if a dependency never resolves
 
 __device__ __forceinline__ void l2_prefetch(const void* p, unsigned bytes) {  // p 16-byte aligned, bytes % 16 == 0
@@ -96,7 +101,8 @@ __device__ __forceinline__ void flow_issue_inA(const FlowCtx& c, int t, int k) {
   const int cmin = i1.z, cspan = (pb.tile_info[4 * t].w & 2) ? i1.w : 0;
   unsigned long long* bar = c.bars + j;
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
-  mbar_expect_tx(bar, 2 * ib + (unsigned)(CAMPREP_FIELDS * cspan * 8));
+  mbar_expect_tx(bar, 2 * ib + (unsigned)(CAMPREP_FIELDS * cspan * 8) + 64u);
+  bulk_g2s(c.sm + FlowSmem::INFO + j * 64, pb.tile_info + 4 * t, 64u, bar);
   bulk_g2s(c.sm + FlowSmem::IDXC + j * FLOW_IDX_BYTES, pb.cam + a0a, ib, bar);
   bulk_g2s(c.sm + FlowSmem::IDXP + j * FLOW_IDX_BYTES, pb.pt + a0a, ib, bar);
   if (cspan > 0) {
@@ -149,7 +155,7 @@ __device__ __forceinline__ bool flow_wait_ctr(const int* ctr, int target, int* e
 __global__ void __launch_bounds__(FLOW_THREADS, 1)
 k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, const double* __restrict__ camprep, double lambda,
            double* __restrict__ pp, double* __restrict__ gp, double* __restrict__ spart, double* __restrict__ dpart,
-           double* __restrict__ part, int* __restrict__ gerr) {
+           double* __restrict__ part, int* __restrict__ gerr, long long* __restrict__ prof) {
   extern __shared__ __align__(128) unsigned char fsm[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int g = lane % FG, sub = lane / FG;
@@ -163,6 +169,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < 8; ++i) ctr[i] = 0;
+    for (int i = 0; i < 128; ++i) reinterpret_cast<double*>(fsm + FlowSmem::TSUM)[i] = 0.0;
     for (int i = 0; i < 4; ++i) mbar_init(bars + i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
@@ -171,15 +178,20 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
     for (int k = 0; k < 2 && k < K; ++k) { flow_issue_inA(cx, tile_of(k), k); flow_issue_meta(cx, tile_of(k), k); }
   }
 
+  long long tA = 0, tC = 0, tB = 0, tW = 0, tQ = 0, nIt = 0;  // FLOW_PROF: cycles per item kind, waits, queue
+  (void)tA; (void)tC; (void)tB; (void)tW; (void)tQ; (void)nIt;
   // ---- item bodies ----------------------------------------------------------------------------------------------
   // A item: warp tile r of tile kk (sequence index) -> records in buffer kk & 1
   auto do_A = [&](int kk, int r, int nA, int tgtA, int tgtBC_prev) -> bool {
     const int j = kk & 1, t = tile_of(kk);
-    const int4 i0 = pb.tile_info[4 * t], i1 = pb.tile_info[4 * t + 1], i2 = pb.tile_info[4 * t + 2];
     // record buffer j was last read by the B / C items of tile kk - 2; the staged inputs of tile kk must have landed
+    const long long c0 = FLOW_PROF ? clock64() : 0;
     bool ok = flow_wait_ctr(&ctr[3 + j], tgtBC_prev, &ctr[5]) && flow_wait_bar(bars + j, kk >> 1, &ctr[5]);
     ok = __all_sync(FULL, ok);
     if (!ok) return false;
+    const long long c1 = FLOW_PROF ? clock64() : 0;
+    const int4* sinfo = reinterpret_cast<const int4*>(fsm + FlowSmem::INFO + j * 64);
+    const int4 i0 = sinfo[0], i1 = sinfo[1], i2 = sinfo[2];
     const int a0 = i2.x, wt = i2.z + r;
     const int* s_cam = reinterpret_cast<const int*>(fsm + FlowSmem::IDXC + j * FLOW_IDX_BYTES) + (a0 & 3);
     const int* s_pt = reinterpret_cast<const int*>(fsm + FlowSmem::IDXP + j * FLOW_IDX_BYTES) + (a0 & 3);
@@ -272,27 +284,34 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       if (old + 1 == tgtA - 1) {
         double s2 = 0.0, m2 = 0.0;
         for (int w = 0; w < nA; ++w) { s2 += tred[2 * w]; m2 = fmax(m2, tred[2 * w + 1]); }
-        part[(int64_t)t * 8] = s2;
-        part[(int64_t)t * 8 + 1] = m2;
+        // per-CTA ring: tiles k and k + 64 are strictly ordered by the dependency chain => fixed summation order
+        double* ts = reinterpret_cast<double*>(fsm + FlowSmem::TSUM) + 2 * (kk & 63);
+        ts[0] += s2;
+        ts[1] = fmax(ts[1], m2);
         add_release_s(&ctr[1 + j], 1);  // now the consumers of the tile may start (and, later, reuse of tred)
         // last A item of tile kk: its staging slot is free -> stage the inputs of tile kk + 2
         if (kk + 2 < K) flow_issue_inA(cx, tile_of(kk + 2), kk + 2);
       }
     }
+    if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; tA += c2 - c1; }
     return true;
   };
 
   // B / C item r of tile k: 8 slots, 4 lanes each, records read from buffer k & 1
-  auto do_BC = [&](int k, int r, int4 i0, int tgtA, int tgtBC) -> bool {
+  auto do_BC = [&](auto staged_tag, int k, int r, int4 i0, int tgtA, int tgtBC) -> bool {
+    constexpr bool STAGED = decltype(staged_tag)::value;  // blob in shared memory (LDS) or too large: global memory
     const int j = k & 1, t = tile_of(k);
+    const long long c0 = FLOW_PROF ? clock64() : 0;
     bool ok = flow_wait_ctr(&ctr[1 + j], tgtA, &ctr[5]) && flow_wait_bar(bars + 2 + j, k >> 1, &ctr[5]);
     ok = __all_sync(FULL, ok);
     if (!ok) return false;
     __threadfence_block();
-    const int4 i3 = pb.tile_info[4 * t + 3];
-    const int* blob = (i0.w & 1) ? reinterpret_cast<const int*>(fsm + FlowSmem::META + j * FLOW_META_CAP)
-                                 : reinterpret_cast<const int*>(pb.blob + pb.tile_info[4 * t + 1].x);
+    const long long c1 = FLOW_PROF ? clock64() : 0;
+    const int* blob;
+    if (STAGED) blob = reinterpret_cast<const int*>(fsm + FlowSmem::META + j * FLOW_META_CAP);
+    else blob = reinterpret_cast<const int*>(pb.blob + pb.tile_info[4 * t + 1].x);
     const int np = i0.y, nd = i0.z, nC = (np + FLOW_SPI - 1) / FLOW_SPI;
+    const int pbase = blob[4], dbase = blob[5];
     const double* rec = reinterpret_cast<const double*>(fsm + FlowSmem::REC) + j * (FLOW_TILE * FREC);
     const int* pdesc = blob + 8;
     const int* ddesc = pdesc + 2 * np;
@@ -309,7 +328,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       double q9[9];
       group_reduce_scatter<18>(acc, q9, g);
       if (active) {
-        double* o = spart + 36 * (int64_t)(i3.x + s) + 9 * (((g & 1) << 1) | (g >> 1));
+        double* o = spart + 36 * (int64_t)(pbase + s) + 9 * (((g & 1) << 1) | (g >> 1));
 #pragma unroll
         for (int q2 = 0; q2 < 9; ++q2) o[q2] = q9[q2];
       }
@@ -324,7 +343,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       double q10[10];
       group_reduce_scatter<20>(acc, q10, g);
       if (active) {
-        double* o = dpart + DPART * (int64_t)(i3.y + s) + 10 * (((g & 1) << 1) | (g >> 1));
+        double* o = dpart + DPART * (int64_t)(dbase + s) + 10 * (((g & 1) << 1) | (g >> 1));
 #pragma unroll
         for (int q2 = 0; q2 < 10; ++q2) o[q2] = q10[q2];
       }
@@ -335,6 +354,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       // last consumer of tile k: its metadata slot is free -> stage the blob of tile k + 2
       if (old + 1 == tgtBC && k + 2 < K) flow_issue_meta(cx, tile_of(k + 2), k + 2);
     }
+    if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; if (r < nC) tC += c2 - c1; else tB += c2 - c1; }
     return true;
   };
 
@@ -343,12 +363,17 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
   // A(2m+2) needs B/C(2m) (one whole group earlier), B/C(2m) needs A(2m) (ditto): a warp that claims an item normally
   // finds its dependency already satisfied.
   int s = -1, base = 0, n0 = 0, n1 = 0;                  // current step, first queue index, item counts of its two halves
-  int4 ie = make_int4(0, 0, 0, 0), io = ie;             // tile_info[.][0] of the even / odd tile of the current pair
+  const int4 zero4 = make_int4(0, 0, 0, 0);
+  int4 ie = zero4, io = zero4;                           // tile_info[.][0] of the even / odd tile of the current pair
+  // the pair after the current one, loaded one pair ahead so that the walk never waits on global memory
+  int4 ie_n = K > 0 ? pb.tile_info[4 * tile_of(0)] : zero4, io_n = K > 1 ? pb.tile_info[4 * tile_of(1)] : zero4;
   // cumulative completion targets per buffer parity (A targets count the items plus the finisher's extra signal)
   int cumA0 = 0, cumA1 = 0, cumBC0 = 0, cumBC1 = 0, prevBC0 = 0, prevBC1 = 0;
   const int n_steps = 2 * ((K + 1) / 2);
   bool ok = true;
+  const long long cstart = FLOW_PROF ? clock64() : 0;
   while (ok) {
+    const long long cq0 = FLOW_PROF ? clock64() : 0;
     int q = 0;
     if (lane == 0) q = atomicAdd(&ctr[0], 1);
     q = __shfl_sync(FULL, q, 0);
@@ -359,8 +384,10 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       if (s >= n_steps) { done = true; break; }
       const int m = s >> 1;
       if (!(s & 1)) {
-        ie = pb.tile_info[4 * tile_of(2 * m)];
-        io = (2 * m + 1 < K) ? pb.tile_info[4 * tile_of(2 * m + 1)] : make_int4(0, 0, 0, 0);
+        ie = ie_n;
+        io = io_n;
+        ie_n = (2 * m + 2 < K) ? pb.tile_info[4 * tile_of(2 * m + 2)] : zero4;
+        io_n = (2 * m + 3 < K) ? pb.tile_info[4 * tile_of(2 * m + 3)] : zero4;
         n0 = ie.x;
         n1 = io.x;
         prevBC0 = cumBC0; prevBC1 = cumBC1;
@@ -374,14 +401,31 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       }
     }
     if (done) break;
+    if (FLOW_PROF) { tQ += clock64() - cq0; ++nIt; }
     const int r = q - base, m = s >> 1;
     if (!(s & 1)) {
       ok = (r < n0) ? do_A(2 * m, r, n0, cumA0, prevBC0) : do_A(2 * m + 1, r - n0, n1, cumA1, prevBC1);
     } else {
-      ok = (r < n0) ? do_BC(2 * m, r, ie, cumA0, cumBC0) : do_BC(2 * m + 1, r - n0, io, cumA1, cumBC1);
+      const bool even = r < n0;
+      const int4 ii = even ? ie : io;
+      const int kk = even ? 2 * m : 2 * m + 1, rr = even ? r : r - n0;
+      const int tA = even ? cumA0 : cumA1, tBC = even ? cumBC0 : cumBC1;
+      if (ii.w & 1) ok = do_BC(std::true_type{}, kk, rr, ii, tA, tBC);
+      else ok = do_BC(std::false_type{}, kk, rr, ii, tA, tBC);
     }
   }
 
+  if (FLOW_PROF && prof && lane == 0) {
+    long long* o = prof + 8 * ((int64_t)blockIdx.x * FLOW_WARPS + wid);
+    o[0] = tA; o[1] = tC; o[2] = tB; o[3] = tW; o[4] = tQ; o[5] = nIt; o[6] = clock64() - cstart; o[7] = K;
+  }
   __syncthreads();
-  if (threadIdx.x == 0 && ctr[5]) atomicExch(gerr, 1);
+  if (threadIdx.x == 0) {
+    const double* ts = reinterpret_cast<const double*>(fsm + FlowSmem::TSUM);
+    double s2 = 0.0, m2 = 0.0;
+    for (int i = 0; i < 64; ++i) { s2 += ts[2 * i]; m2 = fmax(m2, ts[2 * i + 1]); }
+    part[blockIdx.x * 8] = s2;
+    part[blockIdx.x * 8 + 1] = m2;
+    if (ctr[5]) atomicExch(gerr, 1);
+  }
 }

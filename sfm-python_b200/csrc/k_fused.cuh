@@ -262,41 +262,49 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
   }
 }
 
+// Fixed-order sum of a list of strided partials with 8 independent chains (the loads of a round are in flight
+// together; the order of the additions is fixed, so the result is bit-reproducible).
+__device__ __forceinline__ double list_sum8(const int* __restrict__ list, int a, int b, const double* __restrict__ base,
+                                            int stride, int e) {
+  double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int q = a; q < b; q += 8) {
+    int id[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) id[u] = (q + u < b) ? list[q + u] : -1;
+#pragma unroll
+    for (int u = 0; u < 8; ++u)
+      if (id[u] >= 0) s[u] += base[(int64_t)id[u] * stride + e];
+  }
+  return ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
+}
+
+// per camera: sums of its self-slot partials -> camsum[c][40] (N 21 | diag U 6 | g_c 6 | b_c 6), and udiag, g_c, b
+__global__ void k_cam_sums(int C, const int* __restrict__ cam_dslot_off, const int* __restrict__ cam_dslots,
+                           const double* __restrict__ dpart, double* __restrict__ camsum, double* __restrict__ udiag,
+                           double* __restrict__ gc, double* __restrict__ b) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= C * DPART) return;
+  const int c = t / DPART, k = t % DPART;
+  const double s = (k < 39) ? list_sum8(cam_dslots, cam_dslot_off[c], cam_dslot_off[c + 1], dpart, DPART, k) : 0.0;
+  camsum[t] = s;
+  if (k >= 21 && k < 27) udiag[6 * c + (k - 21)] = s;
+  else if (k >= 27 && k < 33) gc[6 * c + (k - 27)] = s;
+  else if (k >= 33 && k < 39) b[6 * c + (k - 33)] = -s;
+}
+
 // Sup[g] = -(sum of the pair-slot partials of block g) [- N_c + lambda diag U_c on diagonal blocks]
 __global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
                                 const int* __restrict__ blk_slot_off, const int* __restrict__ blk_slots,
-                                const double* __restrict__ spart, const int* __restrict__ cam_dslot_off,
-                                const int* __restrict__ cam_dslots, const double* __restrict__ dpart, double lambda,
+                                const double* __restrict__ spart, const double* __restrict__ camsum, double lambda,
                                 double* __restrict__ Sup) {
   const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (t >= (int64_t)n_blk * 36) return;
   const int g = (int)(t / 36), e = (int)(t % 36);
-  double s = 0.0;
-  for (int q = blk_slot_off[g]; q < blk_slot_off[g + 1]; ++q) s += spart[(int64_t)blk_slots[q] * 36 + e];
+  double s = list_sum8(blk_slots, blk_slot_off[g], blk_slot_off[g + 1], spart, 36, e);
   if (blk_r[g] == blk_c[g]) {
     const int c = blk_r[g], r = e / 6, cc = e % 6;
-    const int k = tri6(min(r, cc), max(r, cc));
-    double nn = 0.0, ud = 0.0;
-    for (int q = cam_dslot_off[c]; q < cam_dslot_off[c + 1]; ++q) {
-      const double* d = dpart + DPART * (int64_t)cam_dslots[q];
-      nn += d[k];
-      if (r == cc) ud += d[21 + r];
-    }
-    s += nn - lambda * ud;
+    s += camsum[c * DPART + tri6(min(r, cc), max(r, cc))];
+    if (r == cc) s -= lambda * camsum[c * DPART + 21 + r];
   }
   Sup[t] = -s;
-}
-
-// diag U, g_c = J_c^T r, b_c = -J_c^T rt per camera from the self-slot partials
-__global__ void k_slot_reduce_cam(int C, const int* __restrict__ cam_dslot_off, const int* __restrict__ cam_dslots,
-                                  const double* __restrict__ dpart, double* __restrict__ udiag, double* __restrict__ gc,
-                                  double* __restrict__ b) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= C * 18) return;
-  const int c = t / 18, k = t % 18;
-  double s = 0.0;
-  for (int q = cam_dslot_off[c]; q < cam_dslot_off[c + 1]; ++q) s += dpart[DPART * (int64_t)cam_dslots[q] + 21 + k];
-  if (k < 6) udiag[6 * c + k] = s;
-  else if (k < 12) gc[6 * c + (k - 6)] = s;
-  else b[6 * c + (k - 12)] = -s;
 }

@@ -70,7 +70,7 @@ static inline int fused_grid(const Handle* h) {
   return (int)std::min<int64_t>(std::max(h->pb.n_st, 1), (int64_t)h->sm_count * per_sm);
 }
 int partial_capacity(const Handle* h) {
-  return std::max(std::max(std::max(point_grid(h), obs_grid(h)), fused_grid(h)), h->pb.flow ? h->pb.n_st : 0);
+  return std::max(std::max(point_grid(h), obs_grid(h)), fused_grid(h));
 }
 
 void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* x_out, double* camprep) {
@@ -133,7 +133,8 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
         flow_attr = true;
       }
       k_lin_flow<<<fg, FLOW_THREADS, FlowSmem::TOTAL, st>>>(pb, x, w.camprep, lambda, w.pp, w.gp, w.spart, w.dpart, w.part,
-                                                         reinterpret_cast<int*>(w.scal + S_FLOW_ERR));
+                                                         reinterpret_cast<int*>(w.scal + S_FLOW_ERR),
+                                                         FLOW_PROF ? reinterpret_cast<long long*>(w.Y) : nullptr);
     } else if (pb.tile_obs <= FUSED_TILE_2CTA)
       k_lin_fused<256, 2><<<fg, 256, smem, st>>>(pb, x, w.camprep, lambda, w.pp, w.gp, w.spart, w.dpart, w.part);
     else
@@ -142,13 +143,12 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
     Slots sl{};
     sl.s[0] = S_COST2;
     sl.s[1] = S_GPMAX;
-    k_reduce_partials2<<<1, 256, 0, st>>>(pb.flow ? pb.n_st : fg, 1, 2, w.part, w.sums, w.scal, sl);
+    k_reduce_partials2<<<1, 256, 0, st>>>(fg, 1, 2, w.part, w.sums, w.scal, sl);
     t.begin();
-    k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 256), 256, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_slot_off,
-                                                                       pb.blk_slots, w.spart, pb.cam_dslot_off,
-                                                                       pb.cam_dslots, w.dpart, lambda, w.Sup);
-    k_slot_reduce_cam<<<cdiv(pb.C * 18, 256), 256, 0, st>>>((int)pb.C, pb.cam_dslot_off, pb.cam_dslots, w.dpart, w.udiag,
-                                                           w.gc, w.b);
+    k_cam_sums<<<cdiv(pb.C * 40, 128), 128, 0, st>>>((int)pb.C, pb.cam_dslot_off, pb.cam_dslots, w.dpart, w.camsum, w.udiag,
+                                                    w.gc, w.b);
+    k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 128), 128, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_slot_off,
+                                                                       pb.blk_slots, w.spart, w.camsum, lambda, w.Sup);
     t.end(&h->st.ms_slot_reduce);
     h->st.launches += 4;
     h->st.n_linearize += 1;

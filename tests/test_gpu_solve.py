@@ -67,3 +67,18 @@ def test_config_B_converged_cost(engine, solver):
     assert abs(res.cost - ref_cost) <= 1e-6 * ref_cost
     cost_check = 0.5 * float(np.sum(O.residuals(x, *pb.args()) ** 2))
     assert abs(cost_check - res.cost) <= 1e-9 * res.cost
+
+
+def test_inexact_pcg_reaches_the_exact_minimum(engine):
+    """Mid-size problem (PCG territory, 200 cameras): the default inexact-Newton forcing term must converge to the same
+    cost as a tightly solved reduced system, within the 1e-6 bar of north_star."""
+    import b200ba
+    pb = b200ba.synthetic.make_problem(200, 20000, 80000, seed=4)
+    engine.set_problem(*pb.args())
+    x_a, a = engine.solve(pb.x0, ftol=1e-10, solver="pcg")
+    x_b, b = engine.solve(pb.x0, ftol=1e-10, solver="pcg", pcg_rtol=1e-10, pcg_max_iter=5000)
+    assert a.status > 0 and b.status > 0
+    assert abs(a.cost - b.cost) <= 1e-6 * b.cost
+    assert a.pcg_iters < b.pcg_iters
+    cost_check = 0.5 * float(np.sum(O.residuals(x_a, *pb.args()) ** 2))
+    assert abs(cost_check - a.cost) <= 1e-9 * a.cost
