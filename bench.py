@@ -45,6 +45,9 @@ def parse():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-obs", type=int, default=3000)
+    ap.add_argument("--sweep", action="store_true",
+                    help="config E: residual + materialised Jacobian blocks, N = 1M..--sweep-max observations, vs the HBM roofline")
+    ap.add_argument("--sweep-max", type=int, default=100_000_000)
     return ap.parse_args()
 
 
@@ -137,6 +140,60 @@ def run_reference(a, rank):
                       "data": "synthetic", "config": {"workload": WORKLOADS[a.workload], "sample": sample},
                       "cpu_baseline": {"value": v, "unit": UNIT, "cores": 1, "kind": "port", "sample": sample},
                       "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+# ---------------------------------------------------------------- config E: residual + Jacobian sweep vs the HBM roofline
+def run_sweep(a):
+    """BASELINE.json configs[4]: k_residual (40 B/obs) and k_jacobian (184 B/obs materialised: r 16 + Jc 96 + Jp 48 out,
+    u, v, cam, pt 24 in) at N = 1M .. 100M observations, 1000 cameras, P = N / 4; kernel time from CUDA events placed
+    directly around the kernel on the library stream (profiling mode)."""
+    import torch
+
+    import b200ba
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    eng = b200ba.Engine(0)
+    rows = []
+    for n_obs in (1_000_000, 2_000_000, 5_000_000, 10_000_000, 20_000_000, 50_000_000, 100_000_000):
+        if n_obs > a.sweep_max:
+            break
+        n_cam, n_pts = 1000, n_obs // 4
+        pb = b200ba.synthetic.make_problem(n_cam, n_pts, n_obs, seed=a.seed)
+        os.environ["B200BA_SCHUR_STREAM"] = "1"      # the sweep needs no Schur structures: cheapest setup path
+        os.environ["B200BA_FUSED"] = "0"
+        eng.set_problem(n_cam, n_pts, pb.camera_indices, pb.point_indices, pb.points_2d, pb.K)
+        x = torch.from_numpy(pb.x0).cuda()
+        r = torch.empty(2 * n_obs, dtype=torch.float64, device="cuda")
+        jc = torch.empty(12 * n_obs, dtype=torch.float64, device="cuda")
+        jp = torch.empty(6 * n_obs, dtype=torch.float64, device="cuda")
+        eng.set_profiling(True)
+        for _ in range(3):
+            eng.jacobian_blocks_dev(x.data_ptr(), r.data_ptr(), jc.data_ptr(), jp.data_ptr())
+            eng.residuals_dev(x.data_ptr(), r.data_ptr())
+        eng.reset_stats()
+        reps = 10
+        for _ in range(reps):
+            eng.jacobian_blocks_dev(x.data_ptr(), r.data_ptr(), jc.data_ptr(), jp.data_ptr())
+            eng.residuals_dev(x.data_ptr(), r.data_ptr())
+        st = eng.stats()
+        eng.set_profiling(False)
+        t_j = st["ms_jacobian"] / reps * 1e-3
+        t_r = st["ms_residual"] / reps * 1e-3
+        bj = 184 * n_obs + 48 * n_cam + 24 * n_pts
+        br = 40 * n_obs + 48 * n_cam + 24 * n_pts
+        rows.append({"n_obs": n_obs, "jacobian_ms": t_j * 1e3, "jacobian_GBps": bj / t_j / 1e9, "jacobian_frac": bj / t_j / 1e9 / peak,
+                     "jacobian_obs_per_s": n_obs / t_j, "residual_ms": t_r * 1e3, "residual_GBps": br / t_r / 1e9,
+                     "residual_frac": br / t_r / 1e9 / peak,
+                     "note_residual": "ms_residual covers k_cam_prep + k_residual + the partial reduction"})
+        del x, r, jc, jp
+        torch.cuda.empty_cache()
+    print(json.dumps({"metric": "residual+Jacobian sweep (config E)", "unit": "GB/s", "peak_hbm_gbs": peak,
+                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured)" if peaks else "fallback 6650 GB/s",
+                      "bytes_per_obs": {"jacobian": 184, "residual": 40}, "dtype": "f64", "data": "synthetic", "rows": rows}))
 
 
 # ---------------------------------------------------------------- GPU arm
@@ -235,7 +292,15 @@ def run_b200(a, rank, world, local_rank):
     if td:
         td.all_reduce(lm_ms, op=td.ReduceOp.MAX)
     lm_ms = float(lm_ms.item())
-    lm = {"lm_iters_per_sec": a.steps / (lm_ms * 1e-3), "ms_per_lm_iter": lm_ms / a.steps,
+    # phase breakdown of one LM iteration (profiling mode: events around each phase, separate pass)
+    x_work.copy_(x_dev)
+    eng.set_profiling(True)
+    eng.reset_stats()
+    eng.solve_dev(x_work.data_ptr(), fixed_iters=3, solver=solver)
+    sq = eng.stats()
+    eng.set_profiling(False)
+    lm_phase = {k: sq[k] / 3 for k in ("ms_lin_fused", "ms_slot_reduce", "ms_allreduce", "ms_camera_solve", "ms_backsub_trial")}
+    lm = {"lm_iters_per_sec": a.steps / (lm_ms * 1e-3), "ms_per_lm_iter": lm_ms / a.steps, "lm_phase_ms": lm_phase,
           "pcg_iters_per_lm_iter": res.pcg_iters / max(res.n_iter, 1), "solver": solver,
           "cost_initial": res.initial_cost, "cost_after": res.cost}
 
@@ -329,6 +394,10 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
         run_reference(a, rank)
+        return
+    if a.sweep:
+        if rank == 0:
+            run_sweep(a)
         return
     run_b200(a, rank, world, local_rank)
     if world > 1:

@@ -89,6 +89,7 @@ typedef struct b200ba_stats {
   int64_t bytes_device;   /* device memory held by the handle */
   double ms_lin_fused, ms_slot_reduce;   /* fused linearisation + Schur kernel and its fixed-order partial reduction */
   int64_t n_tiles, n_pair_slots, n_self_slots;
+  double ms_jacobian;     /* k_jacobian alone (config E sweep) */
 } b200ba_stats;
 
 int b200ba_version(void);

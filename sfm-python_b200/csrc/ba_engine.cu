@@ -147,7 +147,7 @@ static int alloc_work(Handle* h) {
   w.n_part = partial_capacity(h);
   WALLOC(w.part, (int64_t)w.n_part * 8);
   WALLOC(w.dc, 6 * C);
-  WALLOC(w.pcg, 6 * C * 4 + C * 36);
+  WALLOC(w.pcg, 6 * C * 5 + C * 36);
   WALLOC(w.pcg_part, (int64_t)2 * 4 * std::max(pcg_grid(h), 1));
   if (C <= DENSE_MAX_CAM) { WALLOC(w.dense, 36 * C * C); }
 #undef WALLOC

@@ -146,7 +146,7 @@ struct Work {
   double* part = nullptr;     // [n_part * 8] per-CTA partials of the point-major kernels
   int n_part = 0;
   double* dc = nullptr;       // [6C] camera step
-  double* pcg = nullptr;      // [6C*4 + C*36] r z p Ap Minv
+  double* pcg = nullptr;      // [6C*5 + C*36] r u p w s Minv
   double* pcg_part = nullptr; // [grid*4]
   double* dense = nullptr;    // [(6C)^2] Cholesky work (only n_cam <= DENSE_MAX_CAM)
   double* h_scal = nullptr;   // pinned host mirror [NSCAL]

@@ -118,16 +118,26 @@ BA_HD void project_jac(const double* __restrict__ cp, const Intrinsics& K, doubl
 // Damped 3x3 point block: V* = V + lambda*diag(V);  V* = L L^T;  returns Linv (lower, 6 entries:
 // i00 i10 i11 i20 i21 i22).  A non-positive pivot (rank-deficient point, e.g. a single observation
 // with lambda = 0) freezes the point: Linv = 0 => no Schur contribution, delta_p = 0.
+// 1/sqrt(x): the device intrinsic is one MUFU + two Newton steps instead of a full sqrt followed by a full division
+// (three of these sit on the dependent chain of every point's 3x3 Cholesky).
+BA_HD double inv_sqrt(double x) {
+#ifdef __CUDA_ARCH__
+  return rsqrt(x);
+#else
+  return 1.0 / sqrt(x);
+#endif
+}
+
 BA_HD bool point_factor(const double* __restrict__ V /*v00 v10 v11 v20 v21 v22*/, double lambda,
                         double* __restrict__ Li) {
   const double d = 1.0 + lambda;
   const double v00 = V[0] * d, v10 = V[1], v11 = V[2] * d, v20 = V[3], v21 = V[4], v22 = V[5] * d;
   bool ok = v00 > 0.0;
-  const double i00 = ok ? 1.0 / sqrt(v00) : 0.0;
+  const double i00 = ok ? inv_sqrt(v00) : 0.0;
   const double l10 = v10 * i00, l20 = v20 * i00;
   const double s11 = v11 - l10 * l10;
   ok = ok && (s11 > 0.0);
-  const double i11 = ok ? 1.0 / sqrt(s11) : 0.0;
+  const double i11 = ok ? inv_sqrt(s11) : 0.0;
   const double l21 = (v21 - l20 * l10) * i11;
   const double s22 = v22 - l20 * l20 - l21 * l21;
   ok = ok && (s22 > 0.0) && (s22 == s22) && (s22 < 1e300);
@@ -135,7 +145,7 @@ BA_HD bool point_factor(const double* __restrict__ V /*v00 v10 v11 v20 v21 v22*/
     Li[0] = Li[1] = Li[2] = Li[3] = Li[4] = Li[5] = 0.0;
     return false;
   }
-  const double i22 = 1.0 / sqrt(s22);
+  const double i22 = inv_sqrt(s22);
   const double i10 = -i11 * l10 * i00;
   const double i21 = -i22 * l21 * i11;
   const double i20 = -(i21 * l10 + i22 * l20) * i00;

@@ -27,7 +27,7 @@ struct PcgArgs {
   int C;
   const int* rowptr; const int* col; const int* src; const int* diag_blk;
   const double* Sup; const double* b;
-  double* x; double* r; double* z; double* p; double* Ap; double* Minv;
+  double* x; double* r; double* z; double* p; double* Ap; double* s; double* Minv;
   double* part;  // [2 * gridDim * 4]
   double* scal;
   double rtol; int max_iter;
@@ -111,7 +111,65 @@ __device__ void inv6(const double* __restrict__ A, double* __restrict__ Mi) {
     }
 }
 
-__global__ void __launch_bounds__(PCG_T) k_pcg(PcgArgs a) {
+// y[6c .. 6c+5] = (S v)[camera c] for the block rows of this warp; returns this lane's share of (y, v) (lanes 0..5).
+// Lane (kq, r) = (lane / 6, lane % 6), lanes 0..29, multiplies row r of every 5th block of the row; two steps (10
+// blocks) are in flight together, B rows and v are read as three 16-byte loads each.
+__device__ __forceinline__ double spmv_rows(const PcgArgs& a, const double* __restrict__ v, double* __restrict__ y,
+                                            int gwarp, int gwarps, int lane) {
+  const int kq = lane / 6, r = lane % 6;
+  double dot = 0.0;
+  for (int c = gwarp; c < a.C; c += gwarps) {
+    const int q0 = a.rowptr[c], q1 = a.rowptr[c + 1];
+    double acc = 0.0;
+    if (lane < 30) {
+      for (int q = q0 + kq; q < q1; q += 10) {
+        const int qb = q + 5;
+        const bool two = qb < q1;
+        const int s0 = a.src[q], c0 = a.col[q];
+        const int s1 = two ? a.src[qb] : s0, c1 = two ? a.col[qb] : c0;
+        const double* B0 = a.Sup + (int64_t)(s0 & 0x7fffffff) * 36;
+        const double* B1 = a.Sup + (int64_t)(s1 & 0x7fffffff) * 36;
+        const double2* v0 = reinterpret_cast<const double2*>(v + 6 * c0);
+        const double2* v1 = reinterpret_cast<const double2*>(v + 6 * c1);
+        double b0[6], b1[6];
+        if (s0 < 0) {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) b0[j] = B0[j * 6 + r];
+        } else {
+          const double2* p = reinterpret_cast<const double2*>(B0 + 6 * r);
+          const double2 t0 = p[0], t1 = p[1], t2 = p[2];
+          b0[0] = t0.x; b0[1] = t0.y; b0[2] = t1.x; b0[3] = t1.y; b0[4] = t2.x; b0[5] = t2.y;
+        }
+        if (s1 < 0) {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) b1[j] = B1[j * 6 + r];
+        } else {
+          const double2* p = reinterpret_cast<const double2*>(B1 + 6 * r);
+          const double2 t0 = p[0], t1 = p[1], t2 = p[2];
+          b1[0] = t0.x; b1[1] = t0.y; b1[2] = t1.x; b1[3] = t1.y; b1[4] = t2.x; b1[5] = t2.y;
+        }
+        const double2 x0 = v0[0], x1 = v0[1], x2 = v0[2];
+        const double2 z0 = v1[0], z1 = v1[1], z2 = v1[2];
+        acc += b0[0] * x0.x + b0[1] * x0.y + b0[2] * x1.x + b0[3] * x1.y + b0[4] * x2.x + b0[5] * x2.y;
+        if (two) acc += b1[0] * z0.x + b1[1] * z0.y + b1[2] * z1.x + b1[3] * z1.y + b1[4] * z2.x + b1[5] * z2.y;
+      }
+    }
+    double tot = 0.0;
+#pragma unroll
+    for (int g = 0; g < 5; ++g) tot += __shfl_sync(FULL, acc, (lane % 6) + 6 * g);
+    if (lane < 6) { y[6 * c + lane] = tot; dot += tot * v[6 * c + lane]; }
+  }
+  return dot;
+}
+
+// Block-Jacobi preconditioned CG in the Chronopoulos-Gear form: one mat-vec, one fused reduction and TWO grid-wide
+// synchronisations per iteration (the textbook form needs four).  With u = M^-1 r, w = S u:
+//     p = u + beta p,  s = w + beta s,  x += alpha p,  r -= alpha s,  u = M^-1 r            (local, per camera)
+//     w = S u                                                                                (after sync 1)
+//     gamma' = (r,u), delta = (w,u), rr = (r,r)                                              (one reduction = sync 2)
+//     beta = gamma'/gamma,  alpha = gamma' / (delta - beta gamma' / alpha)
+// All reductions are in fixed order, so every rank of a multi-GPU run computes the same bits.
+__global__ void __launch_bounds__(PCG_T, 3) k_pcg(PcgArgs a) {
   cg::grid_group grid = cg::this_grid();
   __shared__ double sm[128];
   const int C = a.C, n = 6 * C;
@@ -119,86 +177,83 @@ __global__ void __launch_bounds__(PCG_T) k_pcg(PcgArgs a) {
   const int gthreads = gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31;
   const int gwarp = gtid >> 5, gwarps = gthreads >> 5;
+  double* u = a.z;   // preconditioned residual
+  double* w = a.Ap;  // S u
+  double* s = a.s;   // S p
 
-  // ---- init: block-Jacobi inverse, x = 0, r = b, z = Minv r, p = z
-  double rz = 0.0, bb = 0.0;
+  // ---- init: block-Jacobi inverse, x = 0, r = b, u = Minv r, p = s = 0
+  double gam = 0.0, bb = 0.0;
   int phase = 0;
   for (int c = gtid; c < C; c += gthreads) {
     inv6(a.Sup + (int64_t)a.diag_blk[c] * 36, a.Minv + (int64_t)c * 36);
     double rv[6];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) { rv[k] = a.b[6 * c + k]; a.x[6 * c + k] = 0.0; a.r[6 * c + k] = rv[k]; bb += rv[k] * rv[k]; }
+    for (int k = 0; k < 6; ++k) {
+      rv[k] = a.b[6 * c + k];
+      a.x[6 * c + k] = 0.0; a.r[6 * c + k] = rv[k]; a.p[6 * c + k] = 0.0; s[6 * c + k] = 0.0;
+      bb += rv[k] * rv[k];
+    }
 #pragma unroll
     for (int i = 0; i < 6; ++i) {
-      double s = 0.0;
+      double t = 0.0;
 #pragma unroll
-      for (int k = 0; k < 6; ++k) s += a.Minv[(int64_t)c * 36 + i * 6 + k] * rv[k];
-      a.z[6 * c + i] = s; a.p[6 * c + i] = s; rz += s * rv[i];
+      for (int k = 0; k < 6; ++k) t += a.Minv[(int64_t)c * 36 + i * 6 + k] * rv[k];
+      u[6 * c + i] = t; gam += t * rv[i];
     }
   }
+  grid.sync();
+  double del = spmv_rows(a, u, w, gwarp, gwarps, lane);
   double d0, d1, d2;
-  grid_sum3(grid, a.part, phase, sm, rz, bb, 0.0, d0, d1, d2);
-  rz = d0; bb = d1;
-  double rr = bb;
-  int it = 0;
-  int fail = 0;
+  grid_sum3(grid, a.part, phase, sm, gam, del, bb, d0, d1, d2);
+  gam = d0; del = d1; bb = d2;
+  double rr = bb, alpha = 0.0, beta = 0.0;
+  int it = 0, fail = 0;
   const double thresh = a.rtol * a.rtol * bb;
-  while (it < a.max_iter && rr > thresh && bb > 0.0) {
-    // ---- Ap = S p  (warp per block row; 5 blocks x 6 rows per step on lanes 0..29)
-    double pAp = 0.0;
-    for (int c = gwarp; c < C; c += gwarps) {
-      const int q0 = a.rowptr[c], q1 = a.rowptr[c + 1];
-      const int kq = lane / 6, r = lane % 6;
-      double y = 0.0;
-      if (lane < 30) {
-        for (int q = q0 + kq; q < q1; q += 5) {
-          const int s = a.src[q];
-          const double* B = a.Sup + (int64_t)(s & 0x7fffffff) * 36;
-          const double* pv = a.p + 6 * a.col[q];
-          if (s < 0) {
-#pragma unroll
-            for (int j = 0; j < 6; ++j) y += B[j * 6 + r] * pv[j];
-          } else {
-#pragma unroll
-            for (int j = 0; j < 6; ++j) y += B[r * 6 + j] * pv[j];
-          }
+  if (bb > 0.0) {
+    if (!(del > 0.0)) fail = 1;
+    else alpha = gam / del;
+  }
+  while (!fail && it < a.max_iter && rr > thresh && bb > 0.0) {
+    // ---- local updates, one lane per (camera, component) -- 5 cameras per warp step: p, s, x, r elementwise, then
+    //      u = Minv r with the camera's six r values exchanged by shuffles; partial (r,u) and (r,r)
+    double gam_new = 0.0, rr_new = 0.0;
+    {
+      const int kq = lane / 6, comp = lane % 6;
+      for (int c5 = gwarp * 5; c5 < C; c5 += gwarps * 5) {
+        const int c = c5 + kq;
+        const bool on = lane < 30 && c < C;
+        const int i = 6 * c + comp;
+        double rk = 0.0;
+        if (on) {
+          const double pk = u[i] + beta * a.p[i];
+          const double sk = w[i] + beta * s[i];
+          a.p[i] = pk; s[i] = sk;
+          a.x[i] += alpha * pk;
+          rk = a.r[i] - alpha * sk;
+          a.r[i] = rk;
+          rr_new += rk * rk;
         }
-      }
-      double tot = 0.0;
+        double t = 0.0;
+        const double* mrow = a.Minv + (int64_t)(on ? c : 0) * 36 + comp * 6;
 #pragma unroll
-      for (int g = 0; g < 5; ++g) tot += __shfl_sync(FULL, y, (lane % 6) + 6 * g);
-      if (lane < 6) { a.Ap[6 * c + lane] = tot; pAp += tot * a.p[6 * c + lane]; }
-    }
-    grid_sum3(grid, a.part, phase, sm, pAp, 0.0, 0.0, d0, d1, d2);
-    pAp = d0;
-    if (!(pAp > 0.0)) { fail = 1; break; }  // not positive definite along p (uniform across the grid)
-    const double alpha = rz / pAp;
-    // ---- x += alpha p, r -= alpha Ap, z = Minv r   (thread per camera)
-    double rz_new = 0.0, rr_new = 0.0;
-    for (int c = gtid; c < C; c += gthreads) {
-      double rv[6];
-#pragma unroll
-      for (int k = 0; k < 6; ++k) {
-        a.x[6 * c + k] += alpha * a.p[6 * c + k];
-        rv[k] = a.r[6 * c + k] - alpha * a.Ap[6 * c + k];
-        a.r[6 * c + k] = rv[k];
-        rr_new += rv[k] * rv[k];
-      }
-#pragma unroll
-      for (int i = 0; i < 6; ++i) {
-        double s = 0.0;
-#pragma unroll
-        for (int k = 0; k < 6; ++k) s += a.Minv[(int64_t)c * 36 + i * 6 + k] * rv[k];
-        a.z[6 * c + i] = s; rz_new += s * rv[i];
+        for (int k = 0; k < 6; ++k) {
+          const double rj = __shfl_sync(FULL, rk, 6 * kq + k);
+          t += mrow[k] * rj;
+        }
+        if (on) { u[i] = t; gam_new += t * rk; }
       }
     }
-    grid_sum3(grid, a.part, phase, sm, rz_new, rr_new, 0.0, d0, d1, d2);
-    rz_new = d0; rr = d1;
     ++it;
-    const double beta = rz_new / rz;
-    rz = rz_new;
-    for (int i = gtid; i < n; i += gthreads) a.p[i] = a.z[i] + beta * a.p[i];
-    grid.sync();
+    grid.sync();                                   // u complete before the mat-vec reads it
+    const double del_part = spmv_rows(a, u, w, gwarp, gwarps, lane);
+    grid_sum3(grid, a.part, phase, sm, gam_new, del_part, rr_new, d0, d1, d2);
+    gam_new = d0; del = d1; rr = d2;
+    if (!(rr > thresh)) break;                     // converged: x already holds the iterate that r belongs to
+    beta = gam_new / gam;
+    const double denom = del - beta * gam_new / alpha;
+    if (!(denom > 0.0)) { fail = 1; break; }       // not positive definite along the search direction
+    alpha = gam_new / denom;
+    gam = gam_new;
   }
   // ---- dc . (b - S dc) for the predicted reduction
   double dr = 0.0;
@@ -289,7 +344,8 @@ int launch_pcg(Handle* h, double rtol, int max_iter) {
   a.C = (int)pb.C;
   a.rowptr = pb.bsr_rowptr; a.col = pb.bsr_col; a.src = pb.bsr_src; a.diag_blk = pb.diag_blk;
   a.Sup = w.Sup; a.b = w.b;
-  a.x = w.dc; a.r = w.pcg; a.z = w.pcg + n; a.p = w.pcg + 2 * n; a.Ap = w.pcg + 3 * n; a.Minv = w.pcg + 4 * n;
+  a.x = w.dc; a.r = w.pcg; a.z = w.pcg + n; a.p = w.pcg + 2 * n; a.Ap = w.pcg + 3 * n; a.s = w.pcg + 4 * n;
+  a.Minv = w.pcg + 5 * n;
   a.part = w.pcg_part; a.scal = w.scal; a.rtol = rtol; a.max_iter = max_iter;
   void* args[] = {&a};
   const int grid = pcg_grid(h);

@@ -179,6 +179,8 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
   }
 
   long long tA = 0, tC = 0, tB = 0, tW = 0, tQ = 0, nIt = 0;  // FLOW_PROF: cycles per item kind, waits, queue
+  long long tA1 = 0, tA2 = 0, tA3 = 0, cA = 0;              // A item: loads + projection | segmented scan | 3x3 factor
+  (void)tA1; (void)tA2; (void)tA3; (void)cA;
   (void)tA; (void)tC; (void)tB; (void)tW; (void)tQ; (void)nIt;
   // ---- item bodies ----------------------------------------------------------------------------------------------
   // A item: warp tile r of tile kk (sequence index) -> records in buffer kk & 1
@@ -209,6 +211,30 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
         load_cam(camprep, pb.Cs, c, cp);
       }
     };
+    // cost / gradient-norm partial of this warp tile; the last finisher of the tile sums them in index order, so the
+    // result does not depend on which warp ran which item
+    auto flow_signal_A = [&](double cost2_, double gmax_) {
+      cost2_ = warp_sum(cost2_);
+      gmax_ = warp_max(gmax_);
+      double* tred = sred + j * (2 * FLOW_MAX_WT);
+      if (lane == 0) { tred[2 * r] = cost2_; tred[2 * r + 1] = gmax_; }
+      __threadfence_block();
+      __syncwarp();
+      if (lane == 0) {
+        const int old = add_release_s(&ctr[1 + j], 1);
+        if (old + 1 == tgtA - 1) {
+          double s2 = 0.0, m2 = 0.0;
+          for (int w = 0; w < nA; ++w) { s2 += tred[2 * w]; m2 = fmax(m2, tred[2 * w + 1]); }
+          // per-CTA ring: tiles k and k + 64 are strictly ordered by the dependency chain => fixed summation order
+          double* ts = reinterpret_cast<double*>(fsm + FlowSmem::TSUM) + 2 * (kk & 63);
+          ts[0] += s2;
+          ts[1] = fmax(ts[1], m2);
+          add_release_s(&ctr[1 + j], 1);  // now the consumers of the tile may start (and, later, reuse of tred)
+          // last A item of tile kk: its staging slot is free -> stage the inputs of tile kk + 2
+          if (kk + 2 < K) flow_issue_inA(cx, tile_of(kk + 2), kk + 2);
+        }
+      }
+    };
     if (n <= 32) {
       const bool valid = lane < n;
       const int i = a + (valid ? lane : 0);
@@ -223,21 +249,27 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
 #pragma unroll
         for (int q2 = 0; q2 < 9; ++q2) vals[q2] = 0.0;
       }
+      if (FLOW_PROF) { const long long cc = clock64(); tA1 += cc - c1; cA = cc; }
       const SegInfo sg = seg_info(p, valid, lane);
       seg_allsum<9>(vals, sg, lane);
+      if (FLOW_PROF) { const long long cc = clock64(); tA2 += cc - cA; cA = cc; }
       double Li[6], z[3];
       point_factor(vals, lambda, Li);
       z[0] = Li[0] * vals[6];
       z[1] = Li[1] * vals[6] + Li[2] * vals[7];
       z[2] = Li[3] * vals[6] + Li[4] * vals[7] + Li[5] * vals[8];
+      if (FLOW_PROF) { const long long cc = clock64(); tA3 += cc - cA; cA = cc; }
       if (valid) {
         cost2 += r0 * r0 + r1 * r1;
         store_record(rec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
-        if (lane == sg.first) {
-          store_point(pp, gp, p, Li, z, vals);
-          gmax = fmax(gmax, fmax(fabs(vals[6]), fmax(fabs(vals[7]), fabs(vals[8]))));
-        }
+        if (lane == sg.first) gmax = fmax(gmax, fmax(fabs(vals[6]), fmax(fabs(vals[7]), fabs(vals[8]))));
       }
+      // the records are complete: signal first, write the per-point outputs to global memory afterwards (the fence
+      // below must not wait for them)
+      flow_signal_A(cost2, gmax);
+      if (valid && lane == sg.first) store_point(pp, gp, p, Li, z, vals);
+      if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; tA += c2 - c1; }
+      return true;
     } else {
       const int p = s_pt[a - a0];
       const double X0 = xp[3 * p], X1 = xp[3 * p + 1], X2 = xp[3 * p + 2];
@@ -271,28 +303,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
         store_record(rec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
       }
     }
-    // cost / gradient-norm partial of this warp tile; the last finisher of the tile sums them in index order, so the
-    // result does not depend on which warp ran which item
-    cost2 = warp_sum(cost2);
-    gmax = warp_max(gmax);
-    double* tred = sred + j * (2 * FLOW_MAX_WT);
-    if (lane == 0) { tred[2 * r] = cost2; tred[2 * r + 1] = gmax; }
-    __threadfence_block();
-    __syncwarp();
-    if (lane == 0) {
-      const int old = add_release_s(&ctr[1 + j], 1);
-      if (old + 1 == tgtA - 1) {
-        double s2 = 0.0, m2 = 0.0;
-        for (int w = 0; w < nA; ++w) { s2 += tred[2 * w]; m2 = fmax(m2, tred[2 * w + 1]); }
-        // per-CTA ring: tiles k and k + 64 are strictly ordered by the dependency chain => fixed summation order
-        double* ts = reinterpret_cast<double*>(fsm + FlowSmem::TSUM) + 2 * (kk & 63);
-        ts[0] += s2;
-        ts[1] = fmax(ts[1], m2);
-        add_release_s(&ctr[1 + j], 1);  // now the consumers of the tile may start (and, later, reuse of tred)
-        // last A item of tile kk: its staging slot is free -> stage the inputs of tile kk + 2
-        if (kk + 2 < K) flow_issue_inA(cx, tile_of(kk + 2), kk + 2);
-      }
-    }
+    flow_signal_A(cost2, gmax);
     if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; tA += c2 - c1; }
     return true;
   };
@@ -325,13 +336,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
 #pragma unroll
       for (int q2 = 0; q2 < 36; ++q2) acc[q2] = 0.0;
       pair_slot_body(rec, pent + ea, en, g, acc);
-      double q9[9];
-      group_reduce_scatter<18>(acc, q9, g);
-      if (active) {
-        double* o = spart + 36 * (int64_t)(pbase + s) + 9 * (((g & 1) << 1) | (g >> 1));
-#pragma unroll
-        for (int q2 = 0; q2 < 9; ++q2) o[q2] = q9[q2];
-      }
+      slot_reduce_store<36>(acc, spart + 36 * (int64_t)(pbase + s), g, active);
     } else {
       const int s = (r - nC) * FLOW_SPI + sub;
       const bool active = s < nd;
@@ -340,13 +345,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
 #pragma unroll
       for (int q2 = 0; q2 < 40; ++q2) acc[q2] = 0.0;
       self_slot_body(rec, dent + ea, en, g, acc);
-      double q10[10];
-      group_reduce_scatter<20>(acc, q10, g);
-      if (active) {
-        double* o = dpart + DPART * (int64_t)(dbase + s) + 10 * (((g & 1) << 1) | (g >> 1));
-#pragma unroll
-        for (int q2 = 0; q2 < 10; ++q2) o[q2] = q10[q2];
-      }
+      slot_reduce_store<40>(acc, dpart + DPART * (int64_t)(dbase + s), g, active);
     }
     __syncwarp();
     if (lane == 0) {
@@ -416,8 +415,9 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
   }
 
   if (FLOW_PROF && prof && lane == 0) {
-    long long* o = prof + 8 * ((int64_t)blockIdx.x * FLOW_WARPS + wid);
+    long long* o = prof + 16 * ((int64_t)blockIdx.x * FLOW_WARPS + wid);
     o[0] = tA; o[1] = tC; o[2] = tB; o[3] = tW; o[4] = tQ; o[5] = nIt; o[6] = clock64() - cstart; o[7] = K;
+    o[8] = tA1; o[9] = tA2; o[10] = tA3;
   }
   __syncthreads();
   if (threadIdx.x == 0) {

@@ -14,7 +14,10 @@
 // Replaces the J^T J / J^T r products and the LSMR operator inside scipy's TRF (sfm_lite/sfm.py:266-268).
 
 constexpr int FREC = 22;    // doubles per observation record
-constexpr int FG = 4;       // lanes cooperating on one slot
+#ifndef B200BA_FG
+#define B200BA_FG 2
+#endif
+constexpr int FG = B200BA_FG;  // lanes cooperating on one slot (2 or 4)
 constexpr int DPART = 40;   // doubles per self-slot partial: N (21) | diag U (6) | g_c (6) | b_c (6) | pad
 
 __device__ __forceinline__ void store_record(double* __restrict__ rec, const double* Jc, const double* Jp,
@@ -56,6 +59,35 @@ __device__ __forceinline__ void group_reduce_scatter(const double* acc, double* 
     const double mine = hi ? h[H / 2 + k] : h[k];
     const double give = hi ? h[k] : h[H / 2 + k];
     out[k] = mine + __shfl_xor_sync(FULL, give, 2);
+  }
+}
+
+// Sum the NV accumulators of a slot over its FG lanes and store the partial: every lane writes NV / FG consecutive values.
+template <int NV>
+__device__ __forceinline__ void slot_reduce_store(const double* acc, double* __restrict__ dst, int g, bool active) {
+  if constexpr (FG == 4) {
+    double q[NV / 4];
+    group_reduce_scatter<NV / 2>(acc, q, g);
+    if (active) {
+      double* o = dst + (NV / 4) * (((g & 1) << 1) | (g >> 1));
+#pragma unroll
+      for (int k = 0; k < NV / 4; ++k) o[k] = q[k];
+    }
+  } else {
+    static_assert(FG == 2 || FG == 4, "FG must be 2 or 4");
+    const bool odd = g & 1;
+    double q[NV / 2];
+#pragma unroll
+    for (int k = 0; k < NV / 2; ++k) {
+      const double mine = odd ? acc[NV / 2 + k] : acc[k];
+      const double give = odd ? acc[k] : acc[NV / 2 + k];
+      q[k] = mine + __shfl_xor_sync(FULL, give, 1);
+    }
+    if (active) {
+      double* o = dst + (NV / 2) * (g & 1);
+#pragma unroll
+      for (int k = 0; k < NV / 2; ++k) o[k] = q[k];
+    }
   }
 }
 
@@ -216,14 +248,7 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
 #pragma unroll
         for (int k = 0; k < 40; ++k) acc[k] = 0.0;
         self_slot_body(srec, pb.dent + ea, en, g, acc);
-        // reduce-scatter over the 4 lanes of the group: lane g ends with entries [10 g', 10 g' + 10) of the partial
-        double q10[10];
-        group_reduce_scatter<20>(acc, q10, g);
-        if (active) {
-          double* o = dpart + DPART * (int64_t)s + 10 * (((g & 1) << 1) | (g >> 1));
-#pragma unroll
-          for (int k = 0; k < 10; ++k) o[k] = q10[k];
-        }
+        slot_reduce_store<40>(acc, dpart + DPART * (int64_t)s, g, active);
       }
     }
 
@@ -238,13 +263,7 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
 #pragma unroll
         for (int k = 0; k < 36; ++k) acc[k] = 0.0;
         pair_slot_body(srec, pb.tent + ea, en, g, acc);
-        double q9[9];
-        group_reduce_scatter<18>(acc, q9, g);
-        if (active) {
-          double* o = spart + 36 * (int64_t)s + 9 * (((g & 1) << 1) | (g >> 1));
-#pragma unroll
-          for (int k = 0; k < 9; ++k) o[k] = q9[k];
-        }
+        slot_reduce_store<36>(acc, spart + 36 * (int64_t)s, g, active);
       }
     }
     __syncthreads();  // the next tile overwrites the records

@@ -73,6 +73,21 @@ int partial_capacity(const Handle* h) {
   return std::max(std::max(point_grid(h), obs_grid(h)), fused_grid(h));
 }
 
+// profiling helper: time the launches between begin() and end() with CUDA events on the library stream
+struct KernelTimer {
+  Handle* h; bool on;
+  explicit KernelTimer(Handle* h_) : h(h_), on(h_->profile) {}
+  void begin() { if (on) cudaEventRecord(h->ev0, h->stream); }
+  void end(double* acc) {
+    if (!on) return;
+    cudaEventRecord(h->ev1, h->stream);
+    cudaEventSynchronize(h->ev1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    *acc += ms;
+  }
+};
+
 void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* x_out, double* camprep) {
   const int C = (int)h->pb.C;
   if (C == 0) return;
@@ -91,26 +106,14 @@ void launch_residual(Handle* h, const double* x, const double* camprep, double* 
 
 void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp) {
   if (h->pb.N == 0) return;
+  KernelTimer t(h);
+  t.begin();
   k_jacobian<<<cdiv(h->pb.N, JT), JT, 0, h->stream>>>(h->pb, x, camprep, r_out, Jc, Jp);
+  t.end(&h->st.ms_jacobian);
   h->st.launches += 1;
 }
 
 // residual + Jacobian blocks + J^T J / J^T r blocks + point-block Schur elimination at x (camprep must match x)
-// profiling helper: time the launches between begin() and end() with CUDA events on the library stream
-struct KernelTimer {
-  Handle* h; bool on;
-  explicit KernelTimer(Handle* h_) : h(h_), on(h_->profile) {}
-  void begin() { if (on) cudaEventRecord(h->ev0, h->stream); }
-  void end(double* acc) {
-    if (!on) return;
-    cudaEventRecord(h->ev1, h->stream);
-    cudaEventSynchronize(h->ev1);
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
-    *acc += ms;
-  }
-};
-
 void launch_linearize(Handle* h, const double* x, double lambda) {
   Problem& pb = h->pb;
   Work& w = h->w;
@@ -232,7 +235,9 @@ void launch_densify(Handle* h, double* dense) {
 
 // measured FP64 FMA throughput of the device in TFLOP/s (best of 5 timed launches after a warm-up)
 double measure_fp64_peak(Handle* h) {
-  const int iters = 4096, blocks = h->sm_count * 8, threads = 256;
+  const char* e_bps = getenv("B200BA_PEAK_BLOCKS_PER_SM");  // occupancy experiments (default: 8 x 256 threads = full)
+  const int bps = (e_bps && atoi(e_bps) > 0) ? atoi(e_bps) : 8;
+  const int iters = 4096, blocks = h->sm_count * bps, threads = 256;
   float best = 1e30f;
   for (int rep = 0; rep < 6; ++rep) {
     cudaEventRecord(h->ev0, h->stream);
