@@ -326,6 +326,130 @@ __global__ void __launch_bounds__(CH_T) k_cholesky(int n, double* __restrict__ A
   if (tid == 0) { scal[S_SOLVE_FAIL] = 0.0; scal[S_DC_RES] = 0.0; scal[S_PCG_ITERS] = 0.0; }
 }
 
+// ------------------------------------------------------------------ blocked dense Cholesky, n <= 768 (C <= 128)
+// One CTA; the current 32-column panel lives in shared memory (row stride 33: conflict-free column walks).  Per panel:
+// factor in shared memory, forward-substitute the right-hand side with it, write L back, rank-32 update of the
+// trailing matrix in global memory.  The backward substitution reloads the panels in reverse order.  Replaces the
+// column-at-a-time kernel (every column step paid global-memory latency) for the small real problems (SceauxCastle:
+// n <= 54) and config B (n = 294).
+constexpr int CHB_NB = 32;
+constexpr int CHB_LD = CHB_NB + 1;
+constexpr int CHB_MAX_N = 768;
+constexpr int CHB_T = 1024;
+constexpr int CHB_SMEM = (CHB_MAX_N * CHB_LD + CHB_MAX_N) * 8;
+
+__global__ void __launch_bounds__(CHB_T) k_cholesky_blocked(int n, double* __restrict__ A, const double* __restrict__ b,
+                                                           double* __restrict__ x, double* __restrict__ scal) {
+  extern __shared__ double chb[];
+  double* P = chb;                         // [m][CHB_LD]
+  double* y = chb + CHB_MAX_N * CHB_LD;    // [n]
+  __shared__ int s_fail;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) s_fail = 0;
+  for (int i = tid; i < n; i += CHB_T) y[i] = b[i];
+  __syncthreads();
+  for (int k0 = 0; k0 < n; k0 += CHB_NB) {
+    const int nb = min(CHB_NB, n - k0), m = n - k0;
+    for (int idx = tid; idx < m * nb; idx += CHB_T) {
+      const int j = idx / m, i = idx - j * m;
+      P[i * CHB_LD + j] = A[(int64_t)(k0 + j) * n + k0 + i];
+    }
+    __syncthreads();
+    // ---- panel factorisation
+    for (int j = 0; j < nb; ++j) {
+      if (tid == 0) {
+        const double d = P[j * CHB_LD + j];
+        if (!(d > 0.0) || !(d < 1e300)) s_fail = 1;
+        P[j * CHB_LD + j] = sqrt(d > 0.0 ? d : 1.0);
+      }
+      __syncthreads();
+      if (s_fail) break;
+      const double inv = 1.0 / P[j * CHB_LD + j];
+      for (int i = j + 1 + tid; i < m; i += CHB_T) P[i * CHB_LD + j] *= inv;
+      __syncthreads();
+      const int mr = m - j - 1, nc = nb - j - 1;
+      for (int idx = tid; idx < mr * nc; idx += CHB_T) {
+        const int c = j + 1 + idx / mr, i = j + 1 + idx % mr;
+        if (i >= c) P[i * CHB_LD + c] -= P[i * CHB_LD + j] * P[c * CHB_LD + j];
+      }
+      __syncthreads();
+    }
+    if (s_fail) break;
+    // ---- forward substitution with this panel: triangle by warp 0 (lane per row), the rows below by everybody
+    if (wid == 0) {
+      double yi = lane < nb ? y[k0 + lane] : 0.0;
+      const double invd = 1.0 / P[(lane < nb ? lane : 0) * CHB_LD + (lane < nb ? lane : 0)];
+      for (int j = 0; j < nb; ++j) {
+        double yj = yi * invd;
+        yj = __shfl_sync(FULL, yj, j);
+        if (lane == j) yi = yj;
+        else if (lane > j && lane < nb) yi -= P[lane * CHB_LD + j] * yj;
+      }
+      if (lane < nb) y[k0 + lane] = yi;
+    }
+    __syncthreads();
+    for (int i = nb + tid; i < m; i += CHB_T) {
+      double t = y[k0 + i];
+      for (int j = 0; j < nb; ++j) t -= P[i * CHB_LD + j] * y[k0 + j];
+      y[k0 + i] = t;
+    }
+    // ---- write L back, rank-nb update of the trailing lower triangle
+    for (int idx = tid; idx < m * nb; idx += CHB_T) {
+      const int j = idx / m, i = idx - j * m;
+      if (i >= j) A[(int64_t)(k0 + j) * n + k0 + i] = P[i * CHB_LD + j];
+    }
+    const int mt = m - nb;
+    for (int64_t idx = tid; idx < (int64_t)mt * mt; idx += CHB_T) {
+      const int c = nb + (int)(idx / mt), i = nb + (int)(idx % mt);
+      if (i < c) continue;
+      double t = 0.0;
+#pragma unroll 8
+      for (int j = 0; j < CHB_NB; ++j) t += (j < nb) ? P[i * CHB_LD + j] * P[c * CHB_LD + j] : 0.0;
+      A[(int64_t)(k0 + c) * n + k0 + i] -= t;
+    }
+    __syncthreads();
+  }
+  if (s_fail) {
+    for (int i = tid; i < n; i += CHB_T) x[i] = 0.0;
+    if (tid == 0) { scal[S_SOLVE_FAIL] = 1.0; scal[S_DC_RES] = 0.0; scal[S_PCG_ITERS] = 0.0; }
+    return;
+  }
+  // ---- backward substitution L^T x = y, panels in reverse order (y becomes x in place)
+  const int last = ((n - 1) / CHB_NB) * CHB_NB;
+  for (int k0 = last; k0 >= 0; k0 -= CHB_NB) {
+    const int nb = min(CHB_NB, n - k0), m = n - k0;
+    __syncthreads();
+    for (int idx = tid; idx < m * nb; idx += CHB_T) {
+      const int j = idx / m, i = idx - j * m;
+      P[i * CHB_LD + j] = (i >= j) ? A[(int64_t)(k0 + j) * n + k0 + i] : 0.0;
+    }
+    __syncthreads();
+    // t_j = y_j - sum_{i >= nb} L[i][j] x_i : warp w handles columns w, w + 32, ... (nb <= 32: one each)
+    if (wid < nb) {
+      const int j = wid;
+      double t = 0.0;
+      for (int i = nb + lane; i < m; i += 32) t += P[i * CHB_LD + j] * y[k0 + i];
+      t = warp_sum(t);
+      if (lane == 0) y[k0 + j] -= t;
+    }
+    __syncthreads();
+    if (wid == 0) {
+      double xi = lane < nb ? y[k0 + lane] : 0.0;
+      const double invd = 1.0 / P[(lane < nb ? lane : 0) * CHB_LD + (lane < nb ? lane : 0)];
+      for (int j = nb - 1; j >= 0; --j) {
+        double xj = xi * invd;
+        xj = __shfl_sync(FULL, xj, j);
+        if (lane == j) xi = xj;
+        else if (lane < j) xi -= P[j * CHB_LD + lane] * xj;   // L^T[lane][j] = L[j][lane]
+      }
+      if (lane < nb) y[k0 + lane] = xi;
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += CHB_T) x[i] = y[i];
+  if (tid == 0) { scal[S_SOLVE_FAIL] = 0.0; scal[S_DC_RES] = 0.0; scal[S_PCG_ITERS] = 0.0; }
+}
+
 }  // namespace
 
 int pcg_grid(Handle* h) {
@@ -359,7 +483,13 @@ int launch_cholesky(Handle* h) {
   const int n = (int)(6 * h->pb.C);
   if (!w.dense) return fail(h, B200BA_BAD_ARG, "dense Cholesky needs n_cam <= 512");
   launch_densify(h, w.dense);
-  k_cholesky<<<1, CH_T, n * sizeof(double), h->stream>>>(n, w.dense, w.b, w.dc, w.scal);
+  if (n <= CHB_MAX_N) {
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(k_cholesky_blocked, cudaFuncAttributeMaxDynamicSharedMemorySize, CHB_SMEM); attr = true; }
+    k_cholesky_blocked<<<1, CHB_T, CHB_SMEM, h->stream>>>(n, w.dense, w.b, w.dc, w.scal);
+  } else {
+    k_cholesky<<<1, CH_T, n * sizeof(double), h->stream>>>(n, w.dense, w.b, w.dc, w.scal);
+  }
   h->st.launches += 1;
   BA_CUDA(h, cudaGetLastError());
   return 0;
