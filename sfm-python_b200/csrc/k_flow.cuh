@@ -34,7 +34,8 @@ struct FlowSmem {
   static constexpr int CTR = INFO + 2 * 64;                                  // q_next, doneA[2], doneBC[2], error
   static constexpr int RED = CTR + 8 * 4;                                    // [2][FLOW_MAX_WT][2] doubles: (sum r^2, max |g_p|)
   static constexpr int TSUM = RED + 2 * FLOW_MAX_WT * 2 * 8;                 // [64][2] doubles: tile sums, ring by k % 64
-  static constexpr int TOTAL = TSUM + 64 * 2 * 8;
+  static constexpr int WST = TSUM + 64 * 2 * 8;                              // [FLOW_WARPS][4] int4: per-warp walk state
+  static constexpr int TOTAL = WST + FLOW_WARPS * 64;
 };
 static_assert(FlowSmem::TOTAL <= 232448, "dataflow kernel shared memory exceeds the 227 KB opt-in limit");
 
@@ -363,9 +364,16 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
   // finds its dependency already satisfied.
   int s = -1, base = 0, n0 = 0, n1 = 0;                  // current step, first queue index, item counts of its two halves
   const int4 zero4 = make_int4(0, 0, 0, 0);
-  int4 ie = zero4, io = zero4;                           // tile_info[.][0] of the even / odd tile of the current pair
-  // the pair after the current one, loaded one pair ahead so that the walk never waits on global memory
-  int4 ie_n = K > 0 ? pb.tile_info[4 * tile_of(0)] : zero4, io_n = K > 1 ? pb.tile_info[4 * tile_of(1)] : zero4;
+  // per-warp walk state in shared memory (keeps 16 registers free for the item bodies): [0] / [1] = tile_info[.][0] of
+  // the even / odd tile of the current pair, [2] / [3] = the pair after it, loaded one pair ahead so that the walk
+  // never waits on global memory
+  int4* wst = reinterpret_cast<int4*>(fsm + FlowSmem::WST) + 4 * wid;
+  if (lane == 0) {
+    wst[0] = zero4; wst[1] = zero4;
+    wst[2] = K > 0 ? pb.tile_info[4 * tile_of(0)] : zero4;
+    wst[3] = K > 1 ? pb.tile_info[4 * tile_of(1)] : zero4;
+  }
+  __syncwarp();
   // cumulative completion targets per buffer parity (A targets count the items plus the finisher's extra signal)
   int cumA0 = 0, cumA1 = 0, cumBC0 = 0, cumBC1 = 0, prevBC0 = 0, prevBC1 = 0;
   const int n_steps = 2 * ((K + 1) / 2);
@@ -383,16 +391,21 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       if (s >= n_steps) { done = true; break; }
       const int m = s >> 1;
       if (!(s & 1)) {
-        ie = ie_n;
-        io = io_n;
-        ie_n = (2 * m + 2 < K) ? pb.tile_info[4 * tile_of(2 * m + 2)] : zero4;
-        io_n = (2 * m + 3 < K) ? pb.tile_info[4 * tile_of(2 * m + 3)] : zero4;
-        n0 = ie.x;
-        n1 = io.x;
+        __syncwarp();
+        if (lane == 0) {
+          wst[0] = wst[2];
+          wst[1] = wst[3];
+          wst[2] = (2 * m + 2 < K) ? pb.tile_info[4 * tile_of(2 * m + 2)] : zero4;
+          wst[3] = (2 * m + 3 < K) ? pb.tile_info[4 * tile_of(2 * m + 3)] : zero4;
+        }
+        __syncwarp();
+        n0 = wst[0].x;
+        n1 = wst[1].x;
         prevBC0 = cumBC0; prevBC1 = cumBC1;
         cumA0 += n0 + 1;
         cumA1 += n1 > 0 ? n1 + 1 : 0;
       } else {
+        const int4 ie = wst[0], io = wst[1];
         n0 = (ie.y + FLOW_SPI - 1) / FLOW_SPI + (ie.z + FLOW_SPI - 1) / FLOW_SPI;
         n1 = (io.y + FLOW_SPI - 1) / FLOW_SPI + (io.z + FLOW_SPI - 1) / FLOW_SPI;
         cumBC0 += n0;
@@ -406,7 +419,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       ok = (r < n0) ? do_A(2 * m, r, n0, cumA0, prevBC0) : do_A(2 * m + 1, r - n0, n1, cumA1, prevBC1);
     } else {
       const bool even = r < n0;
-      const int4 ii = even ? ie : io;
+      const int4 ii = wst[even ? 0 : 1];
       const int kk = even ? 2 * m : 2 * m + 1, rr = even ? r : r - n0;
       const int tA = even ? cumA0 : cumA1, tBC = even ? cumBC0 : cumBC1;
       if (ii.w & 1) ok = do_BC(std::true_type{}, kk, rr, ii, tA, tBC);
