@@ -312,8 +312,13 @@ def run_b200(a, rank, world, local_rank):
     # ---- e2e: the public host API with host buffers; every step uploads the problem and x0, solves, downloads x
     e2e_iters = 5
     def e2e_step():
+        t0 = time.perf_counter()
         eng.set_problem(n_cam, hi - lo, ci_h, pi_h, uv_h, pb.K)
+        t1 = time.perf_counter()
         x, r = eng.solve(x0_h, ftol=1e-10, fixed_iters=e2e_iters, solver=solver)
+        if os.environ.get("B200BA_SETUP_PROF"):
+            print(f"[e2e] set_problem {1e3 * (t1 - t0):.1f} ms, solve {1e3 * (time.perf_counter() - t1):.1f} ms "
+                  f"(device {r.solve_ms:.1f} ms)", file=sys.stderr)
         return r
     e2e_step()
     barrier()
@@ -349,7 +354,8 @@ def run_b200(a, rank, world, local_rank):
     # algorithmic flops: 350 per observation + per point [3x3 factor 40 + 120 k + 216 k (k + 1) / 2]
     lin_flops = 350.0 * n_loc + float(np.sum(40.0 + 120.0 * kdeg + 108.0 * kdeg * (kdeg + 1.0)))
     if fused:
-        dom, dom_name = "ms_lin_fused", "k_lin_fused"
+        dom = "ms_lin_fused"
+        dom_name = "k_lin_flow" if os.environ.get("B200BA_FLOW", "1") != "0" else "k_lin_fused"
         alg = {"ms_lin_fused": lin_bytes}
     else:
         alg = {"ms_linearize_points": 24 * n_loc + 24 * p_loc + 192 * n_cam + (144 + 32) * n_loc + (96 + 24) * p_loc,

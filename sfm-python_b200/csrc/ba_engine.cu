@@ -28,13 +28,24 @@ int cuda_fail(Handle* h, cudaError_t e, const char* where) {
   return fail(h, e == cudaErrorMemoryAllocation ? B200BA_OOM : B200BA_CUDA, m);
 }
 
-void* dalloc(Handle* h, size_t bytes) {
+void* pool_alloc(Handle* h, size_t bytes) {
   void* p = nullptr;
+  cudaError_t e = h->pool ? cudaMallocFromPoolAsync(&p, bytes, h->pool, h->stream) : cudaMalloc(&p, bytes);
+  if (e != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+
+void pool_free(Handle* h, void* p) {
+  if (!p) return;
+  if (h->pool) cudaFreeAsync(p, h->stream);
+  else cudaFree(p);
+}
+
+void* dalloc(Handle* h, size_t bytes) {
   bytes = std::max<size_t>(bytes, 256);
-  cudaError_t e = cudaMalloc(&p, bytes);
-  if (e != cudaSuccess) {
-    cudaGetLastError();
-    h->err = "out of device memory (cudaMalloc of " + std::to_string(bytes) + " bytes failed)";
+  void* p = pool_alloc(h, bytes);
+  if (!p) {
+    h->err = "out of device memory (allocation of " + std::to_string(bytes) + " bytes failed)";
     return nullptr;
   }
   h->allocs.push_back(p);
@@ -43,7 +54,7 @@ void* dalloc(Handle* h, size_t bytes) {
 }
 
 void free_problem(Handle* h) {
-  for (void* p : h->allocs) cudaFree(p);
+  for (void* p : h->allocs) pool_free(h, p);
   h->allocs.clear();
   h->bytes_device = 0;
   h->pb = Problem();

@@ -156,6 +156,7 @@ struct Handle {
   int device = 0;
   int sm_count = 148;
   cudaStream_t stream = nullptr;
+  cudaMemPool_t pool = nullptr;   // stream-ordered pool that keeps freed blocks: re-running set_problem costs no cudaMalloc
   std::string err;
   bool has_problem = false;
   Problem pb;
@@ -176,6 +177,8 @@ struct Handle {
 int fail(Handle* h, int code, const std::string& msg);
 int cuda_fail(Handle* h, cudaError_t e, const char* where);
 void* dalloc(Handle* h, size_t bytes);  // nullptr on failure (h->err set)
+void* pool_alloc(Handle* h, size_t bytes);  // raw stream-ordered allocation from h->pool (nullptr on failure)
+void pool_free(Handle* h, void* p);
 void free_problem(Handle* h);
 #define BA_CUDA(h, call)                                             \
   do {                                                               \

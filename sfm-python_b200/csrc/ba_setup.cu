@@ -3,6 +3,7 @@
 // point-major SoA observations, per-point CSR, warp tiles, camera-sorted permutation + chunks,
 // and the Schur pair-entry list sorted by reduced-camera-system block (atomics-free accumulation).
 // One-off per problem; CUB sort/scan/run-length are used here (not on the per-iteration path).
+#include <chrono>
 #include <algorithm>
 #include <cub/cub.cuh>
 
@@ -303,13 +304,14 @@ int upload(Handle* h, T** dst, const std::vector<T>& src) {
   return 0;
 }
 
-struct Tmp {  // scratch freed at the end of setup
+struct Tmp {  // scratch freed (stream-ordered, back into the handle's pool) at the end of setup
+  Handle* h;
   std::vector<void*> p;
-  ~Tmp() { for (void* q : p) cudaFree(q); }
+  explicit Tmp(Handle* hh) : h(hh) {}
+  ~Tmp() { for (void* q : p) pool_free(h, q); }
   void* get(size_t bytes) {
-    void* q = nullptr;
-    if (cudaMalloc(&q, std::max<size_t>(bytes, 16)) != cudaSuccess) return nullptr;
-    p.push_back(q);
+    void* q = pool_alloc(h, std::max<size_t>(bytes, 16));
+    if (q) p.push_back(q);
     return q;
   }
 };
@@ -411,8 +413,18 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   pb.C = C; pb.P = P; pb.N = N;
   pb.Cs = (C + 1) & ~(int64_t)1;
   for (int i = 0; i < 9; ++i) pb.K.k[i] = K[i];
-  Tmp tmp;
+  Tmp tmp(h);
   const int T = 256;
+  // B200BA_SETUP_PROF=1: wall time of every setup phase to stderr (each mark synchronises the stream)
+  const bool prof = getenv("B200BA_SETUP_PROF") && atoi(getenv("B200BA_SETUP_PROF"));
+  auto t_prev = std::chrono::steady_clock::now();
+  auto mark = [&](const char* what) {
+    if (!prof) return;
+    cudaStreamSynchronize(st);
+    auto t = std::chrono::steady_clock::now();
+    fprintf(stderr, "[b200ba setup] %-28s %9.3f ms\n", what, std::chrono::duration<double, std::milli>(t - t_prev).count());
+    t_prev = t;
+  };
 
   // ---- 1. raw inputs to the device, range / order check, int32 indices
   TMP_ALLOC(d_cam64, int64_t, N);
@@ -434,6 +446,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   BA_CUDA(h, cudaStreamSynchronize(st));
   if (flags & 1) return fail(h, B200BA_INDEX_RANGE, "camera or point index out of range");
 
+  mark("1 upload+check");
   // ---- 2. point-major order (stable); identity when the input is already sorted (graph.py:186-191)
   DEV_ALLOC(pb.u, double, N + 2);  // + slack for 16-byte aligned prefetch windows
   DEV_ALLOC(pb.v, double, N + 2);
@@ -457,6 +470,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     k_offsets<<<nblk(N, T), T, 0, st>>>(N, (int)P, pb.pt, pb.pt_off);
   }
 
+  mark("2 point-major order");
   // ---- 3. warp tiles (host greedy packing of whole points into <= 32 observations)
   std::vector<int> h_pt_off(P + 1, 0), h_pt_tile;
   BA_CUDA(h, cudaMemcpyAsync(h_pt_off.data(), pb.pt_off, (P + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -516,6 +530,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     }
   }
 
+  mark("3 warp/CTA tiles (host)");
   // ---- 4. camera-sorted permutation and chunks
   DEV_ALLOC(pb.cperm, int, N);
   DEV_ALLOC(pb.cam_off, int, C + 1);
@@ -551,6 +566,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.cam_choff, coff)) return rc;
   }
 
+  mark("4 camera permutation");
   // ---- 5. Schur pair entries sorted by key: [tile *] C*C + cam_i * C + cam_j  (cam_i <= cam_j)
   const long long CC = (long long)C * C;
   int* d_pt_tile = nullptr;
@@ -638,6 +654,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     }
   }
 
+  mark("5 pair entries");
   // ---- 6. global block structure: union over ranks of the local keys + every diagonal block
   if (h->nranks > 1) {
     long long my_n = (long long)keys_host.size();
@@ -680,6 +697,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     BA_CUDA(h, cudaStreamSynchronize(st));
   }
 
+  mark("6 block structure");
   // ---- 7. host: block coordinates, Schur chunks, full BSR view
   {
     std::vector<int> br(n_blk), bc(n_blk), diag(C, -1), sb, sa, se, choff(n_blk + 1, 0);
@@ -718,6 +736,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.bsr_col, col)) return rc;
     if (int rc = upload(h, &pb.bsr_src, src)) return rc;
   }
+  mark("7 host BSR");
   // ---- 8. tile mode: pair slots = (tile, block) cells ordered inside each tile by decreasing entry count,
   //         per-block reduce lists, entries packed to tile-local 16-bit indices
   if (pb.schur_tiles) {
@@ -733,6 +752,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       k_tile_ent_off<<<nblk(pb.n_st + 1, T), T, 0, st>>>(pb.n_st, (int)n_ent, d_keys_sorted, CC, pb.tile_ent_off);
     }
   }
+  mark("8 pair slots");
   // ---- 9. fused kernel: self slots = the observations of one camera inside one tile
   if (pb.fused) {
     DEV_ALLOC(pb.dent, unsigned short, N);
@@ -765,6 +785,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = build_slots(h, tmp, n_cell, d_dcell, d_dcnt, (long long)C, nullptr, (int)C, pb.n_st, &sl)) return rc;
     pb.n_dslot = sl.n_slot; pb.dslot_a = sl.slot_a; pb.dslot_n = sl.slot_n;
     pb.tile_dslot_off = sl.tile_off; pb.cam_dslot_off = sl.grp_off; pb.cam_dslots = sl.grp_slots;
+    mark("9 self slots");
     // ---- 10. dataflow kernel: per-tile info + contiguous metadata blobs (bulk-copied to shared memory per tile)
     const char* e_flow = getenv("B200BA_FLOW");
     if (pb.tile_obs <= FLOW_TILE && !(e_flow && atoi(e_flow) == 0) && pb.n_st > 0) {
@@ -787,6 +808,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       pb.flow = true;
     }
   }
+  mark("10 dataflow blobs");
   BA_CUDA(h, cudaStreamSynchronize(st));
   BA_CUDA(h, cudaGetLastError());
   h->st.schur_entries = pb.n_ent;
