@@ -126,6 +126,15 @@ int comm_allgather_i64(Handle* h, const long long* send, long long* recv, int64_
   return rc ? nccl_fail(h, rc, "ncclAllGather") : 0;
 }
 
+int comm_allgather_f64(Handle* h, const double* send, double* recv, int64_t count) {
+  if (h->nranks <= 1) {
+    cudaMemcpyAsync(recv, send, count * sizeof(double), cudaMemcpyDeviceToDevice, h->stream);
+    return 0;
+  }
+  int rc = g_nccl.AllGather(send, recv, (size_t)count, NCCL_DOUBLE, h->comm, h->stream);
+  return rc ? nccl_fail(h, rc, "ncclAllGather") : 0;
+}
+
 // ------------------------------------------------------------------ per-problem work buffers
 static int alloc_work(Handle* h) {
   Problem& pb = h->pb;
@@ -154,6 +163,11 @@ static int alloc_work(Handle* h) {
   w.gc = w.b + 6 * C;
   w.udiag = w.gc + 6 * C;
   w.sums = w.udiag + 6 * C;
+  if (pb.xchg) {
+    WALLOC(w.xsend, pb.x_stride);
+    WALLOC(w.xrecv, pb.x_stride * h->nranks);
+    BA_CUDA(h, cudaMemsetAsync(w.xsend, 0, (size_t)pb.x_stride * sizeof(double), h->stream));
+  }
   WALLOC(w.scal, NSCAL);
   w.n_part = partial_capacity(h);
   WALLOC(w.part, (int64_t)w.n_part * 8);
@@ -194,8 +208,13 @@ int linearize_all(Handle* h, double lambda) {
   launch_linearize(h, w.x, lambda);
   {
     PhaseTimer t(h, &h->st.ms_allreduce);
-    if (int rc = comm_allreduce_sum(h, w.comm, w.comm_count)) return rc;
-    if (int rc = comm_allreduce_max(h, w.scal + S_GPMAX, 1)) return rc;
+    if (h->pb.xchg) {
+      if (int rc = comm_allgather_f64(h, w.xsend, w.xrecv, h->pb.x_stride)) return rc;
+      launch_xchg_sum(h);
+    } else {
+      if (int rc = comm_allreduce_sum(h, w.comm, w.comm_count)) return rc;
+      if (int rc = comm_allreduce_max(h, w.scal + S_GPMAX, 1)) return rc;
+    }
   }
   launch_fix_diag(h);
   return 0;

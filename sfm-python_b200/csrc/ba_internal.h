@@ -109,6 +109,14 @@ struct Problem {
   int* cam_dslots = nullptr;     // [n_dslot]
   // dataflow kernel: per-tile info (4 x int4) and one contiguous metadata blob per tile (16-byte units)
   bool flow = false;
+  // sparse exchange of the reduced system (nranks > 1): every rank sends only the blocks of S it has contributions to
+  // (all-gather), then every rank sums the contributions of each block in rank order (identical bits everywhere)
+  bool xchg = false;
+  int xl_n = 0, xl_max = 0;          // local blocks of this rank, max over ranks
+  int* xl_blk = nullptr;             // [xl_n] union index of every local block (ascending)
+  int* xc_off = nullptr;             // [n_blk+1] contributions of every union block ...
+  long long* xc_src = nullptr;       // ... as offsets into the gathered buffer, ascending rank
+  long long x_stride = 0;            // doubles per rank in the gathered buffer: [xl_max*36 | b | g_c | diag U | sums | gpmax]
   int4* tile_info = nullptr;     // [n_st*4] {nA, n_pslot, n_dslot, flags} {blob_off16, blob_units16, cmin, cspan}
                                  //           {obs0, n_obs, wt0, n_pent} {pslot_base, dslot_base, pt0, n_pts}
   uint4* blob = nullptr;         // header(32 B) | pair slots (a, n) | self slots (a, n) | pair entries u32 | self entries u16
@@ -131,6 +139,8 @@ struct Work {
   double* cpart = nullptr;    // [n_cch*33]
   double* spart = nullptr;    // [n_sch*36]
   double* U = nullptr;        // [C*21]
+  double* xsend = nullptr;    // [x_stride] sparse exchange: this rank's blocks + camera vectors + scalars
+  double* xrecv = nullptr;    // [nranks * x_stride]
   double* dpart = nullptr;    // [n_dslot*40] self-slot partials of the fused kernel
   double* camsum = nullptr;   // [C*40] per-camera sums of the self-slot partials
   // ---- contiguous all-reduce buffer: Sup | b | gc | udiag | sums
@@ -190,6 +200,7 @@ void free_problem(Handle* h);
 int comm_allreduce_sum(Handle* h, double* buf, int64_t count);
 int comm_allreduce_max(Handle* h, double* buf, int64_t count);
 int comm_allgather_i64(Handle* h, const long long* send, long long* recv, int64_t count);
+int comm_allgather_f64(Handle* h, const double* send, double* recv, int64_t count);
 
 // ---- ba_setup.cu
 int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam_idx, const int64_t* pt_idx,
@@ -201,6 +212,7 @@ void launch_cam_prep(Handle* h, const double* x_cams, const double* dc /*nullabl
 void launch_residual(Handle* h, const double* x, const double* camprep, double* r_out /*nullable, caller order*/,
                      int scal_slot);
 void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp);
+void launch_xchg_sum(Handle* h);  // sparse exchange: gathered per-rank contributions -> Sup, b, gc, udiag, cost, gpmax
 void launch_linearize(Handle* h, const double* x, double lambda);  // points + cameras + schur -> Sup, b, gc, ...
 void launch_fix_diag(Handle* h);
 void launch_backsub_trial(Handle* h, double lambda);

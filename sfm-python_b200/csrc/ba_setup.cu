@@ -656,21 +656,41 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
 
   mark("5 pair entries");
   // ---- 6. global block structure: union over ranks of the local keys + every diagonal block
+  std::vector<long long> x_all;       // every rank's local block keys (sparse exchange), padded to x_mx per rank
+  std::vector<long long> x_counts;
+  long long x_mx = 0;
+  bool x_ok = false;
   if (h->nranks > 1) {
-    long long my_n = (long long)keys_host.size();
-    TMP_ALLOC(d_n, long long, h->nranks + 1);
-    BA_CUDA(h, cudaMemcpyAsync(d_n + h->nranks, &my_n, sizeof(long long), cudaMemcpyHostToDevice, st));
-    if (int rc = comm_allgather_i64(h, d_n + h->nranks, d_n, 1)) return rc;
-    std::vector<long long> counts(h->nranks);
-    BA_CUDA(h, cudaMemcpyAsync(counts.data(), d_n, h->nranks * sizeof(long long), cudaMemcpyDeviceToHost, st));
+    // sparse exchange needs the fused reducers on every rank; local blocks then include the diagonal blocks of the
+    // cameras this rank observes (self-slot contributions)
+    const char* e_x = getenv("B200BA_XCHG");  // 0: always all-reduce, 1: always sparse exchange (when possible)
+    const bool want_x = pb.fused && pb.schur_tiles && !(e_x && atoi(e_x) == 0);
+    if (want_x) {
+      std::vector<int> h_cam_off(C + 1, 0);
+      BA_CUDA(h, cudaMemcpyAsync(h_cam_off.data(), pb.cam_off, (C + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
+      BA_CUDA(h, cudaStreamSynchronize(st));
+      for (int64_t c = 0; c < C; ++c)
+        if (h_cam_off[c + 1] > h_cam_off[c]) keys_host.push_back((long long)c * C + c);
+      std::sort(keys_host.begin(), keys_host.end());
+      keys_host.erase(std::unique(keys_host.begin(), keys_host.end()), keys_host.end());
+    }
+    long long my_n[2] = {(long long)keys_host.size(), want_x ? 1 : 0};
+    TMP_ALLOC(d_n, long long, 2 * (h->nranks + 1));
+    BA_CUDA(h, cudaMemcpyAsync(d_n + 2 * h->nranks, my_n, 2 * sizeof(long long), cudaMemcpyHostToDevice, st));
+    if (int rc = comm_allgather_i64(h, d_n + 2 * h->nranks, d_n, 2)) return rc;
+    std::vector<long long> cnt2(2 * h->nranks);
+    BA_CUDA(h, cudaMemcpyAsync(cnt2.data(), d_n, 2 * h->nranks * sizeof(long long), cudaMemcpyDeviceToHost, st));
     BA_CUDA(h, cudaStreamSynchronize(st));
+    std::vector<long long> counts(h->nranks);
+    x_ok = true;
+    for (int r = 0; r < h->nranks; ++r) { counts[r] = cnt2[2 * r]; x_ok = x_ok && cnt2[2 * r + 1] != 0; }
     long long mx = 1;
     for (long long c : counts) mx = std::max(mx, c);
     TMP_ALLOC(d_send, long long, mx);
     TMP_ALLOC(d_recv, long long, mx * h->nranks);
     BA_CUDA(h, cudaMemsetAsync(d_send, 0, mx * sizeof(long long), st));
-    if (my_n)
-      BA_CUDA(h, cudaMemcpyAsync(d_send, keys_host.data(), my_n * sizeof(long long), cudaMemcpyHostToDevice, st));
+    if (my_n[0])
+      BA_CUDA(h, cudaMemcpyAsync(d_send, keys_host.data(), my_n[0] * sizeof(long long), cudaMemcpyHostToDevice, st));
     if (int rc = comm_allgather_i64(h, d_send, d_recv, mx)) return rc;
     std::vector<long long> all((size_t)mx * h->nranks);
     BA_CUDA(h, cudaMemcpyAsync(all.data(), d_recv, all.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
@@ -678,12 +698,44 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     keys_host.clear();
     for (int r = 0; r < h->nranks; ++r)
       keys_host.insert(keys_host.end(), all.begin() + (size_t)r * mx, all.begin() + (size_t)r * mx + counts[r]);
+    if (x_ok) { x_all.swap(all); x_counts = counts; x_mx = mx; }
   }
   for (int64_t c = 0; c < C; ++c) keys_host.push_back((long long)c * C + c);
   std::sort(keys_host.begin(), keys_host.end());
   keys_host.erase(std::unique(keys_host.begin(), keys_host.end()), keys_host.end());
   const int n_blk = (int)keys_host.size();
   pb.n_blk = n_blk;
+  if (x_ok) {
+    // worth it when the gathered buffer (nranks x the largest local list) is smaller than what an all-reduce moves
+    // (about twice the union); the decision depends only on gathered counts, so every rank takes the same one
+    const char* e_x = getenv("B200BA_XCHG");
+    const bool force = e_x && atoi(e_x) == 1;
+    if (force || (double)x_mx * h->nranks <= 1.5 * (double)n_blk) {
+      std::vector<int> xoff(n_blk + 1, 0), mine;
+      std::vector<std::vector<int>> idx(h->nranks);
+      for (int r = 0; r < h->nranks; ++r) {
+        idx[r].resize(x_counts[r]);
+        for (long long k = 0; k < x_counts[r]; ++k) {
+          const int g = (int)(std::lower_bound(keys_host.begin(), keys_host.end(), x_all[(size_t)r * x_mx + k]) -
+                              keys_host.begin());
+          idx[r][k] = g;
+          xoff[g + 1]++;
+        }
+      }
+      for (int g = 0; g < n_blk; ++g) xoff[g + 1] += xoff[g];
+      pb.xl_max = (int)x_mx;
+      pb.xl_n = (int)x_counts[h->rank];
+      pb.x_stride = ((long long)pb.xl_max * 36 + 18 * C + S_NSUM + 1 + 1) & ~1ll;
+      std::vector<long long> xsrc(xoff[n_blk]);
+      std::vector<int> fill(xoff.begin(), xoff.end() - 1);
+      for (int r = 0; r < h->nranks; ++r)  // ascending rank inside every block: the summation order of k_xchg_sum
+        for (long long k = 0; k < x_counts[r]; ++k) xsrc[fill[idx[r][k]]++] = r * pb.x_stride + k * 36;
+      if (int rc = upload(h, &pb.xl_blk, idx[h->rank])) return rc;
+      if (int rc = upload(h, &pb.xc_off, xoff)) return rc;
+      if (int rc = upload(h, &pb.xc_src, xsrc)) return rc;
+      pb.xchg = true;
+    }
+  }
 
   // entry range of every global block in the local sorted entry list (stream mode only)
   std::vector<long long> h_blk_off(n_blk + 1, 0);

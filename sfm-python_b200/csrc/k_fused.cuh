@@ -312,13 +312,16 @@ __global__ void k_cam_sums(int C, const int* __restrict__ cam_dslot_off, const i
 }
 
 // Sup[g] = -(sum of the pair-slot partials of block g) [- N_c + lambda diag U_c on diagonal blocks]
-__global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
-                                const int* __restrict__ blk_slot_off, const int* __restrict__ blk_slots,
-                                const double* __restrict__ spart, const double* __restrict__ camsum, double lambda,
-                                double* __restrict__ Sup) {
+// blk_list == nullptr: all n_blk blocks, Sup indexed by block; else the listed blocks only, Sup indexed by list position
+// (sparse exchange: this rank's local blocks, packed)
+__global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_list, const int* __restrict__ blk_r,
+                                const int* __restrict__ blk_c, const int* __restrict__ blk_slot_off,
+                                const int* __restrict__ blk_slots, const double* __restrict__ spart,
+                                const double* __restrict__ camsum, double lambda, double* __restrict__ Sup) {
   const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (t >= (int64_t)n_blk * 36) return;
-  const int g = (int)(t / 36), e = (int)(t % 36);
+  const int e = (int)(t % 36);
+  const int g = blk_list ? blk_list[t / 36] : (int)(t / 36);
   double s = list_sum8(blk_slots, blk_slot_off[g], blk_slot_off[g + 1], spart, 36, e);
   if (blk_r[g] == blk_c[g]) {
     const int c = blk_r[g], r = e / 6, cc = e % 6;
@@ -326,4 +329,33 @@ __global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_r, const 
     if (r == cc) s -= lambda * camsum[c * DPART + 21 + r];
   }
   Sup[t] = -s;
+}
+
+// Sparse exchange, receiving side: every block of S = sum of the ranks' packed contributions in ascending rank order;
+// b, g_c, diag U and the cost = sums over ranks of the per-rank tails; max |g_p| = max over ranks.
+__global__ void k_xchg_sum(int n_blk, int C, int nranks, long long stride, long long tail_off,
+                           const int* __restrict__ xc_off, const long long* __restrict__ xc_src,
+                           const double* __restrict__ xrecv, double* __restrict__ comm, double* __restrict__ sums,
+                           double* __restrict__ scal) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t nS = (int64_t)n_blk * 36, nV = 18 * (int64_t)C;
+  if (t < nS) {
+    const int g = (int)(t / 36), e = (int)(t % 36);
+    double s = 0.0;
+    for (int q = xc_off[g]; q < xc_off[g + 1]; ++q) s += xrecv[xc_src[q] + e];
+    comm[t] = s;
+  } else if (t < nS + nV) {
+    const int64_t k = t - nS;
+    double s = 0.0;
+    for (int r = 0; r < nranks; ++r) s += xrecv[r * stride + tail_off + k];
+    comm[t] = s;
+  } else if (t == nS + nV) {
+    double s = 0.0, m = 0.0;
+    for (int r = 0; r < nranks; ++r) {
+      s += xrecv[r * stride + tail_off + nV + S_COST2];
+      m = fmax(m, xrecv[r * stride + tail_off + nV + S_NSUM]);
+    }
+    sums[S_COST2] = s;
+    scal[S_GPMAX] = m;
+  }
 }

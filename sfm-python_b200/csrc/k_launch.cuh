@@ -146,12 +146,26 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
     Slots sl{};
     sl.s[0] = S_COST2;
     sl.s[1] = S_GPMAX;
-    k_reduce_partials2<<<1, 256, 0, st>>>(fg, 1, 2, w.part, w.sums, w.scal, sl);
+    // sparse exchange: this rank's contribution goes to xsend = [local blocks | b | g_c | diag U | sums | gpmax]
+    double* xt = pb.xchg ? w.xsend + (int64_t)pb.xl_max * 36 : nullptr;
+    double* o_b = pb.xchg ? xt : w.b;
+    double* o_gc = pb.xchg ? xt + 6 * pb.C : w.gc;
+    double* o_ud = pb.xchg ? xt + 12 * pb.C : w.udiag;
+    double* o_sums = pb.xchg ? xt + 18 * pb.C : w.sums;
+    k_reduce_partials2<<<1, 256, 0, st>>>(fg, 1, 2, w.part, o_sums, w.scal, sl);
+    if (pb.xchg)
+      cudaMemcpyAsync(o_sums + S_NSUM, w.scal + S_GPMAX, sizeof(double), cudaMemcpyDeviceToDevice, st);
     t.begin();
-    k_cam_sums<<<cdiv(pb.C * 40, 128), 128, 0, st>>>((int)pb.C, pb.cam_dslot_off, pb.cam_dslots, w.dpart, w.camsum, w.udiag,
-                                                    w.gc, w.b);
-    k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 128), 128, 0, st>>>(pb.n_blk, pb.blk_r, pb.blk_c, pb.blk_slot_off,
-                                                                       pb.blk_slots, w.spart, w.camsum, lambda, w.Sup);
+    k_cam_sums<<<cdiv(pb.C * 40, 128), 128, 0, st>>>((int)pb.C, pb.cam_dslot_off, pb.cam_dslots, w.dpart, w.camsum, o_ud,
+                                                    o_gc, o_b);
+    if (pb.xchg)
+      k_slot_reduce_S<<<cdiv((int64_t)pb.xl_n * 36, 128), 128, 0, st>>>(pb.xl_n, pb.xl_blk, pb.blk_r, pb.blk_c,
+                                                                        pb.blk_slot_off, pb.blk_slots, w.spart, w.camsum,
+                                                                        lambda, w.xsend);
+    else
+      k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 128), 128, 0, st>>>(pb.n_blk, nullptr, pb.blk_r, pb.blk_c,
+                                                                         pb.blk_slot_off, pb.blk_slots, w.spart, w.camsum,
+                                                                         lambda, w.Sup);
     t.end(&h->st.ms_slot_reduce);
     h->st.launches += 4;
     h->st.n_linearize += 1;
@@ -200,6 +214,15 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
   }
   h->st.launches += 6;
   h->st.n_linearize += 1;
+}
+
+void launch_xchg_sum(Handle* h) {
+  Problem& pb = h->pb;
+  Work& w = h->w;
+  const int64_t n = (int64_t)pb.n_blk * 36 + 18 * pb.C + 1;
+  k_xchg_sum<<<cdiv(n, 256), 256, 0, h->stream>>>(pb.n_blk, (int)pb.C, h->nranks, pb.x_stride, (long long)pb.xl_max * 36,
+                                                 pb.xc_off, pb.xc_src, w.xrecv, w.comm, w.sums, w.scal);
+  h->st.launches += 1;
 }
 
 void launch_fix_diag(Handle* h) {
