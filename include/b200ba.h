@@ -90,6 +90,7 @@ typedef struct b200ba_stats {
   double ms_lin_fused, ms_slot_reduce;   /* fused linearisation + Schur kernel and its fixed-order partial reduction */
   int64_t n_tiles, n_pair_slots, n_self_slots;
   double ms_jacobian;     /* k_jacobian alone (config E sweep) */
+  int64_t n_tl_builds;    /* rebuilds of the coarse operator of the two-level PCG preconditioner */
 } b200ba_stats;
 
 int b200ba_version(void);

@@ -35,7 +35,8 @@ class Stats(C.Structure):
                [(n, C.c_int64) for n in ("launches", "n_linearize", "n_pcg_iters", "schur_entries", "schur_blocks",
                                          "bytes_device")] + \
                [(n, C.c_double) for n in ("ms_lin_fused", "ms_slot_reduce")] + \
-               [(n, C.c_int64) for n in ("n_tiles", "n_pair_slots", "n_self_slots")] + [("ms_jacobian", C.c_double)]
+               [(n, C.c_int64) for n in ("n_tiles", "n_pair_slots", "n_self_slots")] + [("ms_jacobian", C.c_double),
+                                                                                         ("n_tl_builds", C.c_int64)]
 
 
 _P = C.c_void_p

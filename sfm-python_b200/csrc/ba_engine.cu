@@ -175,6 +175,19 @@ static int alloc_work(Handle* h) {
   WALLOC(w.pcg, 6 * C * 5 + C * 36);
   WALLOC(w.pcg_part, (int64_t)2 * 4 * std::max(pcg_grid(h), 1));
   if (C <= DENSE_MAX_CAM) { WALLOC(w.dense, 36 * C * C); }
+  if (pb.tl) {
+    WALLOC(w.tl_G, C * 42);
+    WALLOC(w.tl_SP, (int64_t)pb.nnz_sp * 42);
+    WALLOC(w.tl_A, (int64_t)pb.ncp * pb.ncp);
+    WALLOC(w.tl_cb, (int64_t)pb.ncp * 32);
+    WALLOC(w.tl_rb, (int64_t)pb.ncp * 32);
+    WALLOC(w.tl_dsc, pb.ncp);
+    WALLOC(w.tl_cen, (int64_t)pb.n_agg * 3);
+    WALLOC(w.tl_rc, pb.ncp);
+    WALLOC(w.tl_zc, pb.ncp);
+    WALLOC(w.tl_uf, 6 * C);
+  }
+  h->tl_built = false; h->tl_age = 0; h->tl_ref_iters = 0; h->tl_last_iters = 0;
 #undef WALLOC
   cudaStream_t st = h->stream;
   BA_CUDA(h, cudaMemsetAsync(w.pp, 0, (size_t)std::max<int64_t>(P * 12, 1) * sizeof(double), st));
@@ -224,7 +237,27 @@ int camera_solve(Handle* h, int solver, double rtol, int max_iter) {
   PhaseTimer t(h, &h->st.ms_camera_solve);
   if (solver == B200BA_SOLVER_AUTO) solver = (h->pb.C <= 64) ? B200BA_SOLVER_CHOLESKY : B200BA_SOLVER_PCG;
   if (solver == B200BA_SOLVER_CHOLESKY) return launch_cholesky(h);
+  // Two-level preconditioner: starts once block-Jacobi needed more than TL_START iterations (far from the optimum the
+  // right-hand side has little weight in the weak modes and block-Jacobi converges in a handful); the coarse
+  // operator is rebuilt when it is TL_MAX_AGE solves old or the iteration count has grown by half since it was built.
+  // The decisions depend only on iteration counts, which are identical on every rank.
+  constexpr int TL_START = 24, TL_MAX_AGE = 8;
+  static const int tl_force = getenv("B200BA_TWOLEVEL") ? atoi(getenv("B200BA_TWOLEVEL")) : 1;  // 2: from the first solve
+  if (h->pb.tl && (h->tl_built || h->tl_last_iters > TL_START || tl_force == 2)) {
+    const bool rebuild = !h->tl_built || h->tl_age >= TL_MAX_AGE ||
+                         (h->tl_age >= 2 && h->tl_last_iters > h->tl_ref_iters + h->tl_ref_iters / 2 + 8);
+    if (int rc = launch_tl_build(h, rebuild)) return rc;
+    if (rebuild) { h->tl_built = true; h->tl_age = 0; h->st.n_tl_builds += 1; }
+    h->tl_age += 1;
+    return launch_pcg2(h, rtol, max_iter);
+  }
   return launch_pcg(h, rtol, max_iter);
+}
+
+// bookkeeping of the two-level policy after a camera solve (iters = PCG iterations it took)
+void tl_note_iters(Handle* h, int iters) {
+  h->tl_last_iters = iters;
+  if (h->tl_built && h->tl_age == 1) h->tl_ref_iters = iters;
 }
 
 // trial point: cameras x + dc -> xn, camprep_n; points by back-substitution; sums all-reduced

@@ -46,6 +46,7 @@ enum Scal {
   S_PCG_ITERS = 16,
   S_SOLVE_FAIL = 17,
   S_RES_COST2 = 18, // sum r^2 of b200ba_residuals
+  S_TL_OK = 19,     // 1 = the coarse inverse of the two-level preconditioner is valid
   S_FLOW_ERR = 31   // (int) set by k_lin_flow when a dependency wait timed out
 };
 
@@ -120,6 +121,14 @@ struct Problem {
   int4* tile_info = nullptr;     // [n_st*4] {nA, n_pslot, n_dslot, flags} {blob_off16, blob_units16, cmin, cspan}
                                  //           {obs0, n_obs, wt0, n_pent} {pslot_base, dslot_base, pt0, n_pts}
   uint4* blob = nullptr;         // header(32 B) | pair slots (a, n) | self slots (a, n) | pair entries u32 | self entries u16
+  // two-level preconditioner (k_twolevel.cuh): aggregates = contiguous camera runs, 7 coarse unknowns each
+  bool tl = false;
+  int n_agg = 0, nc = 0, ncp = 0;  // nc = 7 n_agg, ncp = nc rounded up to a multiple of 64
+  int* cam_agg = nullptr;          // [C]
+  int* agg_off = nullptr;          // [n_agg+1]
+  int* sp_rowptr = nullptr;        // [C+1] block-CSR structure of S P (6 x 7 blocks)
+  int* sp_col = nullptr;           // [nnz_sp] aggregate of each block
+  int nnz_sp = 0;
   // full (both triangles) block-CSR view for the PCG mat-vec
   int* bsr_rowptr = nullptr;  // [C+1]
   int* bsr_col = nullptr;     // [nnzb]
@@ -159,6 +168,17 @@ struct Work {
   double* pcg = nullptr;      // [6C*5 + C*36] r u p w s Minv
   double* pcg_part = nullptr; // [grid*4]
   double* dense = nullptr;    // [(6C)^2] Cholesky work (only n_cam <= DENSE_MAX_CAM)
+  // two-level preconditioner
+  double* tl_G = nullptr;     // [C*42]   G_c
+  double* tl_SP = nullptr;    // [nnz_sp*42]
+  double* tl_A = nullptr;     // [ncp*ncp] coarse matrix, inverted in place
+  double* tl_cb = nullptr;    // [ncp*32] Gauss-Jordan column panel
+  double* tl_rb = nullptr;    // [32*ncp] Gauss-Jordan row panel
+  double* tl_dsc = nullptr;   // [ncp]
+  double* tl_cen = nullptr;   // [n_agg*3]
+  double* tl_rc = nullptr;    // [ncp]
+  double* tl_zc = nullptr;    // [ncp]
+  double* tl_uf = nullptr;    // [6C]
   double* h_scal = nullptr;   // pinned host mirror [NSCAL]
 };
 
@@ -181,6 +201,11 @@ struct Handle {
   b200ba_stats st{};
   bool profile = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // two-level preconditioner state of the running solve (identical on every rank: driven by PCG iteration counts)
+  bool tl_built = false;      // G / A_c^-1 hold a coarse operator of this solve
+  int tl_age = 0;             // camera solves since the last rebuild
+  int tl_ref_iters = 0;       // PCG iterations of the first solve after the last rebuild
+  int tl_last_iters = 0;      // PCG iterations of the previous camera solve
 };
 
 // ---- helpers (ba_engine.cu)
@@ -222,6 +247,8 @@ double measure_fp64_peak(Handle* h);
 
 // ---- ba_solve.cu
 int launch_pcg(Handle* h, double rtol, int max_iter);
+int launch_tl_build(Handle* h, bool rebuild_coarse);   // SP = S P (always); G, A_c, A_c^-1 when rebuild_coarse
+int launch_pcg2(Handle* h, double rtol, int max_iter);
 int launch_cholesky(Handle* h);
 
 }  // namespace b200ba

@@ -787,6 +787,35 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.bsr_rowptr, rowptr)) return rc;
     if (int rc = upload(h, &pb.bsr_col, col)) return rc;
     if (int rc = upload(h, &pb.bsr_src, src)) return rc;
+    // two-level preconditioner (k_twolevel.cuh): aggregates = contiguous camera runs; block structure of S P
+    const char* e_tl = getenv("B200BA_TWOLEVEL");   // 0: block-Jacobi only
+    const char* e_agg = getenv("B200BA_AGG");       // cameras per aggregate (default max(16, C / 320))
+    if (C >= 128 && !(e_tl && atoi(e_tl) == 0)) {
+      int per = (int)std::max<int64_t>(16, (C + 319) / 320);
+      if (e_agg && atoi(e_agg) >= 2) per = atoi(e_agg);
+      int n_agg = (int)((C + per - 1) / per);
+      if (n_agg > 1 && C - (int64_t)(n_agg - 1) * per < 2) --n_agg;   // a one-camera aggregate has only 6 free motions
+      if ((int64_t)n_agg * 7 <= 3584) {
+        std::vector<int> cam_agg(C), agg_off(n_agg + 1), sp_rowptr(C + 1, 0), sp_col;
+        for (int64_t c = 0; c < C; ++c) cam_agg[c] = (int)std::min<int64_t>(c / per, n_agg - 1);
+        for (int I = 0; I < n_agg; ++I) agg_off[I] = I * per;
+        agg_off[n_agg] = (int)C;
+        for (int64_t c = 0; c < C; ++c) {
+          int cur = -1;
+          for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) {
+            const int J = cam_agg[col[q]];
+            if (J != cur) { sp_col.push_back(J); cur = J; }
+          }
+          sp_rowptr[c + 1] = (int)sp_col.size();
+        }
+        pb.n_agg = n_agg; pb.nc = 7 * n_agg; pb.ncp = (pb.nc + 63) / 64 * 64; pb.nnz_sp = (int)sp_col.size();
+        if (int rc = upload(h, &pb.cam_agg, cam_agg)) return rc;
+        if (int rc = upload(h, &pb.agg_off, agg_off)) return rc;
+        if (int rc = upload(h, &pb.sp_rowptr, sp_rowptr)) return rc;
+        if (int rc = upload(h, &pb.sp_col, sp_col)) return rc;
+        pb.tl = true;
+      }
+    }
   }
   mark("7 host BSR");
   // ---- 8. tile mode: pair slots = (tile, block) cells ordered inside each tile by decreasing entry count,

@@ -450,6 +450,8 @@ __global__ void __launch_bounds__(CHB_T) k_cholesky_blocked(int n, double* __res
   if (tid == 0) { scal[S_SOLVE_FAIL] = 0.0; scal[S_DC_RES] = 0.0; scal[S_PCG_ITERS] = 0.0; }
 }
 
+#include "k_twolevel.cuh"
+
 }  // namespace
 
 int pcg_grid(Handle* h) {
@@ -474,6 +476,74 @@ int launch_pcg(Handle* h, double rtol, int max_iter) {
   void* args[] = {&a};
   const int grid = pcg_grid(h);
   BA_CUDA(h, cudaLaunchCooperativeKernel((void*)k_pcg, dim3(grid), dim3(PCG_T), args, 0, h->stream));
+  h->st.launches += 1;
+  return 0;
+}
+
+// ------------------------------------------------------------------ two-level preconditioner (k_twolevel.cuh)
+static TlArgs tl_args(Handle* h) {
+  Problem& pb = h->pb;
+  Work& w = h->w;
+  TlArgs a;
+  a.C = (int)pb.C; a.n_agg = pb.n_agg; a.nc = pb.nc; a.ncp = pb.ncp; a.Cs = pb.Cs;
+  a.cam_agg = pb.cam_agg; a.agg_off = pb.agg_off; a.sp_rowptr = pb.sp_rowptr; a.sp_col = pb.sp_col;
+  a.rowptr = pb.bsr_rowptr; a.col = pb.bsr_col; a.src = pb.bsr_src;
+  a.Sup = w.Sup; a.camprep = w.camprep;
+  a.G = w.tl_G; a.SP = w.tl_SP; a.A = w.tl_A; a.cb = w.tl_cb; a.rb = w.tl_rb; a.dsc = w.tl_dsc; a.cen = w.tl_cen;
+  a.scal = w.scal;
+  return a;
+}
+
+int launch_tl_build(Handle* h, bool rebuild_coarse) {
+  Problem& pb = h->pb;
+  if (!pb.tl) return fail(h, B200BA_BAD_ARG, "two-level preconditioner is not set up for this problem");
+  TlArgs a = tl_args(h);
+  cudaStream_t st = h->stream;
+  if (rebuild_coarse) {
+    k_tl_gauge<<<pb.n_agg, 64, 0, st>>>(a);
+    h->st.launches += 1;
+  }
+  k_tl_sp<<<(int)((pb.C * 32 + 255) / 256), 256, 0, st>>>(a);
+  h->st.launches += 1;
+  if (rebuild_coarse) {
+    const size_t smem = (size_t)TL_K * pb.ncp * sizeof(double);
+    static bool attr = false;
+    if (!attr) { cudaFuncSetAttribute(k_tl_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
+    const double one = 1.0;
+    BA_CUDA(h, cudaMemcpyAsync(h->w.scal + S_TL_OK, &one, sizeof(double), cudaMemcpyHostToDevice, st));
+    k_tl_assemble<<<pb.n_agg + 1, 256, smem, st>>>(a);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_tl_gj, GJ_T, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    const int grid = std::min(per_sm, 2) * h->sm_count;
+    void* args[] = {&a};
+    BA_CUDA(h, cudaLaunchCooperativeKernel((void*)k_tl_gj, dim3(grid), dim3(GJ_T), args, 0, st));
+    h->st.launches += 2;
+  }
+  BA_CUDA(h, cudaGetLastError());
+  return 0;
+}
+
+int launch_pcg2(Handle* h, double rtol, int max_iter) {
+  Problem& pb = h->pb;
+  Work& w = h->w;
+  const int64_t n = 6 * pb.C;
+  Pcg2Args g;
+  PcgArgs& a = g.p;
+  a.C = (int)pb.C;
+  a.rowptr = pb.bsr_rowptr; a.col = pb.bsr_col; a.src = pb.bsr_src; a.diag_blk = pb.diag_blk;
+  a.Sup = w.Sup; a.b = w.b;
+  a.x = w.dc; a.r = w.pcg; a.z = w.pcg + n; a.p = w.pcg + 2 * n; a.Ap = w.pcg + 3 * n; a.s = w.pcg + 4 * n;
+  a.Minv = w.pcg + 5 * n;
+  a.part = w.pcg_part; a.scal = w.scal; a.rtol = rtol; a.max_iter = max_iter;
+  g.n_agg = pb.n_agg; g.nc = pb.nc; g.ncp = pb.ncp;
+  g.cam_agg = pb.cam_agg; g.agg_off = pb.agg_off; g.sp_rowptr = pb.sp_rowptr; g.sp_col = pb.sp_col;
+  g.G = w.tl_G; g.SP = w.tl_SP; g.Ainv = w.tl_A; g.rc = w.tl_rc; g.zc = w.tl_zc; g.uf = w.tl_uf;
+  void* args[] = {&g};
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg2, PCG_T, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  const int64_t need = std::max<int64_t>((pb.C + (PCG_T / 32) - 1) / (PCG_T / 32), 1);
+  const int grid = (int)std::min<int64_t>(std::min<int64_t>(need, (int64_t)per_sm * h->sm_count), pcg_grid(h));
+  BA_CUDA(h, cudaLaunchCooperativeKernel((void*)k_pcg2, dim3(grid), dim3(PCG_T), args, 0, h->stream));
   h->st.launches += 1;
   return 0;
 }

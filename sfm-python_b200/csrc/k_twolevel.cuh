@@ -1,0 +1,502 @@
+// Two-level preconditioner of the reduced camera system (included by ba_solve.cu, inside its anonymous namespace).
+//
+// Block-Jacobi PCG stalls on long camera chains once the damping gets small: with no gauge fixing (the reference
+// fixes no camera, bundle_adjustment.py:6 `fixed_camera_indices=()`), S has seven exactly-free directions (global
+// rotation, translation, scale) and every locally-rigid similarity motion of a group of neighbouring cameras is nearly
+// free as well.  The coarse space is spanned by exactly those motions:
+//
+//   aggregates   contiguous runs of cameras (ba_setup.cu); 7 coarse unknowns (phi, t, sigma) per aggregate
+//   G_c (6 x 7)  d(w_c, T_c) / d(phi, t, sigma) for a similarity about the aggregate's centroid:
+//                dw = -J_r(w)^-1 phi,   dT = phi x (T - Tbar) + t + sigma (T - Tbar)
+//   P            block column of the G_c of one aggregate;   A_c = P^T S P   (dense, 7 n_agg square)
+//   M^-1         = blockdiag(S)^-1 + P A_c^-1 P^T             (additive, symmetric positive definite)
+//
+// A_c^-1 is formed explicitly (Jacobi-scaled blocked Gauss-Jordan in one cooperative kernel) and applied as a dense
+// mat-vec inside the PCG; it is rebuilt only every few LM iterations (a stale coarse operator is still a valid
+// preconditioner), while SP = S P is refreshed with every new S so that  w = S u  costs one pass over S:
+//   u = u_loc + P z,   w = S u_loc + (S P) z.
+// Every sum runs in a fixed order: all ranks of a multi-GPU run compute identical bits.
+
+constexpr int TL_K = 7;           // coarse unknowns per aggregate
+constexpr int TL_GS = 6 * TL_K;   // doubles per G_c / SP block (6 x 7 row-major)
+constexpr int GJ_NB = 32;         // Gauss-Jordan panel width
+constexpr int GJ_TILE = 64;       // trailing-update tile
+constexpr int GJ_T = 256;
+
+struct TlArgs {
+  int C, n_agg, nc, ncp;          // ncp = nc rounded up to a multiple of GJ_TILE (padding rows/cols = identity)
+  int64_t Cs;
+  const int* cam_agg; const int* agg_off;
+  const int* sp_rowptr; const int* sp_col;
+  const int* rowptr; const int* col; const int* src;   // block-CSR view of S (both triangles)
+  const double* Sup; const double* camprep;
+  double* G; double* SP; double* A; double* cb; double* rb; double* dsc; double* cen;
+  double* scal;
+};
+
+// ------------------------------------------------------------------ G_c per camera (one CTA of 64 threads per aggregate)
+__global__ void __launch_bounds__(64) k_tl_gauge(TlArgs a) {
+  __shared__ double cen[3];
+  const int I = blockIdx.x;
+  const int c0 = a.agg_off[I], c1 = a.agg_off[I + 1];
+  if (threadIdx.x < 32) {
+    double s0 = 0, s1 = 0, s2 = 0;
+    for (int c = c0 + threadIdx.x; c < c1; c += 32) {
+      s0 += a.camprep[18 * a.Cs + c]; s1 += a.camprep[19 * a.Cs + c]; s2 += a.camprep[20 * a.Cs + c];
+    }
+    s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2);
+    if (threadIdx.x == 0) {
+      const double inv = 1.0 / (double)(c1 - c0);
+      cen[0] = s0 * inv; cen[1] = s1 * inv; cen[2] = s2 * inv;
+      a.cen[3 * I] = cen[0]; a.cen[3 * I + 1] = cen[1]; a.cen[3 * I + 2] = cen[2];
+    }
+  }
+  __syncthreads();
+  for (int c = c0 + threadIdx.x; c < c1; c += 64) {
+    double J[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) J[k] = a.camprep[(int64_t)(9 + k) * a.Cs + c];
+    // inverse of J_r by the adjugate (det = 2 (1 - cos t) / t^2 > 0 for |w| < 2 pi)
+    const double c00 = J[4] * J[8] - J[5] * J[7], c01 = J[5] * J[6] - J[3] * J[8], c02 = J[3] * J[7] - J[4] * J[6];
+    double det = J[0] * c00 + J[1] * c01 + J[2] * c02;
+    if (!(fabs(det) > 1e-12)) det = 1.0;
+    const double id = -1.0 / det;   // the block is -J_r^-1
+    double Ji[9];
+    Ji[0] = c00 * id; Ji[1] = (J[2] * J[7] - J[1] * J[8]) * id; Ji[2] = (J[1] * J[5] - J[2] * J[4]) * id;
+    Ji[3] = c01 * id; Ji[4] = (J[0] * J[8] - J[2] * J[6]) * id; Ji[5] = (J[2] * J[3] - J[0] * J[5]) * id;
+    Ji[6] = c02 * id; Ji[7] = (J[1] * J[6] - J[0] * J[7]) * id; Ji[8] = (J[0] * J[4] - J[1] * J[3]) * id;
+    const double x = a.camprep[18 * a.Cs + c] - cen[0], y = a.camprep[19 * a.Cs + c] - cen[1],
+                 z = a.camprep[20 * a.Cs + c] - cen[2];
+    double* G = a.G + (int64_t)c * TL_GS;
+    // rows 0..2: [-J_r^-1 | 0 | 0]
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      G[r * 7 + 0] = Ji[3 * r]; G[r * 7 + 1] = Ji[3 * r + 1]; G[r * 7 + 2] = Ji[3 * r + 2];
+      G[r * 7 + 3] = 0.0; G[r * 7 + 4] = 0.0; G[r * 7 + 5] = 0.0; G[r * 7 + 6] = 0.0;
+    }
+    // rows 3..5: [-[T - Tbar]x | I | T - Tbar]
+    G[21] = 0.0; G[22] = z;   G[23] = -y;  G[24] = 1.0; G[25] = 0.0; G[26] = 0.0; G[27] = x;
+    G[28] = -z;  G[29] = 0.0; G[30] = x;   G[31] = 0.0; G[32] = 1.0; G[33] = 0.0; G[34] = y;
+    G[35] = y;   G[36] = -x;  G[37] = 0.0; G[38] = 0.0; G[39] = 0.0; G[40] = 1.0; G[41] = z;
+  }
+}
+
+// ------------------------------------------------------------------ SP = S P, one warp per block row of S
+// Output block (c, J) = sum over the row's blocks S_cj with agg(j) = J of S_cj G_j; columns are ascending and the
+// aggregates are contiguous camera runs, so the blocks of one J are consecutive.  Lane o (and o + 32 < 42) owns
+// output element o = r * 7 + m.
+__global__ void __launch_bounds__(256) k_tl_sp(TlArgs a) {
+  const int lane = threadIdx.x & 31;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (c >= a.C) return;
+  const int o0 = lane, o1 = lane + 32;
+  const int r0 = o0 / 7, m0 = o0 % 7, r1 = (o1 < TL_GS ? o1 : 0) / 7, m1 = (o1 < TL_GS ? o1 : 0) % 7;
+  int e = a.sp_rowptr[c];
+  int curJ = -1;
+  double acc0 = 0.0, acc1 = 0.0;
+  for (int q = a.rowptr[c]; q < a.rowptr[c + 1]; ++q) {
+    const int j = a.col[q], s = a.src[q];
+    const int J = a.cam_agg[j];
+    if (J != curJ) {
+      if (curJ >= 0) {
+        a.SP[(int64_t)e * TL_GS + o0] = acc0;
+        if (o1 < TL_GS) a.SP[(int64_t)e * TL_GS + o1] = acc1;
+        ++e;
+      }
+      curJ = J; acc0 = 0.0; acc1 = 0.0;
+    }
+    const double* B = a.Sup + (int64_t)(s & 0x7fffffff) * 36;
+    const double* G = a.G + (int64_t)j * TL_GS;
+    const bool tr = s < 0;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const double b0 = tr ? B[k * 6 + r0] : B[r0 * 6 + k];
+      const double b1 = tr ? B[k * 6 + r1] : B[r1 * 6 + k];
+      acc0 = fma(b0, G[k * 7 + m0], acc0);
+      acc1 = fma(b1, G[k * 7 + m1], acc1);
+    }
+  }
+  if (curJ >= 0) {
+    a.SP[(int64_t)e * TL_GS + o0] = acc0;
+    if (o1 < TL_GS) a.SP[(int64_t)e * TL_GS + o1] = acc1;
+  }
+}
+
+// ------------------------------------------------------------------ A_c = P^T (S P): one CTA per aggregate (block row)
+// The block row (7 x ncp) is accumulated in shared memory camera by camera (fixed order), then written out; CTA
+// n_agg writes the identity padding rows.
+__global__ void __launch_bounds__(256) k_tl_assemble(TlArgs a) {
+  extern __shared__ double row[];   // [7][ncp]
+  const int I = blockIdx.x, tid = threadIdx.x;
+  const int ncp = a.ncp;
+  if (I >= a.n_agg) {   // padding rows nc .. ncp-1
+    for (int64_t idx = tid; idx < (int64_t)(ncp - a.nc) * ncp; idx += blockDim.x) {
+      const int r = a.nc + (int)(idx / ncp), cc = (int)(idx % ncp);
+      a.A[(int64_t)r * ncp + cc] = (r == cc) ? 1.0 : 0.0;
+    }
+    return;
+  }
+  for (int i = tid; i < TL_K * ncp; i += blockDim.x) row[i] = 0.0;
+  __syncthreads();
+  const int el = tid / 49, o = tid % 49, ra = o / 7, cb = o % 7;   // 5 entries x 49 outputs at a time
+  for (int c = a.agg_off[I]; c < a.agg_off[I + 1]; ++c) {
+    const double* G = a.G + (int64_t)c * TL_GS;
+    const int e0 = a.sp_rowptr[c], e1 = a.sp_rowptr[c + 1];
+    for (int eb = e0; eb < e1; eb += 5) {
+      const int e = eb + el;
+      if (el < 5 && e < e1) {
+        const double* SPb = a.SP + (int64_t)e * TL_GS;
+        double s = 0.0;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) s = fma(G[k * 7 + ra], SPb[k * 7 + cb], s);
+        row[ra * ncp + TL_K * a.sp_col[e] + cb] += s;   // distinct (e, ra, cb) -> distinct addresses
+      }
+    }
+    __syncthreads();
+  }
+  for (int i = tid; i < TL_K * ncp; i += blockDim.x) {
+    const int r = i / ncp, cc = i % ncp;
+    a.A[(int64_t)(TL_K * I + r) * ncp + cc] = row[i];
+  }
+}
+
+// ------------------------------------------------------------------ in-place inverse of the coarse matrix
+// Cooperative blocked Gauss-Jordan without pivoting (the matrix is symmetric positive definite), Jacobi-scaled first:
+//   A' = D^-1/2 A D^-1/2,   A^-1 = D^-1/2 A'^-1 D^-1/2.
+// Block step k (panel of GJ_NB rows/columns), P = A_kk^-1:
+//   R = [P A_k,: with R_k = P]   (GJ_NB x n),   Ccol = A_:,k (old, zero in the panel's own rows)
+//   rows of the panel:  A_k,: = R;   other rows:  A_i,: = (A_i,: with the panel's columns zeroed) - Ccol_i R.
+// Phase a (panel inverse, R, Ccol) and phase b (trailing update) are separated by grid-wide syncs.
+__global__ void __launch_bounds__(GJ_T) k_tl_gj(TlArgs a) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double Ps[GJ_NB][GJ_NB + 1];
+  __shared__ double Cs[GJ_TILE][GJ_NB + 1];
+  __shared__ __align__(16) double Rs[GJ_NB][GJ_TILE];
+  __shared__ int s_bad;
+  const int n = a.ncp, tid = threadIdx.x;
+  const int gtid = blockIdx.x * blockDim.x + tid, gthreads = gridDim.x * blockDim.x;
+  double* A = a.A;
+  // ---- Jacobi scaling
+  for (int i = gtid; i < n; i += gthreads) {
+    const double d = A[(int64_t)i * n + i];
+    const bool ok = d > 0.0 && d < 1e300;
+    a.dsc[i] = ok ? rsqrt(d) : 1.0;
+    if (!ok) a.scal[S_TL_OK] = 0.0;
+  }
+  grid.sync();
+  for (int64_t idx = gtid; idx < (int64_t)n * n; idx += gthreads) {
+    const int i = (int)(idx / n), j = (int)(idx % n);
+    A[idx] *= a.dsc[i] * a.dsc[j];
+  }
+  grid.sync();
+  const int nt = n / GJ_TILE;
+  for (int k0 = 0; k0 < n; k0 += GJ_NB) {
+    // ---- phase a: column chunks of the row panel (CTAs 0 .. nt-1), copy of the column panel (everybody)
+    if ((int)blockIdx.x < nt) {
+      if (tid == 0) s_bad = 0;
+      for (int i = tid; i < GJ_NB * GJ_NB; i += GJ_T) Ps[i / GJ_NB][i % GJ_NB] = A[(int64_t)(k0 + i / GJ_NB) * n + k0 + i % GJ_NB];
+      __syncthreads();
+      for (int s = 0; s < GJ_NB; ++s) {   // unblocked Gauss-Jordan of the 32 x 32 pivot block in shared memory
+        const double d = Ps[s][s];
+        if (tid == 0 && !(d > 1e-12 && d < 1e300)) s_bad = 1;   // scaled pivots are O(1) unless P is rank deficient
+        const double p = 1.0 / d;
+        double nv[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int i = (tid + q * GJ_T) / GJ_NB, j = (tid + q * GJ_T) % GJ_NB;
+          double v;
+          if (i == s) v = (j == s) ? p : Ps[s][j] * p;
+          else if (j == s) v = -Ps[i][s] * p;
+          else v = Ps[i][j] - Ps[i][s] * Ps[s][j] * p;
+          nv[q] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) Ps[(tid + q * GJ_T) / GJ_NB][(tid + q * GJ_T) % GJ_NB] = nv[q];
+        __syncthreads();
+      }
+      if (s_bad && tid == 0) a.scal[S_TL_OK] = 0.0;
+      for (int jt = blockIdx.x; jt < nt; jt += gridDim.x) {
+        const int j0 = jt * GJ_TILE;
+        for (int i = tid; i < GJ_NB * GJ_TILE; i += GJ_T)
+          Rs[i / GJ_TILE][i % GJ_TILE] = A[(int64_t)(k0 + i / GJ_TILE) * n + j0 + i % GJ_TILE];
+        __syncthreads();
+        for (int i = tid; i < GJ_NB * GJ_TILE; i += GJ_T) {
+          const int r = i / GJ_TILE, cidx = i % GJ_TILE, j = j0 + cidx;
+          double v;
+          if (j >= k0 && j < k0 + GJ_NB) v = Ps[r][j - k0];
+          else {
+            v = 0.0;
+#pragma unroll 8
+            for (int t = 0; t < GJ_NB; ++t) v = fma(Ps[r][t], Rs[t][cidx], v);
+          }
+          a.rb[(int64_t)r * n + j] = v;
+        }
+        __syncthreads();
+      }
+    }
+    for (int64_t idx = gtid; idx < (int64_t)n * GJ_NB; idx += gthreads) {
+      const int i = (int)(idx / GJ_NB), t = (int)(idx % GJ_NB);
+      a.cb[idx] = (i >= k0 && i < k0 + GJ_NB) ? 0.0 : A[(int64_t)i * n + k0 + t];
+    }
+    grid.sync();
+    // ---- phase b: 64 x 64 tiles, thread (ty, tx) owns a 4 x 4 patch
+    const int ty = tid >> 4, tx = tid & 15;
+    for (int t = blockIdx.x; t < nt * nt; t += gridDim.x) {
+      const int i0 = (t / nt) * GJ_TILE, j0 = (t % nt) * GJ_TILE;
+      __syncthreads();
+      for (int i = tid; i < GJ_TILE * GJ_NB; i += GJ_T) Cs[i / GJ_NB][i % GJ_NB] = a.cb[(int64_t)(i0 + i / GJ_NB) * GJ_NB + i % GJ_NB];
+      for (int i = tid; i < GJ_NB * GJ_TILE; i += GJ_T) Rs[i / GJ_TILE][i % GJ_TILE] = a.rb[(int64_t)(i / GJ_TILE) * n + j0 + i % GJ_TILE];
+      __syncthreads();
+      double acc[4][4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int gi = i0 + ty * 4 + r;
+        const double2* p = reinterpret_cast<const double2*>(A + (int64_t)gi * n + j0 + tx * 4);
+        const double2 v0 = p[0], v1 = p[1];
+        acc[r][0] = v0.x; acc[r][1] = v0.y; acc[r][2] = v1.x; acc[r][3] = v1.y;
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          const int gj = j0 + tx * 4 + cc;
+          if (gj >= k0 && gj < k0 + GJ_NB) acc[r][cc] = 0.0;
+        }
+      }
+#pragma unroll 4
+      for (int kk = 0; kk < GJ_NB; ++kk) {
+        const double2 b0 = *reinterpret_cast<const double2*>(&Rs[kk][tx * 4]);
+        const double2 b1 = *reinterpret_cast<const double2*>(&Rs[kk][tx * 4 + 2]);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const double av = -Cs[ty * 4 + r][kk];
+          acc[r][0] = fma(av, b0.x, acc[r][0]); acc[r][1] = fma(av, b0.y, acc[r][1]);
+          acc[r][2] = fma(av, b1.x, acc[r][2]); acc[r][3] = fma(av, b1.y, acc[r][3]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int gi = i0 + ty * 4 + r;
+        double2 v0, v1;
+        if (gi >= k0 && gi < k0 + GJ_NB) {   // panel rows take R
+          const double* rp = &Rs[gi - k0][tx * 4];
+          v0 = make_double2(rp[0], rp[1]); v1 = make_double2(rp[2], rp[3]);
+        } else {
+          v0 = make_double2(acc[r][0], acc[r][1]); v1 = make_double2(acc[r][2], acc[r][3]);
+        }
+        double2* p = reinterpret_cast<double2*>(A + (int64_t)gi * n + j0 + tx * 4);
+        p[0] = v0; p[1] = v1;
+      }
+    }
+    grid.sync();
+  }
+  for (int64_t idx = gtid; idx < (int64_t)n * n; idx += gthreads) {
+    const int i = (int)(idx / n), j = (int)(idx % n);
+    A[idx] *= a.dsc[i] * a.dsc[j];
+  }
+}
+
+// ------------------------------------------------------------------ PCG with the two-level preconditioner
+struct Pcg2Args {
+  PcgArgs p;
+  int n_agg, nc, ncp;
+  const int* cam_agg; const int* agg_off; const int* sp_rowptr; const int* sp_col;
+  const double* G; const double* SP; const double* Ainv;
+  double* rc; double* zc; double* uf;
+};
+
+// phase L: per aggregate (one CTA) -- p, s, x, r updates, u_loc = Minv r, coarse residual rc_I = sum_c G_c^T r_c
+__device__ __forceinline__ void tl_local(const Pcg2Args& g, double* sm, bool first, double alpha, double beta,
+                                         double& rr_acc) {
+  const PcgArgs& a = g.p;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int kq = lane / 6, comp = lane % 6;
+  double* uloc = a.z;
+  for (int I = blockIdx.x; I < g.n_agg; I += gridDim.x) {
+    const int c0 = g.agg_off[I], c1 = g.agg_off[I + 1];
+    double t[TL_K];
+#pragma unroll
+    for (int m = 0; m < TL_K; ++m) t[m] = 0.0;
+    for (int c5 = c0 + wid * 5; c5 < c1; c5 += nw * 5) {
+      const int c = c5 + kq;
+      const bool on = lane < 30 && c < c1;
+      const int i = 6 * (on ? c : c0) + comp;
+      double rk = 0.0;
+      if (on) {
+        if (first) {
+          rk = a.b[i];
+          a.x[i] = 0.0; a.r[i] = rk; a.p[i] = 0.0; a.s[i] = 0.0;
+        } else {
+          const double pk = g.uf[i] + beta * a.p[i];
+          const double sk = a.Ap[i] + beta * a.s[i];
+          a.p[i] = pk; a.s[i] = sk;
+          a.x[i] += alpha * pk;
+          rk = a.r[i] - alpha * sk;
+          a.r[i] = rk;
+        }
+        rr_acc += rk * rk;
+      }
+      double tu = 0.0;
+      const double* mrow = a.Minv + (int64_t)(on ? c : c0) * 36 + comp * 6;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        const double rj = __shfl_sync(FULL, rk, 6 * kq + k);
+        tu += mrow[k] * rj;
+      }
+      if (on) {
+        uloc[i] = tu;
+        const double* Gr = g.G + (int64_t)c * TL_GS + comp * 7;
+#pragma unroll
+        for (int m = 0; m < TL_K; ++m) t[m] = fma(Gr[m], rk, t[m]);
+      }
+    }
+    // fixed-order CTA sum of the 7 partials
+#pragma unroll
+    for (int m = 0; m < TL_K; ++m) {
+      const double s = warp_sum(t[m]);
+      if (lane == 0) sm[100 + wid * TL_K + m] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < TL_K) {
+      double s = 0.0;
+      for (int w = 0; w < nw; ++w) s += sm[100 + w * TL_K + threadIdx.x];
+      g.rc[TL_K * I + threadIdx.x] = s;
+    }
+    __syncthreads();
+  }
+}
+
+// phase Z: z = A_c^-1 rc, one warp per row
+__device__ __forceinline__ void tl_coarse(const Pcg2Args& g, int gwarp, int gwarps, int lane, bool ok) {
+  for (int i = gwarp; i < g.nc; i += gwarps) {
+    if (!ok) { if (lane == 0) g.zc[i] = 0.0; continue; }   // no valid coarse inverse: plain block-Jacobi
+    const double* row = g.Ainv + (int64_t)i * g.ncp;
+    double s0 = 0.0, s1 = 0.0;
+    int j = lane;
+    for (; j + 32 < g.nc; j += 64) { s0 = fma(row[j], g.rc[j], s0); s1 = fma(row[j + 32], g.rc[j + 32], s1); }
+    if (j < g.nc) s0 = fma(row[j], g.rc[j], s0);
+    const double s = warp_sum(s0 + s1);
+    if (lane == 0) g.zc[i] = s;
+  }
+}
+
+// phase S: w = S u_loc + (S P) z,  u = u_loc + P z;  returns this lane's share of (w, u) and (r, u)
+__device__ __forceinline__ void tl_spmv(const Pcg2Args& g, int gwarp, int gwarps, int lane, double& dot_wu, double& dot_ru) {
+  const PcgArgs& a = g.p;
+  const double* v = a.z;
+  double* y = a.Ap;
+  const int kq = lane / 6, r = lane % 6;
+  for (int c = gwarp; c < a.C; c += gwarps) {
+    const int q0 = a.rowptr[c], q1 = a.rowptr[c + 1];
+    double acc = 0.0;
+    if (lane < 30) {
+      for (int q = q0 + kq; q < q1; q += 10) {
+        const int qb = q + 5;
+        const bool two = qb < q1;
+        const int s0 = a.src[q], c0 = a.col[q];
+        const int s1 = two ? a.src[qb] : s0, c1 = two ? a.col[qb] : c0;
+        const double* B0 = a.Sup + (int64_t)(s0 & 0x7fffffff) * 36;
+        const double* B1 = a.Sup + (int64_t)(s1 & 0x7fffffff) * 36;
+        const double2* v0 = reinterpret_cast<const double2*>(v + 6 * c0);
+        const double2* v1 = reinterpret_cast<const double2*>(v + 6 * c1);
+        double b0[6], b1[6];
+        if (s0 < 0) {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) b0[j] = B0[j * 6 + r];
+        } else {
+          const double2* p = reinterpret_cast<const double2*>(B0 + 6 * r);
+          const double2 t0 = p[0], t1 = p[1], t2 = p[2];
+          b0[0] = t0.x; b0[1] = t0.y; b0[2] = t1.x; b0[3] = t1.y; b0[4] = t2.x; b0[5] = t2.y;
+        }
+        if (s1 < 0) {
+#pragma unroll
+          for (int j = 0; j < 6; ++j) b1[j] = B1[j * 6 + r];
+        } else {
+          const double2* p = reinterpret_cast<const double2*>(B1 + 6 * r);
+          const double2 t0 = p[0], t1 = p[1], t2 = p[2];
+          b1[0] = t0.x; b1[1] = t0.y; b1[2] = t1.x; b1[3] = t1.y; b1[4] = t2.x; b1[5] = t2.y;
+        }
+        const double2 x0 = v0[0], x1 = v0[1], x2 = v0[2];
+        const double2 z0 = v1[0], z1 = v1[1], z2 = v1[2];
+        acc += b0[0] * x0.x + b0[1] * x0.y + b0[2] * x1.x + b0[3] * x1.y + b0[4] * x2.x + b0[5] * x2.y;
+        if (two) acc += b1[0] * z0.x + b1[1] * z0.y + b1[2] * z1.x + b1[3] * z1.y + b1[4] * z2.x + b1[5] * z2.y;
+      }
+      for (int e = g.sp_rowptr[c] + kq; e < g.sp_rowptr[c + 1]; e += 5) {
+        const double* SPr = g.SP + (int64_t)e * TL_GS + r * 7;
+        const double* zz = g.zc + TL_K * g.sp_col[e];
+        double t = 0.0;
+#pragma unroll
+        for (int m = 0; m < TL_K; ++m) t = fma(SPr[m], zz[m], t);
+        acc += t;
+      }
+    }
+    double tot = 0.0;
+#pragma unroll
+    for (int gq = 0; gq < 5; ++gq) tot += __shfl_sync(FULL, acc, (lane % 6) + 6 * gq);
+    if (lane < 6) {
+      const double* Gr = g.G + (int64_t)c * TL_GS + lane * 7;
+      const double* zz = g.zc + TL_K * g.cam_agg[c];
+      double uc = v[6 * c + lane];
+#pragma unroll
+      for (int m = 0; m < TL_K; ++m) uc = fma(Gr[m], zz[m], uc);
+      y[6 * c + lane] = tot;
+      g.uf[6 * c + lane] = uc;
+      dot_wu += tot * uc;
+      dot_ru += a.r[6 * c + lane] * uc;
+    }
+  }
+}
+
+// Chronopoulos-Gear PCG as k_pcg, preconditioner M^-1 = blockdiag^-1 + P A_c^-1 P^T; three grid syncs per iteration.
+__global__ void __launch_bounds__(PCG_T, 3) k_pcg2(Pcg2Args g) {
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double sm[192];
+  const PcgArgs& a = g.p;
+  const int C = a.C, n = 6 * C;
+  const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int gthreads = gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  const int gwarp = gtid >> 5, gwarps = gthreads >> 5;
+  for (int c = gtid; c < C; c += gthreads) inv6(a.Sup + (int64_t)a.diag_blk[c] * 36, a.Minv + (int64_t)c * 36);
+  grid.sync();
+  int phase = 0;
+  const bool coarse_ok = a.scal[S_TL_OK] != 0.0;
+  double bb = 0.0, gam = 0.0, del = 0.0, d0, d1, d2;
+  tl_local(g, sm, true, 0.0, 0.0, bb);
+  grid.sync();
+  tl_coarse(g, gwarp, gwarps, lane, coarse_ok);
+  grid.sync();
+  tl_spmv(g, gwarp, gwarps, lane, del, gam);
+  grid_sum3(grid, a.part, phase, sm, gam, del, bb, d0, d1, d2);
+  gam = d0; del = d1; bb = d2;
+  double rr = bb, alpha = 0.0, beta = 0.0;
+  int it = 0, fail = 0;
+  const double thresh = a.rtol * a.rtol * bb;
+  if (bb > 0.0) {
+    if (!(del > 0.0)) fail = 1;
+    else alpha = gam / del;
+  }
+  while (!fail && it < a.max_iter && rr > thresh && bb > 0.0) {
+    double gam_new = 0.0, rr_new = 0.0, del_part = 0.0;
+    tl_local(g, sm, false, alpha, beta, rr_new);
+    ++it;
+    grid.sync();
+    tl_coarse(g, gwarp, gwarps, lane, coarse_ok);
+    grid.sync();
+    tl_spmv(g, gwarp, gwarps, lane, del_part, gam_new);
+    grid_sum3(grid, a.part, phase, sm, gam_new, del_part, rr_new, d0, d1, d2);
+    gam_new = d0; del = d1; rr = d2;
+    if (!(rr > thresh)) break;
+    beta = gam_new / gam;
+    const double denom = del - beta * gam_new / alpha;
+    if (!(denom > 0.0)) { fail = 1; break; }
+    alpha = gam_new / denom;
+    gam = gam_new;
+  }
+  double dr = 0.0;
+  for (int i = gtid; i < n; i += gthreads) dr += a.x[i] * a.r[i];
+  grid_sum3(grid, a.part, phase, sm, dr, 0.0, 0.0, d0, d1, d2);
+  if (gtid == 0) {
+    a.scal[S_DC_RES] = d0;
+    a.scal[S_PCG_ITERS] = (double)it;
+    a.scal[S_SOLVE_FAIL] = (double)fail;
+  }
+}
