@@ -306,8 +306,21 @@ def run_b200(a, rank, world, local_rank):
     eng.set_profiling(False)
     lm_phase = {k: sq[k] / 3 for k in ("ms_lin_fused", "ms_slot_reduce", "ms_allreduce", "ms_camera_solve", "ms_backsub_trial")}
     lm = {"lm_iters_per_sec": a.steps / (lm_ms * 1e-3), "ms_per_lm_iter": lm_ms / a.steps, "lm_phase_ms": lm_phase,
+          "lm_phase_note": "first 3 LM iterations only (block-Jacobi PCG converges in a few iterations there); the "
+                           "camera solve of later iterations is ms_per_lm_iter minus the other phases",
           "pcg_iters_per_lm_iter": res.pcg_iters / max(res.n_iter, 1), "solver": solver,
+          "preconditioner": "two-level (gauge modes per camera aggregate, lagged coarse inverse) once block-Jacobi "
+                            "needs > 24 iterations" if n_cam >= 128 else "block-Jacobi",
           "cost_initial": res.initial_cost, "cost_after": res.cost}
+    # time to convergence with the reference's tolerances (ftol = 1e-10 = --ba_tol default, xtol = gtol = 1e-8)
+    x_work.copy_(x_dev)
+    barrier()
+    rc = eng.solve_dev(x_work.data_ptr(), ftol=1e-10, solver=solver, max_nfev=200)
+    cv = torch.tensor([rc.solve_ms], device=f"cuda:{local_rank}", dtype=torch.float64)
+    if td:
+        td.all_reduce(cv, op=td.ReduceOp.MAX)
+    lm["converge"] = {"ms": float(cv.item()), "lm_iters": int(rc.n_iter), "pcg_iters": int(rc.pcg_iters),
+                      "status": int(rc.status), "cost": rc.cost, "rms_px": rc.rms}
 
     # ---- e2e: the public host API with host buffers; every step uploads the problem and x0, solves, downloads x
     e2e_iters = 5

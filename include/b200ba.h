@@ -135,6 +135,12 @@ int b200ba_linearize_dev(b200ba_handle* h, const double* x_dev, double lambda);
 int b200ba_lm_step(b200ba_handle* h, const double* x, double lambda, int solver, double* delta_out,
                    double* predicted_out, double* new_cost_out);
 
+/* Preconditioner of the reduced-camera PCG (the reference's scipy step has no counterpart; scipy's LSMR is
+ * unpreconditioned): 0 = block-Jacobi only, 1 = automatic (default: block-Jacobi until a solve needs more than 24
+ * iterations, then the two-level preconditioner with a lagged coarse operator), 2 = two-level from the first solve,
+ * coarse operator rebuilt for every solve.  Only problems with >= 128 cameras carry the two-level structure. */
+int b200ba_set_two_level(b200ba_handle* h, int mode);
+
 /* Replaces scipy.optimize.least_squares at sfm.py:266-268: Levenberg-Marquardt on x_inout (host). */
 int b200ba_solve(b200ba_handle* h, double* x_inout, const b200ba_options* opt, b200ba_result* out);
 /* same with x resident on the device */

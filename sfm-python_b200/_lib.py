@@ -61,6 +61,7 @@ SIGNATURES = {
     "b200ba_lm_step": (C.c_int, [_P, _P, C.c_double, C.c_int, _P, _D, _D]),
     "b200ba_solve": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_solve_dev": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
+    "b200ba_set_two_level": (C.c_int, [_P, C.c_int]),
     "b200ba_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "b200ba_reset_stats": (C.c_int, [_P]),
     "b200ba_set_profiling": (C.c_int, [_P, C.c_int]),

@@ -216,6 +216,10 @@ class Engine:
     def set_profiling(self, on):
         self._check(self.lib.b200ba_set_profiling(self.h, int(bool(on))))
 
+    def set_two_level(self, mode):
+        """PCG preconditioner: 0 block-Jacobi, 1 automatic (default), 2 two-level from the first solve."""
+        self._check(self.lib.b200ba_set_two_level(self.h, int(mode)))
+
     def debug_fetch(self, name, count, dtype=np.float64):
         out = np.empty(int(count), dtype=dtype)
         n = self.lib.b200ba_debug_fetch(self.h, name.encode(), _ptr(out), out.nbytes)

@@ -195,6 +195,10 @@ static int alloc_work(Handle* h) {
   BA_CUDA(h, cudaMemsetAsync(w.comm, 0, (size_t)w.comm_count * sizeof(double), st));
   BA_CUDA(h, cudaMemsetAsync(w.scal, 0, NSCAL * sizeof(double), st));
   BA_CUDA(h, cudaMemsetAsync(w.dc, 0, (size_t)std::max<int64_t>(6 * C, 1) * sizeof(double), st));
+  if (pb.tl) {   // the padding entries nc .. ncp-1 stay zero (the coarse mat-vec runs over whole padded rows)
+    BA_CUDA(h, cudaMemsetAsync(w.tl_rc, 0, (size_t)pb.ncp * sizeof(double), st));
+    BA_CUDA(h, cudaMemsetAsync(w.tl_zc, 0, (size_t)pb.ncp * sizeof(double), st));
+  }
   BA_CUDA(h, cudaStreamSynchronize(st));
   return 0;
 }
@@ -239,13 +243,14 @@ int camera_solve(Handle* h, int solver, double rtol, int max_iter) {
   if (solver == B200BA_SOLVER_CHOLESKY) return launch_cholesky(h);
   // Two-level preconditioner: starts once block-Jacobi needed more than TL_START iterations (far from the optimum the
   // right-hand side has little weight in the weak modes and block-Jacobi converges in a handful); the coarse
-  // operator is rebuilt when it is TL_MAX_AGE solves old or the iteration count has grown by half since it was built.
+  // operator is rebuilt when it is TL_MAX_AGE solves old or the iteration count has tripled since it was built
+  // (measured: a coarse operator that is several LM iterations and a factor 30 in lambda old preconditions as well
+  // as a fresh one; the count grows with shrinking lambda and the tighter forcing term, not with staleness).
   // The decisions depend only on iteration counts, which are identical on every rank.
-  constexpr int TL_START = 24, TL_MAX_AGE = 8;
-  static const int tl_force = getenv("B200BA_TWOLEVEL") ? atoi(getenv("B200BA_TWOLEVEL")) : 1;  // 2: from the first solve
-  if (h->pb.tl && (h->tl_built || h->tl_last_iters > TL_START || tl_force == 2)) {
-    const bool rebuild = !h->tl_built || h->tl_age >= TL_MAX_AGE ||
-                         (h->tl_age >= 2 && h->tl_last_iters > h->tl_ref_iters + h->tl_ref_iters / 2 + 8);
+  constexpr int TL_START = 24, TL_MAX_AGE = 12;
+  if (h->pb.tl && h->tl_mode != 0 && (h->tl_built || h->tl_last_iters > TL_START || h->tl_mode == 2)) {
+    const bool rebuild = h->tl_mode == 2 || !h->tl_built || h->tl_age >= TL_MAX_AGE ||
+                         (h->tl_age >= 2 && h->tl_last_iters > 3 * h->tl_ref_iters + 30);
     if (int rc = launch_tl_build(h, rebuild)) return rc;
     if (rebuild) { h->tl_built = true; h->tl_age = 0; h->st.n_tl_builds += 1; }
     h->tl_age += 1;

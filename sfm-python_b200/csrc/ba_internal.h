@@ -202,6 +202,7 @@ struct Handle {
   bool profile = false;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   // two-level preconditioner state of the running solve (identical on every rank: driven by PCG iteration counts)
+  int tl_mode = 1;            // 0 block-Jacobi only, 1 automatic, 2 two-level from the first solve, rebuilt every solve
   bool tl_built = false;      // G / A_c^-1 hold a coarse operator of this solve
   int tl_age = 0;             // camera solves since the last rebuild
   int tl_ref_iters = 0;       // PCG iterations of the first solve after the last rebuild

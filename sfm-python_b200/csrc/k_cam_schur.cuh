@@ -303,12 +303,13 @@ __global__ void k_fix_diag(int C, const int* __restrict__ diag_blk, const double
 }
 
 // camera-side scalars of the step: g_c.dc, dc^T diag(U) dc, |dc|^2, |x_c|^2, max|g_c|
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 k_cam_dots(int n, const double* __restrict__ gc, const double* __restrict__ dc, const double* __restrict__ udiag,
            const double* __restrict__ xc, double* __restrict__ scal) {
   __shared__ double sm[32 * 5];
   double v[5] = {0, 0, 0, 0, 0};
   double mx = 0.0;
+#pragma unroll 4
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const double g = gc[i], d = dc[i], xx = xc[i];
     v[0] += g * d;

@@ -244,7 +244,7 @@ void launch_backsub_trial(Handle* h, double lambda) {
 
 void launch_cam_dots(Handle* h) {
   Work& w = h->w;
-  k_cam_dots<<<1, 256, 0, h->stream>>>((int)(6 * h->pb.C), w.gc, w.dc, w.udiag, w.x, w.scal);
+  k_cam_dots<<<1, 1024, 0, h->stream>>>((int)(6 * h->pb.C), w.gc, w.dc, w.udiag, w.x, w.scal);
   h->st.launches += 1;
 }
 

@@ -364,15 +364,20 @@ __device__ __forceinline__ void tl_local(const Pcg2Args& g, double* sm, bool fir
   }
 }
 
-// phase Z: z = A_c^-1 rc, one warp per row
+// phase Z: z = A_c^-1 rc, one warp per row (rows are ncp = 64 k doubles long, 16-byte aligned; the padding columns of
+// A_c^-1 are zero and rc is zero there)
 __device__ __forceinline__ void tl_coarse(const Pcg2Args& g, int gwarp, int gwarps, int lane, bool ok) {
+  const double2* rc2 = reinterpret_cast<const double2*>(g.rc);
+  const int n2 = g.ncp >> 1;
   for (int i = gwarp; i < g.nc; i += gwarps) {
     if (!ok) { if (lane == 0) g.zc[i] = 0.0; continue; }   // no valid coarse inverse: plain block-Jacobi
-    const double* row = g.Ainv + (int64_t)i * g.ncp;
+    const double2* row = reinterpret_cast<const double2*>(g.Ainv + (int64_t)i * g.ncp);
     double s0 = 0.0, s1 = 0.0;
-    int j = lane;
-    for (; j + 32 < g.nc; j += 64) { s0 = fma(row[j], g.rc[j], s0); s1 = fma(row[j + 32], g.rc[j + 32], s1); }
-    if (j < g.nc) s0 = fma(row[j], g.rc[j], s0);
+#pragma unroll 8
+    for (int j = lane; j < n2; j += 32) {
+      const double2 av = row[j], rv = rc2[j];
+      s0 = fma(av.x, rv.x, s0); s1 = fma(av.y, rv.y, s1);
+    }
     const double s = warp_sum(s0 + s1);
     if (lane == 0) g.zc[i] = s;
   }
