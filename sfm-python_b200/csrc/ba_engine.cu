@@ -147,6 +147,7 @@ static int alloc_work(Handle* h) {
   WALLOC(w.xn, nx + 2);
   WALLOC(w.camprep, (C + 2) * CAMPREP_STRIDE);   // field-major [21][Cs], Cs <= C + 1
   WALLOC(w.camprep_n, (C + 2) * CAMPREP_STRIDE);
+  WALLOC(w.cstep, (C + 2) * 6);
   WALLOC(w.Y, N * 18);
   WALLOC(w.rr, N * 4);
   WALLOC(w.pp, P * 12);
@@ -186,6 +187,7 @@ static int alloc_work(Handle* h) {
     WALLOC(w.tl_rc, pb.ncp);
     WALLOC(w.tl_zc, pb.ncp);
     WALLOC(w.tl_uf, 6 * C);
+    WALLOC(w.tl_prof, 8);
   }
   h->tl_built = false; h->tl_age = 0; h->tl_ref_iters = 0; h->tl_last_iters = 0;
 #undef WALLOC
@@ -198,6 +200,7 @@ static int alloc_work(Handle* h) {
   if (pb.tl) {   // the padding entries nc .. ncp-1 stay zero (the coarse mat-vec runs over whole padded rows)
     BA_CUDA(h, cudaMemsetAsync(w.tl_rc, 0, (size_t)pb.ncp * sizeof(double), st));
     BA_CUDA(h, cudaMemsetAsync(w.tl_zc, 0, (size_t)pb.ncp * sizeof(double), st));
+    BA_CUDA(h, cudaMemsetAsync(w.tl_prof, 0, 8 * sizeof(double), st));
   }
   BA_CUDA(h, cudaStreamSynchronize(st));
   return 0;
@@ -269,7 +272,7 @@ void tl_note_iters(Handle* h, int iters) {
 int trial_step(Handle* h, double lambda) {
   Work& w = h->w;
   PhaseTimer t(h, &h->st.ms_backsub_trial);
-  launch_cam_prep(h, w.x, w.dc, w.xn, w.camprep_n);
+  launch_cam_prep(h, w.x, w.dc, w.xn, w.camprep_n, w.camprep, w.cstep);
   launch_backsub_trial(h, lambda);
   if (int rc = comm_allreduce_sum(h, w.sums + 1, S_NSUM - 1)) return rc;  // slot 0 (cost at x) is already global
   launch_cam_dots(h);

@@ -141,6 +141,7 @@ struct Work {
   double* xn = nullptr;       // [6C+3P] trial parameters
   double* camprep = nullptr;  // [C*24]
   double* camprep_n = nullptr;
+  double* cstep = nullptr;    // [6][Cs] per-camera part of the back-substitution: J_r dw, dT
   double* Y = nullptr;        // [N*18]
   double* rr = nullptr;       // [N*4]  r0 r1 rt0 rt1
   double* pp = nullptr;       // [P*12] Linv(6) z(3) diagV(3)
@@ -179,6 +180,7 @@ struct Work {
   double* tl_rc = nullptr;    // [ncp]
   double* tl_zc = nullptr;    // [ncp]
   double* tl_uf = nullptr;    // [6C]
+  double* tl_prof = nullptr;  // [8] phase nanoseconds of k_pcg2 (debug_fetch "tl_prof")
   double* h_scal = nullptr;   // pinned host mirror [NSCAL]
 };
 
@@ -234,7 +236,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
 
 // ---- ba_kernels.cu (all launches on h->stream)
 void launch_cam_prep(Handle* h, const double* x_cams, const double* dc /*nullable*/, double* x_out /*nullable*/,
-                     double* camprep);
+                     double* camprep, const double* camprep_old = nullptr, double* cstep = nullptr);
 void launch_residual(Handle* h, const double* x, const double* camprep, double* r_out /*nullable, caller order*/,
                      int scal_slot);
 void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp);

@@ -54,8 +54,11 @@ __device__ __forceinline__ void block_sum(double* vals, double* smem /*[32*NV]*/
 }
 
 // ------------------------------------------------------------------ camera prep
+// With a step dc: prep of the trial cameras x + dc; cstep (nullable, field-major [6][Cs]) receives {J_r(w) dw, dT}
+// with J_r taken from camprep_old (the prep of x), the per-camera part of the back-substitution (project_step).
 __global__ void k_cam_prep(int C, int64_t Cs, const double* __restrict__ xc, const double* __restrict__ dc,
-                           double* __restrict__ x_out, double* __restrict__ camprep) {
+                           double* __restrict__ x_out, double* __restrict__ camprep,
+                           const double* __restrict__ camprep_old, double* __restrict__ cstep) {
   int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   double cam[6];
@@ -63,6 +66,16 @@ __global__ void k_cam_prep(int C, int64_t Cs, const double* __restrict__ xc, con
   for (int k = 0; k < 6; ++k) {
     cam[k] = xc[6 * c + k] + (dc ? dc[6 * c + k] : 0.0);
     if (x_out) x_out[6 * c + k] = cam[k];
+  }
+  if (cstep) {
+    const double d0 = dc[6 * c], d1 = dc[6 * c + 1], d2 = dc[6 * c + 2];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+      cstep[(int64_t)r * Cs + c] = camprep_old[(int64_t)(9 + 3 * r) * Cs + c] * d0 +
+                                   camprep_old[(int64_t)(10 + 3 * r) * Cs + c] * d1 +
+                                   camprep_old[(int64_t)(11 + 3 * r) * Cs + c] * d2;
+#pragma unroll
+    for (int r = 0; r < 3; ++r) cstep[(int64_t)(3 + r) * Cs + c] = dc[6 * c + 3 + r];
   }
   double out[CAMPREP_STRIDE];
   cam_prep(cam, out);

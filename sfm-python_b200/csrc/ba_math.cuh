@@ -115,6 +115,38 @@ BA_HD void project_jac(const double* __restrict__ cp, const Intrinsics& K, doubl
   }
 }
 
+// sum-term of the back-substitution for one observation: s3 = J_X^T (Jc dc) without forming Jc.
+// Jc dc = J_w dw + J_T dT = -J_X ([Y]x J_r dw + dT) = -J_X q,  q = Y x m + dT  with m = J_r(w) dw per CAMERA
+// (cs = {m, dT}, k_cam_prep); per observation only J_X = B R is needed (2x3).
+BA_HD void project_step(const double* __restrict__ R, const double* __restrict__ T, const double* __restrict__ cs,
+                        const Intrinsics& K, double X0, double X1, double X2, double* __restrict__ s3) {
+  const double y0 = X0 - T[0], y1 = X1 - T[1], y2 = X2 - T[2];
+  const double z0 = R[0] * y0 + R[1] * y1 + R[2] * y2;
+  const double z1 = R[3] * y0 + R[4] * y1 + R[5] * y2;
+  const double z2 = R[6] * y0 + R[7] * y1 + R[8] * y2;
+  const double p0 = K.k[0] * z0 + K.k[1] * z1 + K.k[2] * z2;
+  const double p1 = K.k[3] * z0 + K.k[4] * z1 + K.k[5] * z2;
+  const double p2 = K.k[6] * z0 + K.k[7] * z1 + K.k[8] * z2;
+  const double ip2 = 1.0 / p2;
+  const double pu = p0 * ip2, pv = p1 * ip2;
+  const double q0 = y1 * cs[2] - y2 * cs[1] + cs[3];
+  const double q1 = y2 * cs[0] - y0 * cs[2] + cs[4];
+  const double q2 = y0 * cs[1] - y1 * cs[0] + cs[5];
+  s3[0] = 0.0; s3[1] = 0.0; s3[2] = 0.0;
+#pragma unroll
+  for (int row = 0; row < 2; ++row) {
+    const double q = row == 0 ? pu : pv;
+    const double b0 = (K.k[3 * row + 0] - q * K.k[6]) * ip2;
+    const double b1 = (K.k[3 * row + 1] - q * K.k[7]) * ip2;
+    const double b2 = (K.k[3 * row + 2] - q * K.k[8]) * ip2;
+    const double a0 = b0 * R[0] + b1 * R[3] + b2 * R[6];
+    const double a1 = b0 * R[1] + b1 * R[4] + b2 * R[7];
+    const double a2 = b0 * R[2] + b1 * R[5] + b2 * R[8];
+    const double t = -(a0 * q0 + a1 * q1 + a2 * q2);
+    s3[0] = fma(a0, t, s3[0]); s3[1] = fma(a1, t, s3[1]); s3[2] = fma(a2, t, s3[2]);
+  }
+}
+
 // Damped 3x3 point block: V* = V + lambda*diag(V);  V* = L L^T;  returns Linv (lower, 6 entries:
 // i00 i10 i11 i20 i21 i22).  A non-positive pivot (rank-deficient point, e.g. a single observation
 // with lambda = 0) freezes the point: Linv = 0 => no Schur contribution, delta_p = 0.

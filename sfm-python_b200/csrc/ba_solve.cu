@@ -537,7 +537,7 @@ int launch_pcg2(Handle* h, double rtol, int max_iter) {
   a.part = w.pcg_part; a.scal = w.scal; a.rtol = rtol; a.max_iter = max_iter;
   g.n_agg = pb.n_agg; g.nc = pb.nc; g.ncp = pb.ncp;
   g.cam_agg = pb.cam_agg; g.agg_off = pb.agg_off; g.sp_rowptr = pb.sp_rowptr; g.sp_col = pb.sp_col;
-  g.G = w.tl_G; g.SP = w.tl_SP; g.Ainv = w.tl_A; g.rc = w.tl_rc; g.zc = w.tl_zc; g.uf = w.tl_uf;
+  g.G = w.tl_G; g.SP = w.tl_SP; g.Ainv = w.tl_A; g.rc = w.tl_rc; g.zc = w.tl_zc; g.uf = w.tl_uf; g.prof = w.tl_prof;
   void* args[] = {&g};
   int per_sm = 0;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg2, PCG_T, 0) != cudaSuccess || per_sm < 1) per_sm = 1;

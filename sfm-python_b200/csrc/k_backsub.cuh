@@ -21,6 +21,21 @@ __device__ __forceinline__ void point_step(const double* __restrict__ ppp, const
   sums[2] = dp[0] * dp[0] + dp[1] * dp[1] + dp[2] * dp[2];
 }
 
+// R -> cp[0..8], T -> cp[18..20] (the fields project_residual reads); the J_r fields are skipped
+__device__ __forceinline__ void load_rt(const double* __restrict__ camprep, int64_t Cs, int c, double* __restrict__ cp) {
+#pragma unroll
+  for (int k = 0; k < 9; ++k) cp[k] = camprep[(int64_t)k * Cs + c];
+#pragma unroll
+  for (int k = 18; k < 21; ++k) cp[k] = camprep[(int64_t)k * Cs + c];
+}
+// as load_rt, plus the camera's step fields {J_r dw, dT} -> cp[9..14]
+__device__ __forceinline__ void load_step_cam(const double* __restrict__ camprep, const double* __restrict__ cstep, int64_t Cs,
+                                              int c, double* __restrict__ cp) {
+  load_rt(camprep, Cs, c, cp);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) cp[9 + k] = cstep[(int64_t)k * Cs + c];
+}
+
 __device__ __forceinline__ void jc_dc_jp(const double* Jc, const double* Jp, const double* __restrict__ d, double* s3) {
   const double t0 = Jc[0] * d[0] + Jc[1] * d[1] + Jc[2] * d[2] + Jc[3] * d[3] + Jc[4] * d[4] + Jc[5] * d[5];
   const double t1 = Jc[6] * d[0] + Jc[7] * d[1] + Jc[8] * d[2] + Jc[9] * d[3] + Jc[10] * d[4] + Jc[11] * d[5];
@@ -31,7 +46,7 @@ __device__ __forceinline__ void jc_dc_jp(const double* Jc, const double* Jp, con
 
 __global__ void __launch_bounds__(LIN_WARPS * 32)
 k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ xn, const double* __restrict__ camprep,
-                const double* __restrict__ camprep_n, const double* __restrict__ dc, const double* __restrict__ pp,
+                const double* __restrict__ camprep_n, const double* __restrict__ cstep, const double* __restrict__ pp,
                 double* __restrict__ part) {
   __shared__ double sred[LIN_WARPS * 5];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -46,17 +61,16 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       const int c = pb.cam[i], p = pb.pt[i];
       const double X0 = xp[3 * p], X1 = xp[3 * p + 1], X2 = xp[3 * p + 2];
       const double uo = pb.u[i], vo = pb.v[i];
-      double r0, r1, Jc[12], Jp[6], s3[3], cp[CAMPREP_FIELDS];
-      load_cam(camprep, pb.Cs, c, cp);
-      project_jac(cp, pb.K, X0, X1, X2, uo, vo, r0, r1, Jc, Jp);
-      jc_dc_jp(Jc, Jp, dc + 6 * c, s3);
+      double r0, r1, s3[3], cp[CAMPREP_FIELDS];
+      load_step_cam(camprep, cstep, pb.Cs, c, cp);
+      project_step(cp, cp + 18, cp + 9, pb.K, X0, X1, X2, s3);
       if (!valid) s3[0] = s3[1] = s3[2] = 0.0;
       const SegInfo s = seg_info(p, valid, lane);
       seg_allsum<3>(s3, s, lane);
       double dp[3], sums[3];
       point_step(pp + 12 * (int64_t)p, s3, dp, sums);
       const double N0 = X0 + dp[0], N1 = X1 + dp[1], N2 = X2 + dp[2];
-      load_cam(camprep_n, pb.Cs, c, cp);
+      load_rt(camprep_n, pb.Cs, c, cp);
       project_residual(cp, pb.K, N0, N1, N2, uo, vo, r0, r1);
       if (valid) {
         acc[0] += r0 * r0 + r1 * r1;
@@ -72,10 +86,9 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       double s3[3] = {0, 0, 0};
       for (int i = a + lane; i < b; i += 32) {
         const int c = pb.cam[i];
-        double r0, r1, Jc[12], Jp[6], t3[3], cp[CAMPREP_FIELDS];
-        load_cam(camprep, pb.Cs, c, cp);
-        project_jac(cp, pb.K, X0, X1, X2, 0.0, 0.0, r0, r1, Jc, Jp);
-        jc_dc_jp(Jc, Jp, dc + 6 * c, t3);
+        double t3[3], cp[CAMPREP_FIELDS];
+        load_step_cam(camprep, cstep, pb.Cs, c, cp);
+        project_step(cp, cp + 18, cp + 9, pb.K, X0, X1, X2, t3);
         s3[0] += t3[0]; s3[1] += t3[1]; s3[2] += t3[2];
       }
       s3[0] = warp_sum(s3[0]); s3[1] = warp_sum(s3[1]); s3[2] = warp_sum(s3[2]);
@@ -84,7 +97,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       const double N0 = X0 + dp[0], N1 = X1 + dp[1], N2 = X2 + dp[2];
       for (int i = a + lane; i < b; i += 32) {
         double r0, r1, cp[CAMPREP_FIELDS];
-        load_cam(camprep_n, pb.Cs, pb.cam[i], cp);
+        load_rt(camprep_n, pb.Cs, pb.cam[i], cp);
         project_residual(cp, pb.K, N0, N1, N2, pb.u[i], pb.v[i], r0, r1);
         acc[0] += r0 * r0 + r1 * r1;
       }

@@ -88,10 +88,11 @@ struct KernelTimer {
   }
 };
 
-void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* x_out, double* camprep) {
+void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* x_out, double* camprep,
+                     const double* camprep_old, double* cstep) {
   const int C = (int)h->pb.C;
   if (C == 0) return;
-  k_cam_prep<<<cdiv(C, 128), 128, 0, h->stream>>>(C, h->pb.Cs, x_cams, dc, x_out, camprep);
+  k_cam_prep<<<cdiv(C, 128), 128, 0, h->stream>>>(C, h->pb.Cs, x_cams, dc, x_out, camprep, camprep_old, cstep);
   h->st.launches += 1;
 }
 
@@ -235,7 +236,7 @@ void launch_backsub_trial(Handle* h, double lambda) {
   (void)lambda;
   Work& w = h->w;
   const int pg = point_grid(h);
-  k_backsub_trial<<<pg, LIN_WARPS * 32, 0, h->stream>>>(h->pb, w.x, w.xn, w.camprep, w.camprep_n, w.dc, w.pp, w.part);
+  k_backsub_trial<<<pg, LIN_WARPS * 32, 0, h->stream>>>(h->pb, w.x, w.xn, w.camprep, w.camprep_n, w.cstep, w.pp, w.part);
   Slots sl{};
   sl.s[0] = S_NEWCOST2; sl.s[1] = S_GP_DP; sl.s[2] = S_DP_D_DP; sl.s[3] = S_DP2; sl.s[4] = S_XP2;
   k_reduce_partials2<<<1, 256, 0, h->stream>>>(pg, 5, 5, w.part, w.sums, w.scal, sl);

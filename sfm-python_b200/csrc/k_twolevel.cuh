@@ -301,6 +301,7 @@ struct Pcg2Args {
   const int* cam_agg; const int* agg_off; const int* sp_rowptr; const int* sp_col;
   const double* G; const double* SP; const double* Ainv;
   double* rc; double* zc; double* uf;
+  double* prof;   // [8] nanoseconds per phase, accumulated by thread 0 of CTA 0 (local, sync, coarse, sync, spmv, reduce)
 };
 
 // phase L: per aggregate (one CTA) -- p, s, x, r updates, u_loc = Minv r, coarse residual rc_I = sum_c G_c^T r_c
@@ -479,15 +480,28 @@ __global__ void __launch_bounds__(PCG_T, 3) k_pcg2(Pcg2Args g) {
     if (!(del > 0.0)) fail = 1;
     else alpha = gam / del;
   }
+  unsigned long long tq[7];
+  double pacc[6] = {0, 0, 0, 0, 0, 0};
+#define TL_STAMP(k) if (gtid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tq[k]))
   while (!fail && it < a.max_iter && rr > thresh && bb > 0.0) {
     double gam_new = 0.0, rr_new = 0.0, del_part = 0.0;
+    TL_STAMP(0);
     tl_local(g, sm, false, alpha, beta, rr_new);
     ++it;
+    TL_STAMP(1);
     grid.sync();
+    TL_STAMP(2);
     tl_coarse(g, gwarp, gwarps, lane, coarse_ok);
+    TL_STAMP(3);
     grid.sync();
+    TL_STAMP(4);
     tl_spmv(g, gwarp, gwarps, lane, del_part, gam_new);
+    TL_STAMP(5);
     grid_sum3(grid, a.part, phase, sm, gam_new, del_part, rr_new, d0, d1, d2);
+    TL_STAMP(6);
+    if (gtid == 0)
+#pragma unroll
+      for (int k = 0; k < 6; ++k) pacc[k] += (double)(tq[k + 1] - tq[k]);
     gam_new = d0; del = d1; rr = d2;
     if (!(rr > thresh)) break;
     beta = gam_new / gam;
@@ -503,5 +517,9 @@ __global__ void __launch_bounds__(PCG_T, 3) k_pcg2(Pcg2Args g) {
     a.scal[S_DC_RES] = d0;
     a.scal[S_PCG_ITERS] = (double)it;
     a.scal[S_SOLVE_FAIL] = (double)fail;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) g.prof[k] += pacc[k];
+    g.prof[6] += (double)it;
   }
+#undef TL_STAMP
 }

@@ -23,3 +23,8 @@ for kw in (dict(fixed_iters=fixed), dict()):
     print(f"[{tag}] {wl} {kw or 'converge'}: cost {r.cost:.9f} status {r.status} lm_iters {r.n_iter} pcg_total {r.pcg_iters} "
           f"solve_ms {r.solve_ms:.1f} ({r.solve_ms / max(r.n_iter, 1):.2f} ms/iter) tl_builds {st['n_tl_builds']} "
           f"wall {time.time() - t:.2f}s opt {r.optimality:.2e}", flush=True)
+    pr = eng.debug_fetch("tl_prof", 8)
+    if len(pr) and pr[6] > 0:
+        names = ("local", "sync", "coarse", "sync", "spmv", "reduce")
+        print("   k_pcg2 us/iteration: " + ", ".join(f"{n} {pr[k] / pr[6] * 1e-3:.1f}" for k, n in enumerate(names)) +
+              f"  (total {pr[:6].sum() / pr[6] * 1e-3:.1f}, {int(pr[6])} iterations since set_problem)", flush=True)
