@@ -91,6 +91,7 @@ typedef struct b200ba_stats {
   int64_t n_tiles, n_pair_slots, n_self_slots;
   double ms_jacobian;     /* k_jacobian alone (config E sweep) */
   int64_t n_tl_builds;    /* rebuilds of the coarse operator of the two-level PCG preconditioner */
+  double ms_reproj;       /* k_reproj_err alone */
 } b200ba_stats;
 
 int b200ba_version(void);
@@ -118,6 +119,17 @@ int b200ba_residuals(b200ba_handle* h, const double* x, double* r_out, double* c
 /* same with DEVICE pointers (torch tensor .data_ptr()); r_out_dev may be NULL */
 int b200ba_residuals_dev(b200ba_handle* h, const double* x_dev, double* r_out_dev, double* cost_out);
 
+/* The per-observation reprojection-error loop of SFM._apply_increment (sfm.py:234-238), which calls
+ * calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14) once per observation in Python:
+ * err_i = || pi(K (R_c X_p + t_c)) - uv_i ||  over the observations of the problem on the handle, in the pipeline's
+ * R X + t convention (node.H, NOT the R (X - T) of the BA residual).  Rt: n_cam x 12 doubles, per camera R row-major
+ * (9) then t (3) = the top three rows of node.H rearranged; X: n_pts x 3.  err_out (N, caller's order, may be NULL);
+ * sum_out = sum_i err_i over all ranks (the `errs` of sfm.py:238; the mean is sum / N). */
+int b200ba_reproj_errors(b200ba_handle* h, const double* Rt, const double* X, double* err_out, double* sum_out);
+/* same with DEVICE pointers */
+int b200ba_reproj_errors_dev(b200ba_handle* h, const double* Rt_dev, const double* X_dev, double* err_out_dev,
+                             double* sum_out);
+
 /* Analytic replacement of scipy's finite-difference Jacobian (sfm.py:266 jac='2-point' + jac_sparsity):
  * Jc N x 2 x 6 ([d/dw | d/dT]), Jp N x 2 x 3, caller's observation order, host buffers. */
 int b200ba_jacobian_blocks(b200ba_handle* h, const double* x, double* Jc, double* Jp);
@@ -134,6 +146,13 @@ int b200ba_linearize_dev(b200ba_handle* h, const double* x_dev, double lambda);
 /* One damped step from x: delta (6C + 3P), predicted reduction, cost at x + delta (host buffers; test hook). */
 int b200ba_lm_step(b200ba_handle* h, const double* x, double lambda, int solver, double* delta_out,
                    double* predicted_out, double* new_cost_out);
+
+/* The `fixed_camera_indices` hook of create_sparsity_matrix (bundle_adjustment.py:6,13; unused by sfm.py:264, default
+ * ()): the listed cameras (dense indices of the current problem) keep their parameters -- in the reference their
+ * Jacobian columns are masked out of jac_sparsity, so scipy's finite differences never see them.  Here rows/columns
+ * of the reduced camera system are deleted, so their step is exactly zero; the points they observe still move.
+ * Call after b200ba_set_problem (which clears the set); n = 0 frees every camera.  On every rank of a multi-GPU job. */
+int b200ba_set_fixed_cameras(b200ba_handle* h, const int64_t* cam_idx, int64_t n);
 
 /* Preconditioner of the reduced-camera PCG (the reference's scipy step has no counterpart; scipy's LSMR is
  * unpreconditioned): 0 = block-Jacobi only, 1 = automatic (default: block-Jacobi until a solve needs more than 24

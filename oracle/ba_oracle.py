@@ -265,11 +265,21 @@ def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2
     return dict(S=S, b=b, Vinv=Vinv, W=W, **nb)
 
 
-def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam):
-    """One damped Gauss-Newton step via the Schur complement; returns (delta, predicted_reduction, sys)."""
+def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam, fixed_cameras=()):
+    """One damped Gauss-Newton step via the Schur complement; returns (delta, predicted_reduction, sys).
+
+    ``fixed_cameras``: the ``fixed_camera_indices`` hook of bundle_adjustment.py:6,13 -- those cameras' Jacobian
+    columns are masked out in the reference, i.e. rows/columns of the reduced system are deleted (delta_c = 0)."""
     s = schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam)
     ci = np.asarray(camera_indices)
     pi = np.asarray(point_indices)
+    for c in fixed_cameras:
+        sl = slice(6 * c, 6 * c + 6)
+        s["S"][sl, :] = 0.0
+        s["S"][:, sl] = 0.0
+        s["S"][sl, sl] = np.eye(6)
+        s["b"][sl] = 0.0
+        s["gc"][c] = 0.0
     dc = np.linalg.solve(s["S"], s["b"])
     Wt_dc = np.zeros((n_points, 3))
     np.add.at(Wt_dc, pi, np.einsum("nij,ni->nj", s["W"], dc.reshape(n_cameras, 6)[ci]))
@@ -282,7 +292,7 @@ def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
 
 
 def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
-             ftol=1e-10, xtol=1e-8, gtol=1e-8, max_iter=100, lam0=1e-4, verbose=0):
+             ftol=1e-10, xtol=1e-8, gtol=1e-8, max_iter=100, lam0=1e-4, verbose=0, fixed_cameras=()):
     """Reference LM loop (numpy twin of the engine's b200ba_solve).
 
     Marquardt damping lam*diag(H); accept iff the cost decreases; Nielsen update
@@ -297,7 +307,7 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
     status, nfev, it = 0, 1, 0
     while it < max_iter:
         it += 1
-        delta, pred, s = lm_step(x, *args, lam)
+        delta, pred, s = lm_step(x, *args, lam, fixed_cameras)
         g = np.concatenate([s["gc"].reshape(-1), s["gp"].reshape(-1)])
         gnorm = float(np.max(np.abs(g)))
         if gnorm < gtol:
@@ -343,7 +353,7 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
 # --------------------------------------------------------------------------
 
 def scipy_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
-                ftol=1e-10, verbose=0, max_nfev=None, fun=None, xtol=1e-8, **kw):
+                ftol=1e-10, verbose=0, max_nfev=None, fun=None, xtol=1e-8, fixed_cameras=(), **kw):
     """scipy.optimize.least_squares with exactly the keyword arguments of sfm.py:266-268.
 
     ``fun`` defaults to the vectorised residual (R2 of BASELINE.md); pass
@@ -352,10 +362,38 @@ def scipy_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2
     from scipy.optimize import least_squares
 
     fun = residuals if fun is None else fun
-    S = sparsity(n_cameras, n_points, len(camera_indices), camera_indices, point_indices)
+    S = sparsity(n_cameras, n_points, len(camera_indices), camera_indices, point_indices, fixed_cameras)
     return least_squares(fun, np.asarray(x0, dtype=np.float64), jac_sparsity=S, verbose=verbose,
                          x_scale="jac", ftol=ftol, xtol=xtol, method="trf", max_nfev=max_nfev,
                          args=(n_cameras, n_points, camera_indices, point_indices, points_2d, K), **kw)
+
+
+# --------------------------------------------------------------------------
+# Reprojection error in the pipeline's R X + t convention (next row 8f-2)
+# --------------------------------------------------------------------------
+
+def reproj_error(point3ds, point2ds, K, R, tvec):
+    """cv2_lite/solve_pnp.py:9-14: (K (R X^T + t))^T, divided by its third column, minus the observations -> (n, 2)."""
+    p = (np.asarray(K) @ (np.asarray(R) @ np.asarray(point3ds).T + np.asarray(tvec).reshape(3, 1))).T
+    p = p / p[:, 2].reshape(-1, 1)
+    return p[:, :2] - point2ds
+
+
+def calc_reproj_error(points3d, points2d, K, R, tvec):
+    """sfm_lite/sfm.py:38-41: mean of the row norms of reproj_error."""
+    return float(np.linalg.norm(reproj_error(points3d, points2d, K, R, tvec), axis=1).mean())
+
+
+def total_reproj_error(K, Hs, X3d, camera_indices, point_indices, points_2d):
+    """The loop of sfm.py:233-238, vectorised: per-observation error norms (n,) and their sum `errs`."""
+    Hs = np.asarray(Hs, dtype=np.float64)
+    ci = np.asarray(camera_indices)
+    pi = np.asarray(point_indices)
+    X = np.asarray(X3d, dtype=np.float64)[pi]
+    Z = np.einsum("nij,nj->ni", Hs[ci, :3, :3], X) + Hs[ci, :3, 3]
+    p = Z @ np.asarray(K, dtype=np.float64).T
+    e = np.linalg.norm(p[:, :2] / p[:, 2:3] - np.asarray(points_2d, dtype=np.float64), axis=1)
+    return e, float(e.sum())
 
 
 def rms(r):

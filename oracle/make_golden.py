@@ -197,6 +197,73 @@ def gen_scipy(ks):
         np.savez_compressed(out_path, **out)
 
 
+def gen_fixed(ks):
+    """The `fixed_camera_indices` hook (bundle_adjustment.py:6,13): scipy with the REAL reference sparsity mask built
+    for a fixed camera (its columns are absent, so scipy never moves it).  The fixed camera is the one with the lowest
+    reprojection RMS at x0 (a camera that sits at the previous call's optimum; on call 0 the identity camera of
+    sfm.py:176) -- fixing one of the two freshly re-registered cameras leaves no good minimum.
+    Call 0 also runs the REAL reference residual; later calls use the vectorised twin.  The oracle LM with the same
+    camera fixed gives the arbiter minimum."""
+    ref = ref_ba()
+    from scipy.optimize import least_squares
+    out = {}
+    for k in ks:
+        d = np.load(os.path.join(GOLD, f"sceaux_ba_{k}.npz"))
+        n_cam = int(d["n_cam"])
+        args = (n_cam, int(d["n_pts"]), d["ci"], d["pi"], d["uv"], d["K"])
+        r0 = O.residuals(d["x0"], *args).reshape(-1, 2)
+        per_cam = [np.sqrt(np.mean(r0[d["ci"] == c] ** 2)) if np.any(d["ci"] == c) else np.inf for c in range(n_cam)]
+        fixed = (int(np.argmin(per_cam)),)
+        t = time.time()
+        S = ref.create_sparsity_matrix(args[0], args[1], len(d["ci"]), d["ci"], d["pi"], fixed_camera_indices=fixed)
+        fun = ref.compute_residuals if k == 0 else O.residuals
+        res = least_squares(fun, d["x0"], jac_sparsity=S, verbose=0, x_scale="jac", ftol=float(d["ftol"]), method="trf",
+                            args=args)
+        moved = float(np.abs(res.x[6 * fixed[0]:6 * fixed[0] + 6] - d["x0"][6 * fixed[0]:6 * fixed[0] + 6]).max())
+        lm = O.lm_solve(d["x0"], *args, ftol=float(d["ftol"]), fixed_cameras=fixed)
+        out[f"fixed_{k}"] = np.array(fixed)
+        out[f"cost_{k}"] = res.cost
+        out[f"rms_{k}"] = O.rms(res.fun)
+        out[f"status_{k}"] = res.status
+        out[f"nfev_{k}"] = res.nfev
+        out[f"moved_{k}"] = moved
+        out[f"real_residual_{k}"] = int(k == 0)
+        out[f"lm_cost_{k}"] = lm["cost"]
+        out[f"lm_rms_{k}"] = lm["rms"]
+        print(f"[fixed {k}] fixed {fixed} (rms at x0 per camera {np.round(per_cam, 2)}) scipy cost {res.cost:.9f} rms "
+              f"{O.rms(res.fun):.6f} status {res.status} nfev {res.nfev} moved {moved:.1e} | oracle LM cost {lm['cost']:.9f} "
+              f"status {lm['status']} nit {lm['nit']}  {time.time() - t:.1f}s", flush=True)
+    np.savez_compressed(os.path.join(GOLD, "sceaux_fixed_ref.npz"), **out)
+
+
+def gen_reproj():
+    """Reprojection error in the pipeline's R X + t convention: the REAL reference functions reproj_error
+    (cv2_lite/solve_pnp.py:9-14) and the loop body of sfm.py:234-238 (calc_reproj_error, sfm.py:38-41, restated in two
+    lines here because sfm.py itself needs matplotlib/Tk to import) on seeded scenes."""
+    sys.path.insert(0, REF)
+    import cv2_lite.solve_pnp as sp
+    syn = synthetic()
+    rng = np.random.default_rng(11)
+    pb = syn.make_problem(9, 300, 1200, seed=3, window=6)
+    cams = pb.x_true[:54].reshape(9, 6)
+    Hs = np.zeros((9, 4, 4))
+    Hs[:, :3, :3] = O.rodrigues(cams[:, :3])
+    Hs[:, :3, 3] = -np.einsum("nij,nj->ni", Hs[:, :3, :3], cams[:, 3:])     # R (X - T) = R X + t with t = -R T
+    Hs[:, 3, 3] = 1.0
+    Hs[:, :3, 3] += 1e-3 * rng.standard_normal((9, 3))
+    X3d = pb.x_true[54:].reshape(-1, 3) + 1e-2 * rng.standard_normal((300, 3))
+    ci, pi, uv = pb.camera_indices, pb.point_indices, np.floor(pb.points_2d)
+    errs, per = 0.0, np.empty(len(ci))
+    for n in range(len(ci)):                      # the loop of sfm.py:234-238, one observation per call
+        e = sp.reproj_error(X3d[pi[n]].reshape(1, 3), uv[n].reshape(1, 2), pb.K, Hs[ci[n], :3, :3], Hs[ci[n], :3, 3])
+        per[n] = np.linalg.norm(e, axis=1).mean()  # sfm.py:40
+        errs += per[n]
+    one = sp.reproj_error(X3d[pi[ci == 4]], uv[ci == 4], pb.K, Hs[4, :3, :3], Hs[4, :3, 3])
+    np.savez_compressed(os.path.join(GOLD, "ref_reproj_error.npz"), Hs=Hs, X3d=X3d, ci=ci, pi=pi, uv=uv, K=pb.K, per_obs=per,
+                        errs=errs, cam4_mean=float(np.linalg.norm(one, axis=1).mean()), cam4_vec=one)
+    print("reproj golden: n", len(ci), "errs", errs, "mean", errs / len(ci), "camera 4 mean", np.linalg.norm(one, axis=1).mean())
+
+
 def gen_synthB():
     """A reduced BAL-shaped problem where scipy (reference kwargs) can be run to the end."""
     syn = synthetic()
@@ -218,5 +285,9 @@ if __name__ == "__main__":
         gen_sceaux()
     elif what == "scipy":
         gen_scipy([int(a) for a in sys.argv[2:]] or [0, 1, 2])
+    elif what == "reproj":
+        gen_reproj()
+    elif what == "fixed":
+        gen_fixed([int(a) for a in sys.argv[2:]] or [0, 1, 2])
     elif what == "synthB":
         gen_synthB()

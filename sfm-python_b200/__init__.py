@@ -4,11 +4,13 @@ The package directory is ``sfm-python_b200`` (not an importable name); ``import 
 root loads it (see ``b200ba.py``).  Public names mirror ``sfm_lite/bundle_adjustment.py`` and the
 ``scipy.optimize.least_squares`` call of ``sfm_lite/sfm.py:266-268``.
 """
-from .bundle_adjustment import (BAError, BAResult, Engine, JacobianSparsity, bundle_adjust, compute_residuals,
-                                create_sparsity_matrix, engine_for, install, least_squares)
+from .bundle_adjustment import (BAError, BAResult, Engine, JacobianSparsity, bundle_adjust, calc_reproj_error,
+                                compute_residuals, create_sparsity_matrix, engine_for, install, least_squares, pack_Rt,
+                                total_reproj_error)
 from . import synthetic
 from . import dist
 
-__all__ = ["BAError", "BAResult", "Engine", "JacobianSparsity", "bundle_adjust", "compute_residuals",
-           "create_sparsity_matrix", "engine_for", "install", "least_squares", "synthetic", "dist"]
+__all__ = ["BAError", "BAResult", "Engine", "JacobianSparsity", "bundle_adjust", "calc_reproj_error", "compute_residuals",
+           "create_sparsity_matrix", "engine_for", "install", "least_squares", "pack_Rt", "total_reproj_error",
+           "synthetic", "dist"]
 __version__ = "0.1.0"

@@ -36,7 +36,8 @@ class Stats(C.Structure):
                                          "bytes_device")] + \
                [(n, C.c_double) for n in ("ms_lin_fused", "ms_slot_reduce")] + \
                [(n, C.c_int64) for n in ("n_tiles", "n_pair_slots", "n_self_slots")] + [("ms_jacobian", C.c_double),
-                                                                                         ("n_tl_builds", C.c_int64)]
+                                                                                         ("n_tl_builds", C.c_int64),
+                                                                                         ("ms_reproj", C.c_double)]
 
 
 _P = C.c_void_p
@@ -54,6 +55,8 @@ SIGNATURES = {
     "b200ba_set_problem": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64, _P, _P, _P, _P]),
     "b200ba_residuals": (C.c_int, [_P, _P, _P, _D]),
     "b200ba_residuals_dev": (C.c_int, [_P, _P, _P, _D]),
+    "b200ba_reproj_errors": (C.c_int, [_P, _P, _P, _P, _D]),
+    "b200ba_reproj_errors_dev": (C.c_int, [_P, _P, _P, _P, _D]),
     "b200ba_jacobian_blocks": (C.c_int, [_P, _P, _P, _P]),
     "b200ba_jacobian_blocks_dev": (C.c_int, [_P, _P, _P, _P, _P]),
     "b200ba_normal_equations": (C.c_int, [_P, _P, C.c_double, _P, _P, _P, _D]),
@@ -62,6 +65,7 @@ SIGNATURES = {
     "b200ba_solve": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_solve_dev": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_set_two_level": (C.c_int, [_P, C.c_int]),
+    "b200ba_set_fixed_cameras": (C.c_int, [_P, _P, C.c_int64]),
     "b200ba_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "b200ba_reset_stats": (C.c_int, [_P]),
     "b200ba_set_profiling": (C.c_int, [_P, C.c_int]),

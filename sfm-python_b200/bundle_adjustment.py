@@ -54,6 +54,7 @@ class Engine:
                           "(a CUDA device is required; there is no CPU fallback)")
         self.h = h
         self.n_cam = self.n_pts = self.n_obs = 0
+        self.fixed = ()
         self.rank, self.nranks = 0, 1
 
     # -- lifetime
@@ -104,6 +105,7 @@ class Engine:
         self._check(self.lib.b200ba_set_problem(self.h, int(n_cam), int(n_pts), len(ci), _ptr(ci), _ptr(pi), _ptr(uv),
                                                 _ptr(Kc)))
         self.n_cam, self.n_pts, self.n_obs = int(n_cam), int(n_pts), len(ci)
+        self.fixed = ()
         return self
 
     @property
@@ -136,6 +138,19 @@ class Engine:
         Jp = np.empty((self.n_obs, 2, 3))
         self._check(self.lib.b200ba_jacobian_blocks(self.h, _ptr(x), _ptr(Jc), _ptr(Jp)))
         return Jc, Jp
+
+    def reproj_errors(self, Rt, X3d, want_errors=True):
+        """Per-observation ``|| pi(K (R X + t)) - uv ||`` over the problem's observations (the loop of
+        ``sfm.py:234-238``); ``Rt`` is ``(n_cam, 12)`` = R row-major then t, or ``(n_cam, 4, 4)`` / ``(n_cam, 3, 4)`` poses
+        ``H``.  Returns ``(errors or None, sum)``."""
+        Rt = pack_Rt(Rt)
+        X = np.ascontiguousarray(X3d, dtype=np.float64).reshape(-1, 3)
+        if Rt.shape[0] != self.n_cam or X.shape[0] != self.n_pts:
+            raise ValueError(f"expected {self.n_cam} poses and {self.n_pts} points")
+        err = np.empty(self.n_obs, dtype=np.float64) if want_errors else None
+        tot = C.c_double(0.0)
+        self._check(self.lib.b200ba_reproj_errors(self.h, _ptr(Rt), _ptr(X), _ptr(err), C.byref(tot)))
+        return err, tot.value
 
     def normal_equations(self, x, lam, want_S=True):
         x = self._x(x)
@@ -216,6 +231,12 @@ class Engine:
     def set_profiling(self, on):
         self._check(self.lib.b200ba_set_profiling(self.h, int(bool(on))))
 
+    def set_fixed_cameras(self, indices=()):
+        """Hold these cameras fixed (``fixed_camera_indices`` of ``bundle_adjustment.py:6``); () frees all."""
+        idx = np.ascontiguousarray(list(indices) if not isinstance(indices, np.ndarray) else indices, dtype=np.int64).ravel()
+        self._check(self.lib.b200ba_set_fixed_cameras(self.h, _ptr(idx) if len(idx) else C.c_void_p(0), len(idx)))
+        self.fixed = tuple(int(i) for i in idx)
+
     def set_two_level(self, mode):
         """PCG preconditioner: 0 block-Jacobi, 1 automatic (default), 2 two-level from the first solve."""
         self._check(self.lib.b200ba_set_two_level(self.h, int(mode)))
@@ -226,6 +247,17 @@ class Engine:
         if n < 0:
             self._check(int(n))
         return out[:n]
+
+
+def pack_Rt(poses):
+    """``(n, 4, 4)`` / ``(n, 3, 4)`` poses ``H = [R | t]`` (``transforms.py:5-9``) or ``(n, 12)`` rows -> contiguous ``(n, 12)``
+    ``[R row-major | t]``."""
+    a = np.asarray(poses, dtype=np.float64)
+    if a.ndim == 3 and a.shape[1:] in ((4, 4), (3, 4)):
+        a = np.concatenate([a[:, :3, :3].reshape(-1, 9), a[:, :3, 3]], axis=1)
+    if a.ndim != 2 or a.shape[1] != 12:
+        raise ValueError("poses must be (n, 4, 4), (n, 3, 4) or (n, 12)")
+    return np.ascontiguousarray(a)
 
 
 # ---------------------------------------------------------------------------------------------
@@ -253,6 +285,35 @@ def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K):
 def compute_residuals(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
     """Same signature / output as ``sfm_lite/bundle_adjustment.py:35-42``: (2N,) float64, projected - observed."""
     return engine_for(n_cameras, n_points, camera_indices, point_indices, points_2d, K).residuals(x)
+
+
+_reproj_engine = {"engine": None}
+
+
+def calc_reproj_error(points3d, points2d, K, R, tvec):
+    """Same signature / value as ``sfm_lite/sfm.py:38-41``: mean over the points of ``|| pi(K (R X + t)) - x ||``
+    (``reproj_error``, ``cv2_lite/solve_pnp.py:9-14``) for ONE camera."""
+    X = np.ascontiguousarray(points3d, dtype=np.float64).reshape(-1, 3)
+    uv = np.ascontiguousarray(points2d, dtype=np.float64).reshape(-1, 2)
+    n = len(X)
+    if len(uv) != n:
+        raise ValueError("points3d and points2d differ in length")
+    eng = _reproj_engine["engine"] = _reproj_engine["engine"] or Engine()
+    eng.set_problem(1, n, np.zeros(n, dtype=np.int64), np.arange(n, dtype=np.int64), uv, K)
+    Rt = np.concatenate([np.asarray(R, dtype=np.float64).reshape(9), np.asarray(tvec, dtype=np.float64).reshape(3)])[None]
+    _, tot = eng.reproj_errors(Rt, X, want_errors=False)
+    return tot / n
+
+
+def total_reproj_error(K, poses, X3d, camera_indices, point_indices, points_2d, engine=None):
+    """The whole loop of ``sfm.py:233-238`` in one call: returns ``(errs, n)`` with ``errs`` the sum over all observations
+    of the per-observation error (each ``calc_reproj_error`` call there sees one point, so its mean is the norm) and
+    ``n`` the observation count; ``poses`` are the registered cameras' ``H`` in dense camera-index order."""
+    Rt = pack_Rt(poses)
+    X = np.ascontiguousarray(X3d, dtype=np.float64).reshape(-1, 3)
+    eng = engine or engine_for(len(Rt), len(X), camera_indices, point_indices, points_2d, K)
+    _, tot = eng.reproj_errors(Rt, X, want_errors=False)
+    return tot, eng.n_obs
 
 
 class JacobianSparsity:
@@ -336,9 +397,14 @@ def _is_ba_residual(fun):
 
 
 def bundle_adjust(x0, n_cam, n_pts, camera_indices, point_indices, points_2d, K, ftol=1e-10, xtol=1e-8, gtol=1e-8,
-                  max_nfev=None, verbose=0, solver="auto", engine=None, **engine_opts):
-    """Global bundle adjustment of ``x0`` (layout of ``sfm.py:255-257``) on the GPU; returns :class:`BAResult`."""
+                  max_nfev=None, verbose=0, solver="auto", engine=None, fixed_camera_indices=(), **engine_opts):
+    """Global bundle adjustment of ``x0`` (layout of ``sfm.py:255-257``) on the GPU; returns :class:`BAResult`.
+
+    ``fixed_camera_indices``: cameras held fixed, the hook of ``bundle_adjustment.py:6,13``."""
     eng = engine or engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
+    fixed = tuple(sorted(int(i) for i in fixed_camera_indices))
+    if fixed != tuple(sorted(getattr(eng, "fixed", ()))):
+        eng.set_fixed_cameras(fixed)
     x, r = eng.solve(x0, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev, verbose=verbose, solver=solver,
                      **engine_opts)
     res = BAResult(x=x, cost=r.cost, optimality=r.optimality, nfev=int(r.nfev), njev=int(r.njev), status=int(r.status),
@@ -364,8 +430,10 @@ def least_squares(fun, x0, jac="2-point", bounds=None, method="trf", ftol=1e-8, 
         raise NotImplementedError("only loss='linear' (the reference's setting) is implemented")
     n_cam, n_pts, ci, pi, uv, K = args
     solver = extra.pop("solver", "auto")
+    # a mask built with fixed_camera_indices (bundle_adjustment.py:6,13) carries the cameras whose columns are absent
+    fixed = tuple(int(i) for i in getattr(jac_sparsity, "fixed", ()))
     return bundle_adjust(x0, n_cam, n_pts, ci, pi, uv, K, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev,
-                         verbose=verbose, solver=solver)
+                         verbose=verbose, solver=solver, fixed_camera_indices=fixed)
 
 
 def install(sfm_module):

@@ -237,6 +237,7 @@ int linearize_all(Handle* h, double lambda) {
     }
   }
   launch_fix_diag(h);
+  launch_fix_cameras(h);
   return 0;
 }
 

@@ -46,6 +46,7 @@ enum Scal {
   S_PCG_ITERS = 16,
   S_SOLVE_FAIL = 17,
   S_RES_COST2 = 18, // sum r^2 of b200ba_residuals
+  S_REPROJ_SUM = 20, // sum of per-observation reprojection error norms (b200ba_reproj_errors)
   S_TL_OK = 19,     // 1 = the coarse inverse of the two-level preconditioner is valid
   S_FLOW_ERR = 31   // (int) set by k_lin_flow when a dependency wait timed out
 };
@@ -121,6 +122,8 @@ struct Problem {
   int4* tile_info = nullptr;     // [n_st*4] {nA, n_pslot, n_dslot, flags} {blob_off16, blob_units16, cmin, cspan}
                                  //           {obs0, n_obs, wt0, n_pent} {pslot_base, dslot_base, pt0, n_pts}
   uint4* blob = nullptr;         // header(32 B) | pair slots (a, n) | self slots (a, n) | pair entries u32 | self entries u16
+  unsigned char* cam_fixed = nullptr;  // [C] 1 = held fixed (b200ba_set_fixed_cameras); null = none
+  int n_fixed = 0;
   // two-level preconditioner (k_twolevel.cuh): aggregates = contiguous camera runs, 7 coarse unknowns each
   bool tl = false;
   int n_agg = 0, nc = 0, ncp = 0;  // nc = 7 n_agg, ncp = nc rounded up to a multiple of 64
@@ -239,10 +242,12 @@ void launch_cam_prep(Handle* h, const double* x_cams, const double* dc /*nullabl
                      double* camprep, const double* camprep_old = nullptr, double* cstep = nullptr);
 void launch_residual(Handle* h, const double* x, const double* camprep, double* r_out /*nullable, caller order*/,
                      int scal_slot);
+void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out /*nullable, caller order*/);
 void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp);
 void launch_xchg_sum(Handle* h);  // sparse exchange: gathered per-rank contributions -> Sup, b, gc, udiag, cost, gpmax
 void launch_linearize(Handle* h, const double* x, double lambda);  // points + cameras + schur -> Sup, b, gc, ...
 void launch_fix_diag(Handle* h);
+void launch_fix_cameras(Handle* h);  // no-op unless b200ba_set_fixed_cameras marked some
 void launch_backsub_trial(Handle* h, double lambda);
 void launch_cam_dots(Handle* h);
 void launch_densify(Handle* h, double* dense /*6C x 6C*/);

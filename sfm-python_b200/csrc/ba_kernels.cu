@@ -113,6 +113,33 @@ __global__ void __launch_bounds__(256) k_residual(Problem pb, const double* __re
   if (threadIdx.x == 0) part[blockIdx.x * 8] = acc;
 }
 
+// ------------------------------------------------------------------ per-observation reprojection error (sfm.py:234-238)
+// The loop of SFM._apply_increment calls calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14)
+// once per observation: || pi(K (R X + t)) - uv ||, the pipeline's R X + t convention (NOT the R (X - T) of the BA
+// residual).  Rt = [R row-major (9) | t (3)] per camera; 24 B/observation in, 8 B out.
+__global__ void __launch_bounds__(256) k_reproj_err(Problem pb, const double* __restrict__ Rt, const double* __restrict__ X,
+                                                    double* __restrict__ err_out, double* __restrict__ part) {
+  __shared__ double sm[32];
+  double acc = 0.0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pb.N; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = pb.cam[i], p = pb.pt[i];
+    const double* q = Rt + 12 * (int64_t)c;
+    const double X0 = X[3 * (int64_t)p], X1 = X[3 * (int64_t)p + 1], X2 = X[3 * (int64_t)p + 2];
+    const double z0 = q[0] * X0 + q[1] * X1 + q[2] * X2 + q[9];
+    const double z1 = q[3] * X0 + q[4] * X1 + q[5] * X2 + q[10];
+    const double z2 = q[6] * X0 + q[7] * X1 + q[8] * X2 + q[11];
+    const double p0 = pb.K.k[0] * z0 + pb.K.k[1] * z1 + pb.K.k[2] * z2;
+    const double p1 = pb.K.k[3] * z0 + pb.K.k[4] * z1 + pb.K.k[5] * z2;
+    const double p2 = pb.K.k[6] * z0 + pb.K.k[7] * z1 + pb.K.k[8] * z2;
+    const double du = p0 / p2 - pb.u[i], dv = p1 / p2 - pb.v[i];
+    const double e = sqrt(du * du + dv * dv);
+    acc += e;
+    if (err_out) err_out[pb.perm ? pb.perm[i] : i] = e;
+  }
+  block_sum<1>(&acc, sm);
+  if (threadIdx.x == 0) part[blockIdx.x * 8] = acc;
+}
+
 // ------------------------------------------------------------------ materialised Jacobian blocks (config E)
 // One observation per thread; outputs staged in shared memory so the 16 + 96 + 48 B per observation leave the
 // SM as fully coalesced 8-byte-strided stores (identity order). With a caller permutation the stores scatter.

@@ -488,7 +488,7 @@ static TlArgs tl_args(Handle* h) {
   a.C = (int)pb.C; a.n_agg = pb.n_agg; a.nc = pb.nc; a.ncp = pb.ncp; a.Cs = pb.Cs;
   a.cam_agg = pb.cam_agg; a.agg_off = pb.agg_off; a.sp_rowptr = pb.sp_rowptr; a.sp_col = pb.sp_col;
   a.rowptr = pb.bsr_rowptr; a.col = pb.bsr_col; a.src = pb.bsr_src;
-  a.Sup = w.Sup; a.camprep = w.camprep;
+  a.Sup = w.Sup; a.camprep = w.camprep; a.fixed = pb.cam_fixed;
   a.G = w.tl_G; a.SP = w.tl_SP; a.A = w.tl_A; a.cb = w.tl_cb; a.rb = w.tl_rb; a.dsc = w.tl_dsc; a.cen = w.tl_cen;
   a.scal = w.scal;
   return a;

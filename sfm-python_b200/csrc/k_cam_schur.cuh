@@ -302,6 +302,22 @@ __global__ void k_fix_diag(int C, const int* __restrict__ diag_blk, const double
   if (udiag[t] == 0.0) Sup[(int64_t)diag_blk[t / 6] * 36 + 7 * (t % 6)] = 1.0;
 }
 
+// Fixed cameras (the `fixed_camera_indices` hook of bundle_adjustment.py:6,13: their Jacobian columns are masked out,
+// so scipy never moves them).  Holding camera c fixed = deleting row/column c of the reduced system, which is
+// independent of the point elimination: blocks touching c become 0 (identity on the diagonal), b_c = g_c = 0, hence
+// delta_c = 0 exactly and the optimality norm ignores c.
+__global__ void k_fix_cameras(int n_blk, int C, const int* __restrict__ blk_r, const int* __restrict__ blk_c,
+                              const unsigned char* __restrict__ fixed, double* __restrict__ Sup, double* __restrict__ b,
+                              double* __restrict__ gc) {
+  const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (t < (int64_t)n_blk * 36) {
+    const int q = (int)(t / 36), e = (int)(t % 36);
+    const int r = blk_r[q], c = blk_c[q];
+    if (fixed[r] || fixed[c]) Sup[t] = (r == c && e % 7 == 0) ? 1.0 : 0.0;
+  }
+  if (t < 6 * (int64_t)C && fixed[t / 6]) { b[t] = 0.0; gc[t] = 0.0; }
+}
+
 // camera-side scalars of the step: g_c.dc, dc^T diag(U) dc, |dc|^2, |x_c|^2, max|g_c|
 __global__ void __launch_bounds__(1024)
 k_cam_dots(int n, const double* __restrict__ gc, const double* __restrict__ dc, const double* __restrict__ udiag,

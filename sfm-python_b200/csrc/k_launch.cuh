@@ -105,6 +105,18 @@ void launch_residual(Handle* h, const double* x, const double* camprep, double* 
   h->st.launches += 2;
 }
 
+void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out) {
+  const int g = obs_grid(h);
+  KernelTimer t(h);
+  t.begin();
+  k_reproj_err<<<g, 256, 0, h->stream>>>(h->pb, Rt, X, err_out, h->w.part);
+  t.end(&h->st.ms_reproj);
+  Slots sl{};
+  sl.s[0] = S_REPROJ_SUM;
+  k_reduce_partials2<<<1, 256, 0, h->stream>>>(g, 1, 1, h->w.part, h->w.scal, h->w.scal, sl);
+  h->st.launches += 2;
+}
+
 void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp) {
   if (h->pb.N == 0) return;
   KernelTimer t(h);
@@ -228,6 +240,15 @@ void launch_xchg_sum(Handle* h) {
 
 void launch_fix_diag(Handle* h) {
   k_fix_diag<<<cdiv(6 * h->pb.C, 256), 256, 0, h->stream>>>((int)h->pb.C, h->pb.diag_blk, h->w.udiag, h->w.Sup);
+  h->st.launches += 1;
+}
+
+void launch_fix_cameras(Handle* h) {
+  Problem& pb = h->pb;
+  if (!pb.cam_fixed) return;
+  const int64_t n = std::max<int64_t>((int64_t)pb.n_blk * 36, 6 * pb.C);
+  k_fix_cameras<<<cdiv(n, 256), 256, 0, h->stream>>>(pb.n_blk, (int)pb.C, pb.blk_r, pb.blk_c, pb.cam_fixed, h->w.Sup, h->w.b,
+                                                     h->w.gc);
   h->st.launches += 1;
 }
 

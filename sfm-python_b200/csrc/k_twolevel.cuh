@@ -30,6 +30,7 @@ struct TlArgs {
   const int* sp_rowptr; const int* sp_col;
   const int* rowptr; const int* col; const int* src;   // block-CSR view of S (both triangles)
   const double* Sup; const double* camprep;
+  const unsigned char* fixed;      // nullable: cameras held fixed get G_c = 0 (the coarse correction must not move them)
   double* G; double* SP; double* A; double* cb; double* rb; double* dsc; double* cen;
   double* scal;
 };
@@ -78,6 +79,9 @@ __global__ void __launch_bounds__(64) k_tl_gauge(TlArgs a) {
     G[21] = 0.0; G[22] = z;   G[23] = -y;  G[24] = 1.0; G[25] = 0.0; G[26] = 0.0; G[27] = x;
     G[28] = -z;  G[29] = 0.0; G[30] = x;   G[31] = 0.0; G[32] = 1.0; G[33] = 0.0; G[34] = y;
     G[35] = y;   G[36] = -x;  G[37] = 0.0; G[38] = 0.0; G[39] = 0.0; G[40] = 1.0; G[41] = z;
+    if (a.fixed && a.fixed[c])
+#pragma unroll
+      for (int k = 0; k < TL_GS; ++k) G[k] = 0.0;
   }
 }
 

@@ -84,3 +84,42 @@ def test_jacobian_vs_central_differences_of_gpu_residual(engine):
             an = Jp[sel][:, :, k]
         assert np.abs(fd[sel] - an).max() <= 1e-6 * max(1.0, np.abs(an).max())
         assert np.abs(fd[~sel]).max() == 0.0
+
+
+# ------------------------------------------------------------------ reprojection error, R X + t convention
+def test_reproj_errors_vs_reference_golden(engine):
+    """b200ba_reproj_errors against the REAL reference reproj_error run per observation as in sfm.py:234-238."""
+    import b200ba
+    d = load_golden("ref_reproj_error.npz")
+    engine.set_problem(len(d["Hs"]), len(d["X3d"]), d["ci"], d["pi"], d["uv"], d["K"])
+    err, tot = engine.reproj_errors(d["Hs"], d["X3d"])
+    assert np.abs(err - d["per_obs"]).max() <= 1e-9 * d["per_obs"].max()
+    assert abs(tot - float(d["errs"])) <= 1e-9 * float(d["errs"])
+    tot2, n = b200ba.total_reproj_error(d["K"], d["Hs"], d["X3d"], d["ci"], d["pi"], d["uv"])
+    assert n == len(d["ci"]) and abs(tot2 - float(d["errs"])) <= 1e-9 * float(d["errs"])
+    m = d["ci"] == 4
+    one = b200ba.calc_reproj_error(d["X3d"][d["pi"][m]], d["uv"][m], d["K"], d["Hs"][4, :3, :3], d["Hs"][4, :3, 3])
+    assert abs(one - float(d["cam4_mean"])) <= 1e-9 * float(d["cam4_mean"])
+
+
+def test_reproj_errors_unsorted_and_large(engine):
+    """Caller's observation order is kept for unsorted input; a 200k-observation problem against the oracle."""
+    import b200ba
+    pb = b200ba.synthetic.make_problem(40, 50000, 200000, seed=2)
+    rng = np.random.default_rng(0)
+    perm = rng.permutation(pb.n_obs)
+    ci, pi, uv = pb.camera_indices[perm], pb.point_indices[perm], pb.points_2d[perm]
+    cams = pb.x0[:6 * 40].reshape(40, 6)
+    Hs = np.zeros((40, 4, 4))
+    Hs[:, :3, :3] = O.rodrigues(cams[:, :3])
+    Hs[:, :3, 3] = -np.einsum("nij,nj->ni", Hs[:, :3, :3], cams[:, 3:])
+    Hs[:, 3, 3] = 1.0
+    X = pb.x0[240:].reshape(-1, 3)
+    engine.set_problem(40, 50000, ci, pi, uv, pb.K)
+    err, tot = engine.reproj_errors(Hs, X)
+    e_ref, tot_ref = O.total_reproj_error(pb.K, Hs, X, ci, pi, uv)
+    assert np.abs(err - e_ref).max() <= 1e-9 * e_ref.max()
+    assert abs(tot - tot_ref) <= 1e-9 * tot_ref
+    # R X + t with t = -R T is the BA model: the norms of the BA residual pairs agree
+    r = engine.residuals(pb.x0).reshape(-1, 2)
+    assert np.abs(np.linalg.norm(r, axis=1) - err).max() <= 1e-8 * e_ref.max()

@@ -168,3 +168,49 @@ def test_two_level_converged_cost(engine):
     assert abs(a.cost - b.cost) <= 1e-6 * b.cost
     cost_check = 0.5 * float(np.sum(O.residuals(x_a, *pb.args()) ** 2))
     assert abs(cost_check - a.cost) <= 1e-9 * a.cost
+
+
+# ------------------------------------------------------------------ fixed cameras
+@pytest.mark.parametrize("k", [0, 1, 2, 3])
+@pytest.mark.parametrize("solver", ["cholesky", "pcg"])
+def test_fixed_camera_hook(engine, k, solver):
+    """`fixed_camera_indices` of bundle_adjustment.py:6,13 through the drop-in surface: the camera keeps its bits, the
+    cost reaches the oracle-LM minimum with that camera fixed (two-sided 1e-6) and is not above scipy's result with the
+    REAL reference mask (one-sided: scipy stops on xtol early once columns are masked)."""
+    import b200ba
+    g = load_golden("sceaux_fixed_ref.npz")
+    d = load_golden(f"sceaux_ba_{k}.npz")
+    n_cam, n_pts, ci, pi, uv, K = golden_args(d)
+    fixed = tuple(int(c) for c in g[f"fixed_{k}"])
+    mask = b200ba.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi, fixed_camera_indices=fixed)
+    res = b200ba.least_squares(b200ba.compute_residuals, d["x0"], jac_sparsity=mask, verbose=0, x_scale='jac',
+                               ftol=float(d["ftol"]), method='trf', args=(n_cam, n_pts, ci, pi, uv, K), solver=solver)
+    c = fixed[0]
+    assert res.status > 0
+    assert np.array_equal(res.x[6 * c:6 * c + 6], d["x0"][6 * c:6 * c + 6])
+    lm = float(g[f"lm_cost_{k}"])
+    assert abs(res.cost - lm) <= 1e-6 * lm
+    assert res.cost <= float(g[f"cost_{k}"]) * (1 + 1e-6)
+    assert np.abs(res.grad[6 * c:6 * c + 6]).max() == 0.0
+    # and the next call without a mask frees the camera again
+    free = b200ba.least_squares(b200ba.compute_residuals, d["x0"], ftol=float(d["ftol"]),
+                                args=(n_cam, n_pts, ci, pi, uv, K), solver=solver)
+    assert not np.array_equal(free.x[6 * c:6 * c + 6], d["x0"][6 * c:6 * c + 6])
+
+
+def test_fixed_cameras_two_level(engine):
+    """Fixed cameras on a chain that uses the two-level preconditioner: the fixed cameras stay bit-fixed under an
+    inexact PCG (their rows of the prolongation are zero) and the cost matches a tight block-Jacobi solve."""
+    pb = _chain(n_cam=256, n_pts=12000, n_obs=48000, seed=9)
+    engine.set_problem(*pb.args())
+    engine.set_fixed_cameras([0, 100])
+    try:
+        x_a, a = engine.solve(pb.x0, ftol=1e-10, solver="pcg")
+        engine.set_two_level(0)
+        x_b, b = engine.solve(pb.x0, ftol=1e-10, solver="pcg", pcg_rtol=1e-8, pcg_max_iter=5000)
+    finally:
+        engine.set_two_level(1)
+        engine.set_fixed_cameras(())
+    for c in (0, 100):
+        assert np.array_equal(x_a[6 * c:6 * c + 6], pb.x0[6 * c:6 * c + 6])
+    assert a.status > 0 and abs(a.cost - b.cost) <= 1e-6 * b.cost

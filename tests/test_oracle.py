@@ -94,3 +94,34 @@ def test_true_reference_scipy_golden_consistent():
     for k in (0, 1, 2):
         d = load_golden(f"sceaux_ba_{k}.npz")
         assert abs(float(ref[f"cost_{k}"]) - float(d["scipy_cost"])) <= 1e-7 * float(d["scipy_cost"])
+
+
+# ------------------------------------------------------------------ next rows: reprojection error, fixed cameras
+def test_reproj_error_oracle_vs_reference():
+    """oracle.reproj_error / total_reproj_error against the REAL reference reproj_error (cv2_lite/solve_pnp.py:9-14) run
+    per observation as in sfm.py:234-238 (ref_reproj_error.npz)."""
+    d = load_golden("ref_reproj_error.npz")
+    e, tot = O.total_reproj_error(d["K"], d["Hs"], d["X3d"], d["ci"], d["pi"], d["uv"])
+    assert np.abs(e - d["per_obs"]).max() <= 1e-12 * d["per_obs"].max()
+    assert abs(tot - float(d["errs"])) <= 1e-12 * float(d["errs"])
+    m = d["ci"] == 4
+    vec = O.reproj_error(d["X3d"][d["pi"][m]], d["uv"][m], d["K"], d["Hs"][4, :3, :3], d["Hs"][4, :3, 3])
+    assert np.abs(vec - d["cam4_vec"]).max() <= 1e-12 * np.abs(d["cam4_vec"]).max()
+    assert abs(O.calc_reproj_error(d["X3d"][d["pi"][m]], d["uv"][m], d["K"], d["Hs"][4, :3, :3], d["Hs"][4, :3, 3]) -
+               float(d["cam4_mean"])) <= 1e-12 * float(d["cam4_mean"])
+
+
+@pytest.mark.parametrize("k", [0, 2])
+def test_oracle_lm_with_fixed_camera(k):
+    """`fixed_camera_indices` (bundle_adjustment.py:6,13): the oracle LM with that camera's rows/columns deleted keeps it
+    bit-fixed, reaches the frozen minimum and beats scipy run with the REAL reference mask (scipy stops on xtol far
+    above the minimum once columns are masked, sceaux_fixed_ref.npz)."""
+    g = load_golden("sceaux_fixed_ref.npz")
+    d = load_golden(f"sceaux_ba_{k}.npz")
+    fixed = tuple(int(c) for c in g[f"fixed_{k}"])
+    lm = O.lm_solve(d["x0"], *golden_args(d), ftol=float(d["ftol"]), fixed_cameras=fixed)
+    c = fixed[0]
+    assert np.array_equal(lm["x"][6 * c:6 * c + 6], d["x0"][6 * c:6 * c + 6])
+    assert abs(lm["cost"] - float(g[f"lm_cost_{k}"])) <= 1e-6 * float(g[f"lm_cost_{k}"])
+    assert lm["cost"] <= float(g[f"cost_{k}"]) * (1 + 1e-6)
+    assert float(g[f"moved_{k}"]) <= 1e-9     # scipy, too, left the camera where it was
