@@ -119,6 +119,13 @@ int b200ba_residuals(b200ba_handle* h, const double* x, double* r_out, double* c
 /* same with DEVICE pointers (torch tensor .data_ptr()); r_out_dev may be NULL */
 int b200ba_residuals_dev(b200ba_handle* h, const double* x_dev, double* r_out_dev, double* cost_out);
 
+/* Pose <-> parameter conversion at the boundary.  pack = sfm.py:252-257: for each of n row-major
+ * 4x4 poses H, params = [Rot.from_matrix(H[:3,:3]).as_rotvec() (3) | H[:3,3] (3)]; unpack = sfm.py:273-278:
+ * H = [[Rot.from_rotvec(w).as_matrix(), T], [0 0 0 1]].  Restates scipy.spatial.transform's arithmetic (orthogonality
+ * test + polar factor, Markley's quaternion, canonical sign, series below 1e-3); host buffers; no problem needed. */
+int b200ba_pack_cameras(b200ba_handle* h, int64_t n, const double* H /* n x 16 */, double* params /* n x 6 */);
+int b200ba_unpack_cameras(b200ba_handle* h, int64_t n, const double* params /* n x 6 */, double* H /* n x 16 */);
+
 /* The per-observation reprojection-error loop of SFM._apply_increment (sfm.py:234-238), which calls
  * calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14) once per observation in Python:
  * err_i = || pi(K (R_c X_p + t_c)) - uv_i ||  over the observations of the problem on the handle, in the pipeline's

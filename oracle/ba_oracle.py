@@ -369,6 +369,29 @@ def scipy_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2
 
 
 # --------------------------------------------------------------------------
+# Pose <-> parameter conversion at the boundary
+# --------------------------------------------------------------------------
+
+def pack_cameras(Hs):
+    """sfm.py:252-255 per camera: (Rot.from_matrix(R).as_rotvec(), T) with R, T = RT_from_H(H) (transforms.py:12-15)."""
+    from scipy.spatial.transform import Rotation as Rot
+    Hs = np.asarray(Hs, dtype=np.float64)
+    return np.stack([np.hstack([Rot.from_matrix(H[:3, :3]).as_rotvec(), H[:3, 3].flatten()]) for H in Hs])
+
+
+def unpack_cameras(params):
+    """sfm.py:273-278 per camera: H_from_RT(Rot.from_rotvec(w).as_matrix(), T) (transforms.py:5-9)."""
+    from scipy.spatial.transform import Rotation as Rot
+    out = []
+    for p in np.asarray(params, dtype=np.float64).reshape(-1, 6):
+        H = np.eye(4)
+        H[:3, :3] = Rot.from_rotvec(p[:3]).as_matrix()
+        H[:3, 3] = p[3:]
+        out.append(H)
+    return np.stack(out)
+
+
+# --------------------------------------------------------------------------
 # Reprojection error in the pipeline's R X + t convention (next row 8f-2)
 # --------------------------------------------------------------------------
 

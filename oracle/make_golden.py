@@ -236,6 +236,35 @@ def gen_fixed(ks):
     np.savez_compressed(os.path.join(GOLD, "sceaux_fixed_ref.npz"), **out)
 
 
+def gen_poses():
+    """Pose <-> parameter conversions exactly as written at sfm.py:252-257 / 273-278 (scipy Rotation, the reference's
+    own dependency; scipy version recorded): random rotations, theta in {0, 1e-12 .. pi - 1e-9}, slightly and clearly
+    non-orthogonal matrices (cv2.recoverPose / cv2.Rodrigues outputs are orthogonal to ~1e-16)."""
+    import scipy
+    from scipy.spatial.transform import Rotation as Rot
+    rng = np.random.default_rng(5)
+    w = [rng.standard_normal(3) * s for s in (0.0, 1e-12, 1e-8, 1e-4, 9e-4, 1.1e-3, 0.3, 1.0, 2.5)]
+    for th in (np.pi - 1e-9, np.pi - 1e-4, 3.0, np.pi):
+        a = rng.standard_normal(3)
+        w.append(a / np.linalg.norm(a) * th)
+    w += [np.array([np.pi, 0, 0]), np.array([0, -np.pi + 1e-7, 0]), np.array([0, 0, 3.1])]
+    w += list(rng.standard_normal((40, 3)) * 1.5)
+    w = np.array(w)
+    R = Rot.from_rotvec(w).as_matrix()
+    Hs = np.tile(np.eye(4), (len(w), 1, 1))
+    Hs[:, :3, :3] = R
+    Hs[:, :3, 3] = rng.standard_normal((len(w), 3)) * 5
+    noisy = Hs.copy()
+    noisy[10:30, :3, :3] += 1e-9 * rng.standard_normal((20, 3, 3))      # fails the 1e-12 orthogonality test
+    noisy[30:45, :3, :3] += 1e-3 * rng.standard_normal((15, 3, 3))
+    allH = np.concatenate([Hs, noisy])
+    params = np.stack([np.hstack([Rot.from_matrix(H[:3, :3]).as_rotvec(), H[:3, 3].flatten()]) for H in allH])  # sfm.py:252-255
+    back = np.stack([Rot.from_rotvec(p[:3]).as_matrix() for p in params])                                        # sfm.py:277
+    np.savez_compressed(os.path.join(GOLD, "ref_pose_conversions.npz"), H=allH, params=params, R_back=back,
+                        scipy_version=scipy.__version__)
+    print("pose golden:", allH.shape, "scipy", scipy.__version__, "max angle", np.linalg.norm(params[:, :3], axis=1).max())
+
+
 def gen_reproj():
     """Reprojection error in the pipeline's R X + t convention: the REAL reference functions reproj_error
     (cv2_lite/solve_pnp.py:9-14) and the loop body of sfm.py:234-238 (calc_reproj_error, sfm.py:38-41, restated in two
@@ -285,6 +314,8 @@ if __name__ == "__main__":
         gen_sceaux()
     elif what == "scipy":
         gen_scipy([int(a) for a in sys.argv[2:]] or [0, 1, 2])
+    elif what == "poses":
+        gen_poses()
     elif what == "reproj":
         gen_reproj()
     elif what == "fixed":

@@ -152,6 +152,21 @@ class Engine:
         self._check(self.lib.b200ba_reproj_errors(self.h, _ptr(Rt), _ptr(X), _ptr(err), C.byref(tot)))
         return err, tot.value
 
+    def pack_cameras(self, poses):
+        """``(n, 4, 4)`` poses -> ``(n, 6)`` rows ``[rotvec | T]``: the per-camera conversion of ``sfm.py:252-257``
+        (``Rot.from_matrix(R).as_rotvec()``, ``T = H[:3, 3]``) for all cameras in one call."""
+        H = np.ascontiguousarray(poses, dtype=np.float64).reshape(-1, 16)
+        out = np.empty((len(H), 6), dtype=np.float64)
+        self._check(self.lib.b200ba_pack_cameras(self.h, len(H), _ptr(H), _ptr(out)))
+        return out
+
+    def unpack_cameras(self, params):
+        """``(n, 6)`` rows ``[rotvec | T]`` -> ``(n, 4, 4)`` poses: ``sfm.py:273-278`` for all cameras in one call."""
+        P = np.ascontiguousarray(params, dtype=np.float64).reshape(-1, 6)
+        out = np.empty((len(P), 4, 4), dtype=np.float64)
+        self._check(self.lib.b200ba_unpack_cameras(self.h, len(P), _ptr(P), _ptr(out)))
+        return out
+
     def normal_equations(self, x, lam, want_S=True):
         x = self._x(x)
         n = 6 * self.n_cam
@@ -287,6 +302,38 @@ def compute_residuals(x, n_cameras, n_points, camera_indices, point_indices, poi
     return engine_for(n_cameras, n_points, camera_indices, point_indices, points_2d, K).residuals(x)
 
 
+def _aux_engine():
+    _reproj_engine["engine"] = _reproj_engine["engine"] or Engine()
+    return _reproj_engine["engine"]
+
+
+def pack_parameters(poses, X3d, engine=None):
+    """``initial_guess`` of ``sfm.py:252-257``: ``[w_0 T_0 ... w_{C-1} T_{C-1} | X3d.ravel()]`` from the registered cameras'
+    poses ``H`` (dense camera-index order) and the points."""
+    cams = (engine or _aux_engine()).pack_cameras(poses)
+    return np.concatenate([cams.ravel(), np.asarray(X3d, dtype=np.float64).ravel()])
+
+
+def unpack_parameters(x, n_cam, engine=None):
+    """Write-back of ``sfm.py:271-281``: ``result.x`` -> (poses ``(n_cam, 4, 4)``, ``X3d (n_points, 3)``)."""
+    x = np.asarray(x, dtype=np.float64)
+    Hs = (engine or _aux_engine()).unpack_cameras(x[:6 * n_cam])
+    return Hs, x[6 * n_cam:].reshape(-1, 3)
+
+
+def gather_observations(track_point_idx, track_cam_id, track_xy, registered_cam_ids):
+    """Vectorised ``Graph.pt3ds_pt2ds`` + the index remapping of ``sfm.py:248-256``: from flat track arrays (one row per
+    ``(point, camera, x, y)`` track entry, point-major as ``graph.py:186-191`` iterates) keep the entries of registered
+    cameras and map graph camera ids to dense ranks.  Returns ``(camera_indices, point_indices, points_2d)``."""
+    pidx = np.asarray(track_point_idx, dtype=np.int64)
+    cid = np.asarray(track_cam_id, dtype=np.int64)
+    xy = np.asarray(track_xy)
+    reg = np.asarray(sorted(int(c) for c in registered_cam_ids), dtype=np.int64)   # node order = ascending graph id
+    pos = np.searchsorted(reg, cid)
+    keep = (pos < len(reg)) & (reg[np.minimum(pos, len(reg) - 1)] == cid)
+    return pos[keep], pidx[keep], xy[keep]
+
+
 _reproj_engine = {"engine": None}
 
 
@@ -298,7 +345,7 @@ def calc_reproj_error(points3d, points2d, K, R, tvec):
     n = len(X)
     if len(uv) != n:
         raise ValueError("points3d and points2d differ in length")
-    eng = _reproj_engine["engine"] = _reproj_engine["engine"] or Engine()
+    eng = _aux_engine()
     eng.set_problem(1, n, np.zeros(n, dtype=np.int64), np.arange(n, dtype=np.int64), uv, K)
     Rt = np.concatenate([np.asarray(R, dtype=np.float64).reshape(9), np.asarray(tvec, dtype=np.float64).reshape(3)])[None]
     _, tot = eng.reproj_errors(Rt, X, want_errors=False)

@@ -113,6 +113,94 @@ __global__ void __launch_bounds__(256) k_residual(Problem pb, const double* __re
   if (threadIdx.x == 0) part[blockIdx.x * 8] = acc;
 }
 
+// ------------------------------------------------------------------ pose <-> parameter conversion at the boundary
+// pack   (sfm.py:252-257): per registered camera  [Rot.from_matrix(H[:3,:3]).as_rotvec() | H[:3,3]]
+// unpack (sfm.py:273-278): H = [[Rot.from_rotvec(w).as_matrix(), T], [0, 1]]
+// The arithmetic restates scipy.spatial.transform (1.18, _rotation_xp.py): from_matrix = orthogonality test
+// |R R^T - I| <= 1e-12, else the orthogonal polar factor (scipy: U V^T of the SVD; here Newton's iteration
+// X <- (X + X^-T) / 2, which converges to the same matrix), then Markley's choice of the largest of
+// {R00, R11, R22, trace}, normalisation; as_rotvec = canonical sign (w >= 0), angle = 2 atan2(|v|, w), series below
+// 1e-3; from_rotvec / as_matrix likewise.  One thread per camera: C <= 1e4, the point is that no Python object per
+// camera is created (the reference builds C scipy Rotation objects per BA call, each way).
+__device__ __forceinline__ void polar3(double* R) {
+  for (int it = 0; it < 32; ++it) {
+    const double c00 = R[4] * R[8] - R[5] * R[7], c01 = R[5] * R[6] - R[3] * R[8], c02 = R[3] * R[7] - R[4] * R[6];
+    const double det = R[0] * c00 + R[1] * c01 + R[2] * c02;
+    const double id = 1.0 / det;
+    // X^-T = cofactor matrix / det
+    double T[9];
+    T[0] = c00 * id; T[1] = c01 * id; T[2] = c02 * id;
+    T[3] = (R[2] * R[7] - R[1] * R[8]) * id; T[4] = (R[0] * R[8] - R[2] * R[6]) * id; T[5] = (R[1] * R[6] - R[0] * R[7]) * id;
+    T[6] = (R[1] * R[5] - R[2] * R[4]) * id; T[7] = (R[2] * R[3] - R[0] * R[5]) * id; T[8] = (R[0] * R[4] - R[1] * R[3]) * id;
+    double diff = 0.0;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const double n = 0.5 * (R[k] + T[k]);
+      diff = fmax(diff, fabs(n - R[k]));
+      R[k] = n;
+    }
+    if (diff < 1e-16) break;
+  }
+}
+
+__global__ void k_pack_cameras(int64_t n, const double* __restrict__ H, double* __restrict__ params) {
+  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  const double* h = H + 16 * c;
+  double R[9] = {h[0], h[1], h[2], h[4], h[5], h[6], h[8], h[9], h[10]};
+  bool orth = true;
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double g = R[3 * i] * R[3 * j] + R[3 * i + 1] * R[3 * j + 1] + R[3 * i + 2] * R[3 * j + 2];
+      const double e = (i == j) ? 1.0 : 0.0;
+      orth = orth && (fabs(g - e) <= 1e-12 + 1e-5 * fabs(e));   // isclose(gramian, eye, atol = 1e-12), rtol = 1e-5 default
+    }
+  if (!orth) polar3(R);
+  const double tr = R[0] + R[4] + R[8];
+  double q[4];
+  int choice = 0;
+  double best = R[0];
+  if (R[4] > best) { best = R[4]; choice = 1; }
+  if (R[8] > best) { best = R[8]; choice = 2; }
+  if (tr > best) choice = 3;
+  if (choice == 0) { q[0] = 1.0 - tr + 2.0 * R[0]; q[1] = R[3] + R[1]; q[2] = R[6] + R[2]; q[3] = R[7] - R[5]; }
+  else if (choice == 1) { q[0] = R[3] + R[1]; q[1] = 1.0 - tr + 2.0 * R[4]; q[2] = R[7] + R[5]; q[3] = R[2] - R[6]; }
+  else if (choice == 2) { q[0] = R[6] + R[2]; q[1] = R[7] + R[5]; q[2] = 1.0 - tr + 2.0 * R[8]; q[3] = R[3] - R[1]; }
+  else { q[0] = R[7] - R[5]; q[1] = R[2] - R[6]; q[2] = R[3] - R[1]; q[3] = 1.0 + tr; }
+  const double qn = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) q[k] /= qn;
+  if (q[3] < 0.0 || (q[3] == 0.0 && (q[0] < 0.0 || (q[0] == 0.0 && (q[1] < 0.0 || (q[1] == 0.0 && q[2] < 0.0))))))
+#pragma unroll
+    for (int k = 0; k < 4; ++k) q[k] = -q[k];
+  const double an = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2]);
+  const double angle = 2.0 * atan2(an, q[3]);
+  const double a2 = angle * angle;
+  const double scale = (angle <= 1e-3) ? 2.0 + a2 / 12.0 + 7.0 * a2 * a2 / 2880.0 : angle / sin(angle / 2.0);
+  double* o = params + 6 * c;
+  o[0] = scale * q[0]; o[1] = scale * q[1]; o[2] = scale * q[2];
+  o[3] = h[3]; o[4] = h[7]; o[5] = h[11];
+}
+
+__global__ void k_unpack_cameras(int64_t n, const double* __restrict__ params, double* __restrict__ H) {
+  const int64_t c = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (c >= n) return;
+  const double* p = params + 6 * c;
+  const double angle = sqrt(p[0] * p[0] + p[1] * p[1] + p[2] * p[2]);
+  const double a2 = angle * angle;
+  const double scale = (angle <= 1e-3) ? 0.5 - a2 / 48.0 + a2 * a2 / 3840.0 : sin(angle / 2.0) / angle;
+  const double x = p[0] * scale, y = p[1] * scale, z = p[2] * scale, w = cos(angle / 2.0);
+  const double x2 = x * x, y2 = y * y, z2 = z * z, w2 = w * w;
+  const double xy = x * y, zw = z * w, xz = x * z, yw = y * w, yz = y * z, xw = x * w;
+  double* h = H + 16 * c;
+  h[0] = x2 - y2 - z2 + w2; h[1] = 2.0 * (xy - zw);    h[2] = 2.0 * (xz + yw);     h[3] = p[3];
+  h[4] = 2.0 * (xy + zw);   h[5] = -x2 + y2 - z2 + w2; h[6] = 2.0 * (yz - xw);     h[7] = p[4];
+  h[8] = 2.0 * (xz - yw);   h[9] = 2.0 * (yz + xw);    h[10] = -x2 - y2 + z2 + w2; h[11] = p[5];
+  h[12] = 0.0; h[13] = 0.0; h[14] = 0.0; h[15] = 1.0;
+}
+
 // ------------------------------------------------------------------ per-observation reprojection error (sfm.py:234-238)
 // The loop of SFM._apply_increment calls calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14)
 // once per observation: || pi(K (R X + t)) - uv ||, the pipeline's R X + t convention (NOT the R (X - T) of the BA

@@ -105,6 +105,17 @@ void launch_residual(Handle* h, const double* x, const double* camprep, double* 
   h->st.launches += 2;
 }
 
+void launch_pack_cameras(Handle* h, int64_t n, const double* H_dev, double* params_dev) {
+  if (n <= 0) return;
+  k_pack_cameras<<<cdiv(n, 128), 128, 0, h->stream>>>(n, H_dev, params_dev);
+  h->st.launches += 1;
+}
+void launch_unpack_cameras(Handle* h, int64_t n, const double* params_dev, double* H_dev) {
+  if (n <= 0) return;
+  k_unpack_cameras<<<cdiv(n, 128), 128, 0, h->stream>>>(n, params_dev, H_dev);
+  h->st.launches += 1;
+}
+
 void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out) {
   const int g = obs_grid(h);
   KernelTimer t(h);

@@ -123,3 +123,27 @@ def test_reproj_errors_unsorted_and_large(engine):
     # R X + t with t = -R T is the BA model: the norms of the BA residual pairs agree
     r = engine.residuals(pb.x0).reshape(-1, 2)
     assert np.abs(np.linalg.norm(r, axis=1) - err).max() <= 1e-8 * e_ref.max()
+
+
+# ------------------------------------------------------------------ pose <-> parameter conversion
+def test_pack_unpack_cameras_vs_scipy_golden(engine):
+    """b200ba_pack_cameras / b200ba_unpack_cameras against scipy Rotation run exactly as at sfm.py:252-257 / 273-278
+    (ref_pose_conversions.npz): theta = 0, the series region, near pi, and non-orthogonal input (polar factor)."""
+    import b200ba
+    d = load_golden("ref_pose_conversions.npz")
+    p = engine.pack_cameras(d["H"])
+    ang = np.linalg.norm(d["params"][:, :3], axis=1)
+    tol = np.where(ang > np.pi - 1e-3, 1e-7, 1e-11)       # at theta -> pi the axis sign / rounding of asin-like maps
+    same = np.abs(p - d["params"]).max(axis=1)
+    flipped = np.abs(p[:, :3] + d["params"][:, :3]).max(axis=1)   # theta = pi: w and -w are the same rotation
+    ok = (same <= tol) | ((ang > np.pi - 1e-6) & (flipped <= 1e-7))
+    assert ok.all(), (np.flatnonzero(~ok), same[~ok])
+    H = engine.unpack_cameras(d["params"])
+    assert np.abs(H[:, :3, :3] - d["R_back"]).max() <= 1e-14
+    assert np.array_equal(H[:, :3, 3], d["params"][:, 3:])
+    assert np.array_equal(H[:, 3], np.tile([0.0, 0.0, 0.0, 1.0], (len(H), 1)))
+    # round trip through the packer of the whole parameter vector
+    X = np.arange(30.0).reshape(10, 3)
+    x0 = b200ba.pack_parameters(d["H"][:8], X)
+    Hs, Xb = b200ba.unpack_parameters(x0, 8)
+    assert np.array_equal(Xb, X) and np.abs(Hs[:, :3, :3] - d["H"][:8, :3, :3]).max() <= 1e-13

@@ -125,3 +125,33 @@ def test_oracle_lm_with_fixed_camera(k):
     assert abs(lm["cost"] - float(g[f"lm_cost_{k}"])) <= 1e-6 * float(g[f"lm_cost_{k}"])
     assert lm["cost"] <= float(g[f"cost_{k}"]) * (1 + 1e-6)
     assert float(g[f"moved_{k}"]) <= 1e-9     # scipy, too, left the camera where it was
+
+
+def test_pose_conversion_oracle_vs_golden():
+    """oracle.pack_cameras / unpack_cameras (sfm.py:252-257 / 273-278 through scipy Rotation) against the frozen vectors;
+    guards against a scipy on the test machine that converts differently from the one the goldens were made with."""
+    d = load_golden("ref_pose_conversions.npz")
+    p = O.pack_cameras(d["H"])
+    assert np.abs(p - d["params"]).max() <= 1e-12
+    Hb = O.unpack_cameras(d["params"])
+    assert np.abs(Hb[:, :3, :3] - d["R_back"]).max() <= 1e-14
+    assert np.array_equal(Hb[:, :3, 3], d["params"][:, 3:])
+
+
+def test_gather_observations_matches_reference_iteration():
+    """b200ba.gather_observations against a literal restatement of Graph.pt3ds_pt2ds (graph.py:186-191) + the index
+    remapping of sfm.py:248-256 on a small random track set (host logic only)."""
+    import b200ba
+    rng = np.random.default_rng(3)
+    n_pts, cam_ids = 50, [2, 3, 5, 8, 9, 11]
+    registered = [3, 9, 2, 11]
+    tracks = [[(int(c), int(rng.integers(0, 999)), int(rng.integers(0, 2000)), int(rng.integers(0, 1500)))
+               for c in rng.choice(cam_ids, size=int(rng.integers(2, 5)), replace=False)] for _ in range(n_pts)]
+    data = [(idx, cam_id, np.array([x, y])) for idx in range(n_pts) for cam_id, _, x, y in tracks[idx] if cam_id in registered]
+    pt_indices, cam_indices, pt2ds = map(np.array, zip(*data))                      # sfm.py:248-249
+    camera_map = {c: i for i, c in enumerate(sorted(registered))}                     # node order = ascending id
+    camera_indices = np.array([camera_map[c] for c in cam_indices])                   # sfm.py:256
+    flat = [(idx, c, x, y) for idx in range(n_pts) for c, _, x, y in tracks[idx]]
+    tp, tc, tx, ty = map(np.array, zip(*flat))
+    ci, pi, uv = b200ba.gather_observations(tp, tc, np.stack([tx, ty], 1), registered)
+    assert np.array_equal(ci, camera_indices) and np.array_equal(pi, pt_indices) and np.array_equal(uv, pt2ds)
