@@ -169,6 +169,15 @@ int b200ba_set_two_level(b200ba_handle* h, int mode);
 
 /* Replaces scipy.optimize.least_squares at sfm.py:266-268: Levenberg-Marquardt on x_inout (host). */
 int b200ba_solve(b200ba_handle* h, double* x_inout, const b200ba_options* opt, b200ba_result* out);
+/* Page-locked host memory for result / input buffers (cudaHostAlloc): device <-> host copies of the parameter
+ * vector (96 MB at config D) run at link speed instead of through the driver's staging copies.  The host mirror keeps
+ * a free list of these and wraps them in numpy arrays that own them. */
+void* b200ba_host_alloc(int64_t bytes);
+void b200ba_host_free(void* p);
+
+/* b200ba_solve with separate input and output buffers (x_in is only read: a pinned caller buffer is uploaded
+ * without a staging copy, and the host mirror need not duplicate x0 before the call). */
+int b200ba_solve_io(b200ba_handle* h, const double* x_in, double* x_out, const b200ba_options* opt, b200ba_result* out);
 /* same with x resident on the device */
 int b200ba_solve_dev(b200ba_handle* h, double* x_inout_dev, const b200ba_options* opt, b200ba_result* out);
 

@@ -65,6 +65,9 @@ SIGNATURES = {
     "b200ba_linearize_dev": (C.c_int, [_P, _P, C.c_double]),
     "b200ba_lm_step": (C.c_int, [_P, _P, C.c_double, C.c_int, _P, _D, _D]),
     "b200ba_solve": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
+    "b200ba_host_alloc": (_P, [C.c_int64]),
+    "b200ba_host_free": (None, [_P]),
+    "b200ba_solve_io": (C.c_int, [_P, _P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_solve_dev": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_set_two_level": (C.c_int, [_P, C.c_int]),
     "b200ba_set_fixed_cameras": (C.c_int, [_P, _P, C.c_int64]),

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import os
+import weakref
 
 import numpy as np
 
@@ -41,6 +42,37 @@ def default_device():
     return int(os.environ.get("LOCAL_RANK", "0"))
 
 
+class _PinnedPool:
+    """Free list of page-locked host buffers (``b200ba_host_alloc``) handed out as numpy arrays that OWN them: when the
+    last view of an array dies its buffer returns to the list, so a steady stream of solves allocates nothing and the
+    result download runs at link speed.  Small results use ordinary memory."""
+
+    MIN_BYTES = 1 << 20
+    MAX_CACHED = 4
+
+    def __init__(self, lib):
+        self.lib, self.free = lib, {}
+
+    def empty(self, n):
+        nbytes = 8 * int(n)
+        if nbytes < self.MIN_BYTES:
+            return np.empty(int(n), dtype=np.float64)
+        lst = self.free.get(nbytes)
+        ptr = lst.pop() if lst else self.lib.b200ba_host_alloc(nbytes)
+        if not ptr:
+            return np.empty(int(n), dtype=np.float64)
+        buf = (C.c_double * int(n)).from_address(ptr)
+        weakref.finalize(buf, self._release, nbytes, ptr)
+        return np.frombuffer(buf, dtype=np.float64)
+
+    def _release(self, nbytes, ptr):
+        lst = self.free.setdefault(nbytes, [])
+        if len(lst) < self.MAX_CACHED:
+            lst.append(ptr)
+        else:
+            self.lib.b200ba_host_free(C.c_void_p(ptr))
+
+
 class Engine:
     """One GPU's handle (``b200ba_handle``): problem upload, residual/Jacobian/normal equations, LM solve."""
 
@@ -53,6 +85,7 @@ class Engine:
             raise BAError(f"b200ba_create(device={self.device}) failed: {_lib.STATUS.get(rc, rc)} "
                           "(a CUDA device is required; there is no CPU fallback)")
         self.h = h
+        self._pinned = _PinnedPool(self.lib)
         self.n_cam = self.n_pts = self.n_obs = 0
         self.fixed = ()
         self.rank, self.nranks = 0, 1
@@ -199,10 +232,11 @@ class Engine:
 
     def solve(self, x0, **kw):
         """LM on host ``x0``; returns (x, Result)."""
-        x = self._x(x0).copy()
+        xin = self._x(x0)
+        x = self._pinned.empty(xin.size)
         o = self.make_options(**kw)
         res = _lib.Result()
-        self._check(self.lib.b200ba_solve(self.h, _ptr(x), C.byref(o), C.byref(res)))
+        self._check(self.lib.b200ba_solve_io(self.h, _ptr(xin), _ptr(x), C.byref(o), C.byref(res)))
         return x, res
 
     # -- device-pointer variants (torch tensors are only carriers of device memory)

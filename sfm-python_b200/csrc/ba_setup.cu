@@ -184,6 +184,20 @@ __global__ void k_tile_ent_off(int n_st, int n_ent, const long long* __restrict_
   off[t] = lo;
 }
 
+// tile of every point: the last CTA tile whose first observation is <= the point's first observation
+__global__ void k_pt_tile(int P, const int* __restrict__ pt_off, const int* __restrict__ st_off, int n_st,
+                          int* __restrict__ pt_tile) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const int i = pt_off[p];
+  int lo = 0, hi = n_st;
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (st_off[mid] <= i) lo = mid; else hi = mid;
+  }
+  pt_tile[p] = lo;
+}
+
 __global__ void k_pack_entries(long long n, const long long* __restrict__ ent64, const int* __restrict__ st_off,
                                int n_st, unsigned* __restrict__ tent) {
   long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -472,16 +486,17 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
 
   mark("2 point-major order");
   // ---- 3. warp tiles (host greedy packing of whole points into <= 32 observations)
-  std::vector<int> h_pt_off(P + 1, 0), h_pt_tile;
+  std::vector<int> h_pt_off(P + 1, 0);
   BA_CUDA(h, cudaMemcpyAsync(h_pt_off.data(), pb.pt_off, (P + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
   BA_CUDA(h, cudaStreamSynchronize(st));
   {
     std::vector<int> wt;
     wt.reserve(N / 24 + 16);
     wt.push_back(0);
-    int start = 0;
+    int start = 0, max_deg = 0;
     for (int64_t p = 0; p < P; ++p) {
       int e = h_pt_off[p + 1];
+      max_deg = std::max(max_deg, e - h_pt_off[p]);
       if (e - start > 32) {
         if (h_pt_off[p] > start) wt.push_back(h_pt_off[p]);  // close the tile before this point
         start = wt.back();
@@ -492,8 +507,6 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     pb.n_wt = (int)wt.size() - 1;
     if (int rc = upload(h, &pb.wt_off, wt)) return rc;
     // CTA tiles: runs of warp tiles (whole points) with at most tile_obs observations (records fit shared memory)
-    int max_deg = 0;
-    for (int64_t p = 0; p < P; ++p) max_deg = std::max(max_deg, h_pt_off[p + 1] - h_pt_off[p]);
     const char* e_fused = getenv("B200BA_FUSED");        // 0: unfused A/B path (k_lin_points + k_cam_side + k_schur_tiles)
     const char* e_tile = getenv("B200BA_TILE_OBS");      // tuning sweeps
     const bool want_fused = !(e_fused && atoi(e_fused) == 0);
@@ -520,12 +533,6 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
         pb.fused = want_fused;
         if (int rc = upload(h, &pb.st_off, stv)) return rc;
         if (int rc = upload(h, &pb.st_wt_off, stw)) return rc;
-        h_pt_tile.assign(P, 0);
-        int t = 0;
-        for (int64_t p = 0; p < P; ++p) {
-          while (t + 1 < pb.n_st && h_pt_off[p] >= stv[t + 1]) ++t;
-          h_pt_tile[p] = t;
-        }
       }
     }
   }
@@ -573,7 +580,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   if (pb.schur_tiles) {
     d_pt_tile = (int*)tmp.get(std::max<size_t>(P, 1) * sizeof(int));
     if (!d_pt_tile) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
-    if (P > 0) BA_CUDA(h, cudaMemcpyAsync(d_pt_tile, h_pt_tile.data(), P * sizeof(int), cudaMemcpyHostToDevice, st));
+    if (P > 0) k_pt_tile<<<nblk(P, T), T, 0, st>>>((int)P, pb.pt_off, pb.st_off, pb.n_st, d_pt_tile);
   }
   TMP_ALLOC(d_cnt, long long, P + 1);
   TMP_ALLOC(d_ent_off, long long, P + 1);

@@ -374,13 +374,16 @@ __device__ __forceinline__ void tl_local(const Pcg2Args& g, double* sm, bool fir
 __device__ __forceinline__ void tl_coarse(const Pcg2Args& g, int gwarp, int gwarps, int lane, bool ok) {
   const double2* rc2 = reinterpret_cast<const double2*>(g.rc);
   const int n2 = g.ncp >> 1;
-  for (int i = gwarp; i < g.nc; i += gwarps) {
+  const int wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  // rows dealt round-robin over the CTAs first (every SM gets its share), then over the warps of a CTA
+  for (int i = blockIdx.x + gridDim.x * wid; i < g.nc; i += gridDim.x * nw) {
     if (!ok) { if (lane == 0) g.zc[i] = 0.0; continue; }   // no valid coarse inverse: plain block-Jacobi
     const double2* row = reinterpret_cast<const double2*>(g.Ainv + (int64_t)i * g.ncp);
     double s0 = 0.0, s1 = 0.0;
 #pragma unroll 8
     for (int j = lane; j < n2; j += 32) {
-      const double2 av = row[j], rv = rc2[j];
+      const double2 av = __ldcs(row + j);   // streamed once per iteration: evict-first, S keeps its place in L2
+      const double2 rv = rc2[j];
       s0 = fma(av.x, rv.x, s0); s1 = fma(av.y, rv.y, s1);
     }
     const double s = warp_sum(s0 + s1);
@@ -484,9 +487,15 @@ __global__ void __launch_bounds__(PCG_T, 3) k_pcg2(Pcg2Args g) {
     if (!(del > 0.0)) fail = 1;
     else alpha = gam / del;
   }
+  // phase timers (thread 0 of CTA 0, globaltimer): compiled in only with -DB200BA_TL_PROF (make EXTRA=-DB200BA_TL_PROF);
+  // they cost ~15 % of an iteration (measured), so the shipped kernel carries none
+#ifdef B200BA_TL_PROF
   unsigned long long tq[7];
   double pacc[6] = {0, 0, 0, 0, 0, 0};
 #define TL_STAMP(k) if (gtid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tq[k]))
+#else
+#define TL_STAMP(k)
+#endif
   while (!fail && it < a.max_iter && rr > thresh && bb > 0.0) {
     double gam_new = 0.0, rr_new = 0.0, del_part = 0.0;
     TL_STAMP(0);
@@ -503,9 +512,11 @@ __global__ void __launch_bounds__(PCG_T, 3) k_pcg2(Pcg2Args g) {
     TL_STAMP(5);
     grid_sum3(grid, a.part, phase, sm, gam_new, del_part, rr_new, d0, d1, d2);
     TL_STAMP(6);
+#ifdef B200BA_TL_PROF
     if (gtid == 0)
 #pragma unroll
       for (int k = 0; k < 6; ++k) pacc[k] += (double)(tq[k + 1] - tq[k]);
+#endif
     gam_new = d0; del = d1; rr = d2;
     if (!(rr > thresh)) break;
     beta = gam_new / gam;
@@ -521,9 +532,11 @@ __global__ void __launch_bounds__(PCG_T, 3) k_pcg2(Pcg2Args g) {
     a.scal[S_DC_RES] = d0;
     a.scal[S_PCG_ITERS] = (double)it;
     a.scal[S_SOLVE_FAIL] = (double)fail;
+#ifdef B200BA_TL_PROF
 #pragma unroll
     for (int k = 0; k < 6; ++k) g.prof[k] += pacc[k];
     g.prof[6] += (double)it;
+#endif
   }
 #undef TL_STAMP
 }
