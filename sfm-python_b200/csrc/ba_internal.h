@@ -124,11 +124,13 @@ struct Problem {
   uint4* blob = nullptr;         // header(32 B) | pair slots (a, n) | self slots (a, n) | pair entries u32 | self entries u16
   unsigned char* cam_fixed = nullptr;  // [C] 1 = held fixed (b200ba_set_fixed_cameras); null = none
   int n_fixed = 0;
-  // two-level preconditioner (k_twolevel.cuh): aggregates = contiguous camera runs, 7 coarse unknowns each
+  // two-level preconditioner (k_twolevel.cuh): aggregates = connected groups of cameras, 7 coarse unknowns each
   bool tl = false;
   int n_agg = 0, nc = 0, ncp = 0;  // nc = 7 n_agg, ncp = nc rounded up to a multiple of 64
   int* cam_agg = nullptr;          // [C]
-  int* agg_off = nullptr;          // [n_agg+1]
+  int* agg_off = nullptr;          // [n_agg+1] ranges into agg_cams
+  int* agg_cams = nullptr;         // [C] cameras grouped by aggregate (ascending inside one)
+  int* sp_of = nullptr;            // [nnzb] block of S P that block q of the BSR view of S contributes to
   int* sp_rowptr = nullptr;        // [C+1] block-CSR structure of S P (6 x 7 blocks)
   int* sp_col = nullptr;           // [nnz_sp] aggregate of each block
   int nnz_sp = 0;

@@ -794,7 +794,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     if (int rc = upload(h, &pb.bsr_rowptr, rowptr)) return rc;
     if (int rc = upload(h, &pb.bsr_col, col)) return rc;
     if (int rc = upload(h, &pb.bsr_src, src)) return rc;
-    // two-level preconditioner (k_twolevel.cuh): aggregates = contiguous camera runs; block structure of S P
+    // two-level preconditioner (k_twolevel.cuh): camera aggregates and the block structure of S P
     const char* e_tl = getenv("B200BA_TWOLEVEL");   // 0: block-Jacobi only
     const char* e_agg = getenv("B200BA_AGG");       // cameras per aggregate (default max(16, C / 320))
     if (C >= 128 && !(e_tl && atoi(e_tl) == 0)) {
@@ -803,24 +803,103 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       int n_agg = (int)((C + per - 1) / per);
       if (n_agg > 1 && C - (int64_t)(n_agg - 1) * per < 2) --n_agg;   // a one-camera aggregate has only 6 free motions
       if ((int64_t)n_agg * 7 <= 3584) {
-        std::vector<int> cam_agg(C), agg_off(n_agg + 1), sp_rowptr(C + 1, 0), sp_col;
-        for (int64_t c = 0; c < C; ++c) cam_agg[c] = (int)std::min<int64_t>(c / per, n_agg - 1);
-        for (int I = 0; I < n_agg; ++I) agg_off[I] = I * per;
-        agg_off[n_agg] = (int)C;
-        for (int64_t c = 0; c < C; ++c) {
-          int cur = -1;
-          for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) {
-            const int J = cam_agg[col[q]];
-            if (J != cur) { sp_col.push_back(J); cur = J; }
+        // Aggregates = connected groups of about `per` cameras of the graph of S (block (i, j) present <=> the two cameras
+        // share a point), grown greedily from the lowest unassigned camera by strongest connection to the group.  On
+        // an ordered sequence this gives index runs; on an arbitrary camera numbering (incremental SfM registers cameras
+        // in match order) it still groups cameras that see the same points, which is what makes a locally rigid motion
+        // cheap.  Groups smaller than half the target are merged into the neighbouring aggregate they touch most.
+        std::vector<int> cam_agg(C, -1);
+        std::vector<int> agg_size;
+        {
+          // greedy growth: repeatedly add the unassigned camera with the most blocks of S into the aggregate so far
+          // (ties: lowest index) -- on a sequence this walks outwards from the seed, whatever the numbering
+          std::vector<int> score(C, 0), cand;
+          for (int64_t seed = 0; seed < C; ++seed) {
+            if (cam_agg[seed] >= 0) continue;
+            const int I = (int)agg_size.size();
+            cand.clear();
+            int size = 0, next = (int)seed;
+            while (next >= 0) {
+              cam_agg[next] = I;
+              ++size;
+              for (int q = rowptr[next]; q < rowptr[next + 1]; ++q) {
+                const int j = col[q];
+                if (cam_agg[j] >= 0) continue;
+                if (score[j]++ == 0) cand.push_back(j);
+              }
+              next = -1;
+              if (size >= per) break;
+              int best = -1;
+              for (size_t k = 0; k < cand.size(); ++k) {
+                const int j = cand[k];
+                if (cam_agg[j] >= 0) continue;
+                if (best < 0 || score[j] > score[best] || (score[j] == score[best] && j < best)) best = j;
+              }
+              next = best;
+            }
+            for (int j : cand) score[j] = 0;
+            agg_size.push_back(size);
           }
+          // merge fragments (a one-camera aggregate has only 6 free motions for 7 coarse unknowns)
+          const int n0 = (int)agg_size.size();
+          std::vector<int> target(n0);
+          for (int I = 0; I < n0; ++I) target[I] = I;
+          if (n0 > 1) {
+            std::vector<int> votes(n0);
+            for (int I = 0; I < n0; ++I) {
+              if (agg_size[I] * 2 >= per) continue;
+              std::fill(votes.begin(), votes.end(), 0);
+              for (int64_t c = 0; c < C; ++c)
+                if (cam_agg[c] == I)
+                  for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) {
+                    int J = cam_agg[col[q]];
+                    while (target[J] != J) J = target[J];
+                    if (J != I) votes[J]++;
+                  }
+              int best = -1;
+              for (int J = 0; J < n0; ++J) if (votes[J] > 0 && (best < 0 || votes[J] > votes[best])) best = J;
+              if (best < 0 && agg_size[I] < 2) best = (I > 0) ? I - 1 : 1;   // isolated camera: any partner
+              if (best >= 0) {
+                while (target[best] != best) best = target[best];
+                if (best != I) { target[I] = best; agg_size[best] += agg_size[I]; agg_size[I] = 0; }
+              }
+            }
+          }
+          std::vector<int> renum(n0, -1);
+          int n_new = 0;
+          for (int I = 0; I < n0; ++I) { int J = I; while (target[J] != J) J = target[J]; if (renum[J] < 0) renum[J] = n_new++; }
+          for (int64_t c = 0; c < C; ++c) { int J = cam_agg[c]; while (target[J] != J) J = target[J]; cam_agg[c] = renum[J]; }
+          n_agg = n_new;
+        }
+        if ((int64_t)n_agg * 7 <= 3584) {
+        std::vector<int> agg_off(n_agg + 1, 0), agg_cams(C), sp_rowptr(C + 1, 0), sp_col, sp_of(pb.nnzb);
+        for (int64_t c = 0; c < C; ++c) agg_off[cam_agg[c] + 1]++;
+        for (int I = 0; I < n_agg; ++I) agg_off[I + 1] += agg_off[I];
+        {
+          std::vector<int> fill(agg_off.begin(), agg_off.end() - 1);
+          for (int64_t c = 0; c < C; ++c) agg_cams[fill[cam_agg[c]]++] = (int)c;   // ascending camera index inside an aggregate
+        }
+        std::vector<int> rowJ;
+        for (int64_t c = 0; c < C; ++c) {
+          rowJ.clear();
+          for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) rowJ.push_back(cam_agg[col[q]]);
+          std::sort(rowJ.begin(), rowJ.end());
+          rowJ.erase(std::unique(rowJ.begin(), rowJ.end()), rowJ.end());
+          const int base = (int)sp_col.size();
+          for (int q = rowptr[c]; q < rowptr[c + 1]; ++q)
+            sp_of[q] = base + (int)(std::lower_bound(rowJ.begin(), rowJ.end(), cam_agg[col[q]]) - rowJ.begin());
+          sp_col.insert(sp_col.end(), rowJ.begin(), rowJ.end());
           sp_rowptr[c + 1] = (int)sp_col.size();
         }
         pb.n_agg = n_agg; pb.nc = 7 * n_agg; pb.ncp = (pb.nc + 63) / 64 * 64; pb.nnz_sp = (int)sp_col.size();
         if (int rc = upload(h, &pb.cam_agg, cam_agg)) return rc;
         if (int rc = upload(h, &pb.agg_off, agg_off)) return rc;
+        if (int rc = upload(h, &pb.agg_cams, agg_cams)) return rc;
         if (int rc = upload(h, &pb.sp_rowptr, sp_rowptr)) return rc;
         if (int rc = upload(h, &pb.sp_col, sp_col)) return rc;
+        if (int rc = upload(h, &pb.sp_of, sp_of)) return rc;
         pb.tl = true;
+        }
       }
     }
   }

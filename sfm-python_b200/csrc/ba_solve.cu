@@ -486,7 +486,8 @@ static TlArgs tl_args(Handle* h) {
   Work& w = h->w;
   TlArgs a;
   a.C = (int)pb.C; a.n_agg = pb.n_agg; a.nc = pb.nc; a.ncp = pb.ncp; a.Cs = pb.Cs;
-  a.cam_agg = pb.cam_agg; a.agg_off = pb.agg_off; a.sp_rowptr = pb.sp_rowptr; a.sp_col = pb.sp_col;
+  a.cam_agg = pb.cam_agg; a.agg_off = pb.agg_off; a.agg_cams = pb.agg_cams;
+  a.sp_rowptr = pb.sp_rowptr; a.sp_col = pb.sp_col; a.sp_of = pb.sp_of;
   a.rowptr = pb.bsr_rowptr; a.col = pb.bsr_col; a.src = pb.bsr_src;
   a.Sup = w.Sup; a.camprep = w.camprep; a.fixed = pb.cam_fixed;
   a.G = w.tl_G; a.SP = w.tl_SP; a.A = w.tl_A; a.cb = w.tl_cb; a.rb = w.tl_rb; a.dsc = w.tl_dsc; a.cen = w.tl_cen;
@@ -536,7 +537,7 @@ int launch_pcg2(Handle* h, double rtol, int max_iter) {
   a.Minv = w.pcg + 5 * n;
   a.part = w.pcg_part; a.scal = w.scal; a.rtol = rtol; a.max_iter = max_iter;
   g.n_agg = pb.n_agg; g.nc = pb.nc; g.ncp = pb.ncp;
-  g.cam_agg = pb.cam_agg; g.agg_off = pb.agg_off; g.sp_rowptr = pb.sp_rowptr; g.sp_col = pb.sp_col;
+  g.cam_agg = pb.cam_agg; g.agg_off = pb.agg_off; g.agg_cams = pb.agg_cams; g.sp_rowptr = pb.sp_rowptr; g.sp_col = pb.sp_col;
   g.G = w.tl_G; g.SP = w.tl_SP; g.Ainv = w.tl_A; g.rc = w.tl_rc; g.zc = w.tl_zc; g.uf = w.tl_uf; g.prof = w.tl_prof;
   void* args[] = {&g};
   int per_sm = 0;

@@ -5,7 +5,8 @@
 // rotation, translation, scale) and every locally-rigid similarity motion of a group of neighbouring cameras is nearly
 // free as well.  The coarse space is spanned by exactly those motions:
 //
-//   aggregates   contiguous runs of cameras (ba_setup.cu); 7 coarse unknowns (phi, t, sigma) per aggregate
+//   aggregates   connected groups of cameras of the graph of S, grown greedily (ba_setup.cu; index runs on an
+//                ordered sequence); 7 coarse unknowns (phi, t, sigma) per aggregate
 //   G_c (6 x 7)  d(w_c, T_c) / d(phi, t, sigma) for a similarity about the aggregate's centroid:
 //                dw = -J_r(w)^-1 phi,   dT = phi x (T - Tbar) + t + sigma (T - Tbar)
 //   P            block column of the G_c of one aggregate;   A_c = P^T S P   (dense, 7 n_agg square)
@@ -26,8 +27,8 @@ constexpr int GJ_T = 256;
 struct TlArgs {
   int C, n_agg, nc, ncp;          // ncp = nc rounded up to a multiple of GJ_TILE (padding rows/cols = identity)
   int64_t Cs;
-  const int* cam_agg; const int* agg_off;
-  const int* sp_rowptr; const int* sp_col;
+  const int* cam_agg; const int* agg_off; const int* agg_cams;
+  const int* sp_rowptr; const int* sp_col; const int* sp_of;
   const int* rowptr; const int* col; const int* src;   // block-CSR view of S (both triangles)
   const double* Sup; const double* camprep;
   const unsigned char* fixed;      // nullable: cameras held fixed get G_c = 0 (the coarse correction must not move them)
@@ -42,7 +43,8 @@ __global__ void __launch_bounds__(64) k_tl_gauge(TlArgs a) {
   const int c0 = a.agg_off[I], c1 = a.agg_off[I + 1];
   if (threadIdx.x < 32) {
     double s0 = 0, s1 = 0, s2 = 0;
-    for (int c = c0 + threadIdx.x; c < c1; c += 32) {
+    for (int k = c0 + threadIdx.x; k < c1; k += 32) {
+      const int c = a.agg_cams[k];
       s0 += a.camprep[18 * a.Cs + c]; s1 += a.camprep[19 * a.Cs + c]; s2 += a.camprep[20 * a.Cs + c];
     }
     s0 = warp_sum(s0); s1 = warp_sum(s1); s2 = warp_sum(s2);
@@ -53,7 +55,8 @@ __global__ void __launch_bounds__(64) k_tl_gauge(TlArgs a) {
     }
   }
   __syncthreads();
-  for (int c = c0 + threadIdx.x; c < c1; c += 64) {
+  for (int k = c0 + threadIdx.x; k < c1; k += 64) {
+    const int c = a.agg_cams[k];
     double J[9];
 #pragma unroll
     for (int k = 0; k < 9; ++k) J[k] = a.camprep[(int64_t)(9 + k) * a.Cs + c];
@@ -86,41 +89,32 @@ __global__ void __launch_bounds__(64) k_tl_gauge(TlArgs a) {
 }
 
 // ------------------------------------------------------------------ SP = S P, one warp per block row of S
-// Output block (c, J) = sum over the row's blocks S_cj with agg(j) = J of S_cj G_j; columns are ascending and the
-// aggregates are contiguous camera runs, so the blocks of one J are consecutive.  Lane o (and o + 32 < 42) owns
-// output element o = r * 7 + m.
+// Output block e = (c, J) = sum over the row's blocks S_cj with agg(j) = J of S_cj G_j, in column order (sp_of[q] names
+// the output block of BSR entry q; the aggregates need not be index runs).  Lane o (and o + 32 < 42) owns output
+// element o = r * 7 + m.
 __global__ void __launch_bounds__(256) k_tl_sp(TlArgs a) {
   const int lane = threadIdx.x & 31;
   const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (c >= a.C) return;
   const int o0 = lane, o1 = lane + 32;
   const int r0 = o0 / 7, m0 = o0 % 7, r1 = (o1 < TL_GS ? o1 : 0) / 7, m1 = (o1 < TL_GS ? o1 : 0) % 7;
-  int e = a.sp_rowptr[c];
-  int curJ = -1;
-  double acc0 = 0.0, acc1 = 0.0;
-  for (int q = a.rowptr[c]; q < a.rowptr[c + 1]; ++q) {
-    const int j = a.col[q], s = a.src[q];
-    const int J = a.cam_agg[j];
-    if (J != curJ) {
-      if (curJ >= 0) {
-        a.SP[(int64_t)e * TL_GS + o0] = acc0;
-        if (o1 < TL_GS) a.SP[(int64_t)e * TL_GS + o1] = acc1;
-        ++e;
-      }
-      curJ = J; acc0 = 0.0; acc1 = 0.0;
-    }
-    const double* B = a.Sup + (int64_t)(s & 0x7fffffff) * 36;
-    const double* G = a.G + (int64_t)j * TL_GS;
-    const bool tr = s < 0;
+  const int q0 = a.rowptr[c], q1 = a.rowptr[c + 1];
+  for (int e = a.sp_rowptr[c]; e < a.sp_rowptr[c + 1]; ++e) {
+    double acc0 = 0.0, acc1 = 0.0;
+    for (int q = q0; q < q1; ++q) {
+      if (a.sp_of[q] != e) continue;
+      const int j = a.col[q], s = a.src[q];
+      const double* B = a.Sup + (int64_t)(s & 0x7fffffff) * 36;
+      const double* G = a.G + (int64_t)j * TL_GS;
+      const bool tr = s < 0;
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      const double b0 = tr ? B[k * 6 + r0] : B[r0 * 6 + k];
-      const double b1 = tr ? B[k * 6 + r1] : B[r1 * 6 + k];
-      acc0 = fma(b0, G[k * 7 + m0], acc0);
-      acc1 = fma(b1, G[k * 7 + m1], acc1);
+      for (int k = 0; k < 6; ++k) {
+        const double b0 = tr ? B[k * 6 + r0] : B[r0 * 6 + k];
+        const double b1 = tr ? B[k * 6 + r1] : B[r1 * 6 + k];
+        acc0 = fma(b0, G[k * 7 + m0], acc0);
+        acc1 = fma(b1, G[k * 7 + m1], acc1);
+      }
     }
-  }
-  if (curJ >= 0) {
     a.SP[(int64_t)e * TL_GS + o0] = acc0;
     if (o1 < TL_GS) a.SP[(int64_t)e * TL_GS + o1] = acc1;
   }
@@ -143,7 +137,8 @@ __global__ void __launch_bounds__(256) k_tl_assemble(TlArgs a) {
   for (int i = tid; i < TL_K * ncp; i += blockDim.x) row[i] = 0.0;
   __syncthreads();
   const int el = tid / 49, o = tid % 49, ra = o / 7, cb = o % 7;   // 5 entries x 49 outputs at a time
-  for (int c = a.agg_off[I]; c < a.agg_off[I + 1]; ++c) {
+  for (int kc = a.agg_off[I]; kc < a.agg_off[I + 1]; ++kc) {
+    const int c = a.agg_cams[kc];
     const double* G = a.G + (int64_t)c * TL_GS;
     const int e0 = a.sp_rowptr[c], e1 = a.sp_rowptr[c + 1];
     for (int eb = e0; eb < e1; eb += 5) {
@@ -302,7 +297,7 @@ __global__ void __launch_bounds__(GJ_T) k_tl_gj(TlArgs a) {
 struct Pcg2Args {
   PcgArgs p;
   int n_agg, nc, ncp;
-  const int* cam_agg; const int* agg_off; const int* sp_rowptr; const int* sp_col;
+  const int* cam_agg; const int* agg_off; const int* agg_cams; const int* sp_rowptr; const int* sp_col;
   const double* G; const double* SP; const double* Ainv;
   double* rc; double* zc; double* uf;
   double* prof;   // [8] nanoseconds per phase, accumulated by thread 0 of CTA 0 (local, sync, coarse, sync, spmv, reduce)
@@ -321,9 +316,9 @@ __device__ __forceinline__ void tl_local(const Pcg2Args& g, double* sm, bool fir
 #pragma unroll
     for (int m = 0; m < TL_K; ++m) t[m] = 0.0;
     for (int c5 = c0 + wid * 5; c5 < c1; c5 += nw * 5) {
-      const int c = c5 + kq;
-      const bool on = lane < 30 && c < c1;
-      const int i = 6 * (on ? c : c0) + comp;
+      const bool on = lane < 30 && c5 + kq < c1;
+      const int c = g.agg_cams[on ? c5 + kq : c0];
+      const int i = 6 * c + comp;
       double rk = 0.0;
       if (on) {
         if (first) {
@@ -340,7 +335,7 @@ __device__ __forceinline__ void tl_local(const Pcg2Args& g, double* sm, bool fir
         rr_acc += rk * rk;
       }
       double tu = 0.0;
-      const double* mrow = a.Minv + (int64_t)(on ? c : c0) * 36 + comp * 6;
+      const double* mrow = a.Minv + (int64_t)c * 36 + comp * 6;
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
         const double rj = __shfl_sync(FULL, rk, 6 * kq + k);

@@ -83,6 +83,11 @@ class DistributedBA:
         ci, pil, uv, _ = local_problem(camera_indices, point_indices, points_2d, lo, hi)
         return self.set_local_problem(n_cam, n_pts, (lo, hi), ci, pil, uv, K)
 
+    def set_fixed_cameras(self, indices=()):
+        """Hold these cameras fixed on every rank (``fixed_camera_indices`` of ``bundle_adjustment.py:6``)."""
+        self.engine.set_fixed_cameras(indices)
+        return self
+
     def solve_local(self, x_local, **kw):
         """Collective LM; ``x_local`` = cameras + this shard's points. Returns (x_local, Result)."""
         return self.engine.solve(x_local, **kw)
