@@ -148,11 +148,15 @@ static int alloc_work(Handle* h) {
   WALLOC(w.camprep, (C + 2) * CAMPREP_STRIDE);   // field-major [21][Cs], Cs <= C + 1
   WALLOC(w.camprep_n, (C + 2) * CAMPREP_STRIDE);
   WALLOC(w.cstep, (C + 2) * 6);
-  WALLOC(w.Y, N * 18);
-  WALLOC(w.rr, N * 4);
+  // Y: 18 N doubles for the unfused pipeline (per-observation W L^-T blocks); the fused kernels keep those records in
+  // shared memory, so only a 2 N staging area (residuals / reprojection errors in the caller's order) is held and the
+  // Jacobian-block export grows it on demand (ensure_Y).  rr / cpart belong to the unfused pipeline only.
+  w.Y_count = pb.fused ? std::max<int64_t>(2 * N, 16 * 16 * (int64_t)h->sm_count) : 18 * N;
+  WALLOC(w.Y, w.Y_count);
+  if (!pb.fused) { WALLOC(w.rr, N * 4); }
   WALLOC(w.pp, P * 12);
   WALLOC(w.gp, P * 3);
-  WALLOC(w.cpart, (int64_t)pb.n_cch * 33);
+  if (!pb.fused) { WALLOC(w.cpart, (int64_t)pb.n_cch * 33); }
   WALLOC(w.spart, (int64_t)std::max(pb.n_sch, pb.n_slot) * 36);
   WALLOC(w.U, C * 21);
   WALLOC(w.dpart, (int64_t)pb.n_dslot * 40);
@@ -203,6 +207,16 @@ static int alloc_work(Handle* h) {
     BA_CUDA(h, cudaMemsetAsync(w.tl_prof, 0, 8 * sizeof(double), st));
   }
   BA_CUDA(h, cudaStreamSynchronize(st));
+  return 0;
+}
+
+int ensure_Y(Handle* h, int64_t count) {
+  Work& w = h->w;
+  if (w.Y_count >= count) return 0;
+  double* p = (double*)dalloc(h, (size_t)std::max<int64_t>(count, 1) * sizeof(double));
+  if (!p) return B200BA_OOM;
+  w.Y = p;   // the smaller block stays on the handle's list until the problem is released
+  w.Y_count = count;
   return 0;
 }
 

@@ -147,7 +147,8 @@ struct Work {
   double* camprep = nullptr;  // [C*24]
   double* camprep_n = nullptr;
   double* cstep = nullptr;    // [6][Cs] per-camera part of the back-substitution: J_r dw, dT
-  double* Y = nullptr;        // [N*18]
+  double* Y = nullptr;        // [Y_count] 18 N (unfused pipeline / Jacobian export) or a 2 N staging area
+  int64_t Y_count = 0;
   double* rr = nullptr;       // [N*4]  r0 r1 rt0 rt1
   double* pp = nullptr;       // [P*12] Linv(6) z(3) diagV(3)
   double* gp = nullptr;       // [P*3]
@@ -218,6 +219,7 @@ struct Handle {
 
 // ---- helpers (ba_engine.cu)
 int fail(Handle* h, int code, const std::string& msg);
+int ensure_Y(Handle* h, int64_t count);  // grow w.Y (staging / Jacobian export)
 int cuda_fail(Handle* h, cudaError_t e, const char* where);
 void* dalloc(Handle* h, size_t bytes);  // nullptr on failure (h->err set)
 void* pool_alloc(Handle* h, size_t bytes);  // raw stream-ordered allocation from h->pool (nullptr on failure)
