@@ -59,7 +59,8 @@ typedef struct b200ba_options {
   int32_t solver;         /* b200ba_solver */
   double lambda0;         /* initial Marquardt damping, <= 0 -> 1e-4 */
   double pcg_rtol;        /* relative residual of the reduced-camera PCG; <= 0 -> inexact-Newton forcing term chosen by
-                             the LM loop (0.1, tightened to 1e-2 once the relative cost reduction drops below 1e-4) */
+                             the LM loop (0.3 with the two-level preconditioner, 0.1 with block-Jacobi; tightened to 0.1 /
+                             1e-2 once the relative cost reduction drops below 1e-4; 1e-8 for <= 100 cameras) */
   int32_t pcg_max_iter;   /* <= 0 -> 500 */
   int32_t fixed_iters;    /* > 0: run exactly this many LM iterations, ignoring the tolerances (benchmarks) */
 } b200ba_options;
