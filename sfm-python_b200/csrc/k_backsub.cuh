@@ -44,7 +44,7 @@ __device__ __forceinline__ void jc_dc_jp(const double* Jc, const double* Jp, con
   s3[2] = Jp[2] * t0 + Jp[5] * t1;
 }
 
-__global__ void __launch_bounds__(LIN_WARPS * 32)
+__global__ void __launch_bounds__(LIN_WARPS * 32, 4)
 k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ xn, const double* __restrict__ camprep,
                 const double* __restrict__ camprep_n, const double* __restrict__ cstep, const double* __restrict__ pp,
                 double* __restrict__ part) {
