@@ -135,6 +135,147 @@ int comm_allgather_f64(Handle* h, const double* send, double* recv, int64_t coun
   return rc ? nccl_fail(h, rc, "ncclAllGather") : 0;
 }
 
+// ------------------------------------------------------------------ exchange through peer memory (see struct P2P)
+namespace {
+struct PeerPtrs { double* p[P2P_MAX_RANKS]; unsigned long long* f[P2P_MAX_RANKS]; };
+
+__global__ void __launch_bounds__(256) k_p2p_push(const double2* __restrict__ src, long long n2, int rank, int nranks,
+                                                  PeerPtrs peers, long long slot_off, unsigned long long epoch,
+                                                  unsigned int* __restrict__ done) {
+  // four 16-byte loads in flight per thread; the peer loop starts at the next rank so that at any moment the ranks
+  // write to different destinations
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < n2; i0 += 4 * stride) {
+    double2 v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] = (i0 + k * stride < n2) ? src[i0 + k * stride] : make_double2(0.0, 0.0);
+    for (int q = 1; q <= nranks; ++q) {
+      const int p = (rank + q) % nranks;
+      double2* dst = reinterpret_cast<double2*>(peers.p[p] + slot_off);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (i0 + k * stride < n2) dst[i0 + k * stride] = v[k];
+    }
+  }
+  __threadfence_system();   // this thread's stores are visible system-wide before the CTA is counted as done
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(done, 1u);
+    if (prev == gridDim.x - 1) {   // last CTA: every CTA's data is out -> publish the epoch on every rank
+      *done = 0;
+      __threadfence_system();
+      for (int p = 0; p < nranks; ++p)
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(peers.f[p] + rank), "l"(epoch) : "memory");
+    }
+  }
+}
+
+__global__ void k_p2p_wait(const unsigned long long* __restrict__ flags, int nranks, unsigned long long epoch,
+                           int* __restrict__ err) {
+  const int p = threadIdx.x;
+  if (p >= nranks) return;
+  const long long t0 = clock64();
+  unsigned long long v = 0;
+  while (true) {
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flags + p) : "memory");
+    if (v >= epoch) break;
+    if (clock64() - t0 > 20000000000ll) { *err = 1 + p; break; }   // ~10 s: report instead of hanging the device
+    __nanosleep(200);
+  }
+}
+}  // namespace
+
+void p2p_release(Handle* h) {
+  P2P& q = h->p2p;
+  for (int r = 0; r < P2P_MAX_RANKS; ++r)
+    if (q.peer[r] && q.peer[r] != q.base) cudaIpcCloseMemHandle(q.peer[r]);
+  if (q.base) cudaFree(q.base);
+  if (q.done) cudaFree(q.done);
+  cudaGetLastError();
+  q = P2P();
+}
+
+int p2p_setup(Handle* h) {
+  P2P& q = h->p2p;
+  Problem& pb = h->pb;
+  const char* e = getenv("B200BA_P2P");   // 0: always NCCL all-gather
+  const bool want = h->nranks > 1 && h->nranks <= P2P_MAX_RANKS && pb.xchg && !(e && atoi(e) == 0);
+  if (!want) { q.on = false; return 0; }   // the same decision on every rank (xchg and nranks are global)
+  const size_t need = 512 + (size_t)2 * h->nranks * (size_t)pb.x_stride * sizeof(double);
+  if (q.base && q.bytes >= need) { q.on = true; return 0; }   // x_stride is global, so every rank takes this branch together
+  // (re)allocate on every rank, exchange the IPC handles through the communicator
+  cudaStreamSynchronize(h->stream);
+  p2p_release(h);
+  long long ok = 1;
+  cudaIpcMemHandle_t mine;
+  memset(&mine, 0, sizeof(mine));
+  if (cudaMalloc(&q.base, need) != cudaSuccess || cudaMalloc((void**)&q.done, 256) != cudaSuccess ||
+      cudaMemset(q.base, 0, need) != cudaSuccess || cudaMemset(q.done, 0, 256) != cudaSuccess ||
+      cudaIpcGetMemHandle(&mine, q.base) != cudaSuccess) {
+    cudaGetLastError();
+    ok = 0;
+  }
+  q.bytes = need;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  const int per = 9;   // 8 longs of handle + 1 status
+  long long* d = (long long*)pool_alloc(h, (size_t)per * (h->nranks + 1) * sizeof(long long));
+  if (!d) return fail(h, B200BA_OOM, "out of device memory");
+  long long send[per];
+  memcpy(send, &mine, 64);
+  send[8] = ok;
+  BA_CUDA(h, cudaMemcpyAsync(d + (size_t)per * h->nranks, send, sizeof(send), cudaMemcpyHostToDevice, h->stream));
+  if (int rc = comm_allgather_i64(h, d + (size_t)per * h->nranks, d, per)) { pool_free(h, d); return rc; }
+  std::vector<long long> all((size_t)per * h->nranks);
+  BA_CUDA(h, cudaMemcpyAsync(all.data(), d, all.size() * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+  BA_CUDA(h, cudaStreamSynchronize(h->stream));
+  for (int r = 0; r < h->nranks; ++r) ok = ok && all[(size_t)per * r + 8];
+  if (ok) {
+    for (int r = 0; r < h->nranks; ++r) {
+      if (r == h->rank) { q.peer[r] = q.base; continue; }
+      cudaIpcMemHandle_t hh;
+      memcpy(&hh, &all[(size_t)per * r], 64);
+      if (cudaIpcOpenMemHandle(&q.peer[r], hh, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+        cudaGetLastError();
+        q.peer[r] = nullptr;
+        ok = 0;
+      }
+    }
+  }
+  // second round: everybody must have opened everybody, otherwise every rank falls back to NCCL together
+  long long mine_ok = ok;
+  BA_CUDA(h, cudaMemcpyAsync(d + h->nranks, &mine_ok, sizeof(long long), cudaMemcpyHostToDevice, h->stream));
+  if (int rc = comm_allgather_i64(h, d + h->nranks, d, 1)) { pool_free(h, d); return rc; }
+  BA_CUDA(h, cudaMemcpyAsync(all.data(), d, h->nranks * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+  BA_CUDA(h, cudaStreamSynchronize(h->stream));
+  pool_free(h, d);
+  for (int r = 0; r < h->nranks; ++r) ok = ok && all[r];
+  if (!ok) { p2p_release(h); return 0; }
+  q.epoch = 0;
+  q.on = true;
+  return 0;
+}
+
+int p2p_exchange(Handle* h) {
+  P2P& q = h->p2p;
+  Problem& pb = h->pb;
+  Work& w = h->w;
+  ++q.epoch;
+  const long long parity = (long long)(q.epoch & 1);
+  const long long slots = 64 + parity * h->nranks * pb.x_stride;        // doubles from the base of a buffer
+  PeerPtrs pp{};
+  for (int r = 0; r < h->nranks; ++r) { pp.p[r] = (double*)q.peer[r]; pp.f[r] = (unsigned long long*)q.peer[r]; }
+  const long long n2 = pb.x_stride / 2;
+  const int grid = (int)std::min<long long>((n2 + 1023) / 1024, (long long)h->sm_count * 8);
+  k_p2p_push<<<grid, 256, 0, h->stream>>>(reinterpret_cast<const double2*>(w.xsend), n2, h->rank, h->nranks, pp,
+                                          slots + (long long)h->rank * pb.x_stride, q.epoch, q.done);
+  k_p2p_wait<<<1, 32, 0, h->stream>>>((const unsigned long long*)q.base, h->nranks, q.epoch,
+                                      reinterpret_cast<int*>(w.scal + S_P2P_ERR));
+  h->st.launches += 2;
+  w.xrecv = (double*)q.base + slots;
+  BA_CUDA(h, cudaGetLastError());
+  return 0;
+}
+
 // ------------------------------------------------------------------ per-problem work buffers
 static int alloc_work(Handle* h) {
   Problem& pb = h->pb;
@@ -170,7 +311,8 @@ static int alloc_work(Handle* h) {
   w.sums = w.udiag + 6 * C;
   if (pb.xchg) {
     WALLOC(w.xsend, pb.x_stride);
-    WALLOC(w.xrecv, pb.x_stride * h->nranks);
+    WALLOC(w.xrecv_nccl, pb.x_stride * h->nranks);
+    w.xrecv = w.xrecv_nccl;
     BA_CUDA(h, cudaMemsetAsync(w.xsend, 0, (size_t)pb.x_stride * sizeof(double), h->stream));
   }
   WALLOC(w.scal, NSCAL);
@@ -243,7 +385,12 @@ int linearize_all(Handle* h, double lambda) {
   {
     PhaseTimer t(h, &h->st.ms_allreduce);
     if (h->pb.xchg) {
-      if (int rc = comm_allgather_f64(h, w.xsend, w.xrecv, h->pb.x_stride)) return rc;
+      if (h->p2p.on) {
+        if (int rc = p2p_exchange(h)) return rc;
+      } else {
+        w.xrecv = w.xrecv_nccl;
+        if (int rc = comm_allgather_f64(h, w.xsend, w.xrecv, h->pb.x_stride)) return rc;
+      }
       launch_xchg_sum(h);
     } else {
       if (int rc = comm_allreduce_sum(h, w.comm, w.comm_count)) return rc;
@@ -302,6 +449,10 @@ int fetch_scalars(Handle* h) {
   int flow_err = 0;
   memcpy(&flow_err, w.h_scal + S_FLOW_ERR, sizeof(int));
   if (flow_err) return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
+  int p2p_err = 0;
+  memcpy(&p2p_err, w.h_scal + S_P2P_ERR, sizeof(int));
+  if (p2p_err) return fail(h, B200BA_NCCL, "peer-memory exchange: the contribution of rank " + std::to_string(p2p_err - 1) +
+                                           " did not arrive (results invalid)");
   return 0;
 }
 

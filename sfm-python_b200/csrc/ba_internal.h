@@ -48,6 +48,7 @@ enum Scal {
   S_RES_COST2 = 18, // sum r^2 of b200ba_residuals
   S_REPROJ_SUM = 20, // sum of per-observation reprojection error norms (b200ba_reproj_errors)
   S_TL_OK = 19,     // 1 = the coarse inverse of the two-level preconditioner is valid
+  S_P2P_ERR = 30,   // (int) set by k_p2p_wait when a peer's contribution did not arrive in time
   S_FLOW_ERR = 31   // (int) set by k_lin_flow when a dependency wait timed out
 };
 
@@ -156,7 +157,8 @@ struct Work {
   double* spart = nullptr;    // [n_sch*36]
   double* U = nullptr;        // [C*21]
   double* xsend = nullptr;    // [x_stride] sparse exchange: this rank's blocks + camera vectors + scalars
-  double* xrecv = nullptr;    // [nranks * x_stride]
+  double* xrecv = nullptr;    // [nranks * x_stride] gathered contributions of this exchange (NCCL buffer or peer-memory slots)
+  double* xrecv_nccl = nullptr;
   double* dpart = nullptr;    // [n_dslot*40] self-slot partials of the fused kernel
   double* camsum = nullptr;   // [C*40] per-camera sums of the self-slot partials
   // ---- contiguous all-reduce buffer: Sup | b | gc | udiag | sums
@@ -190,6 +192,20 @@ struct Work {
   double* h_scal = nullptr;   // pinned host mirror [NSCAL]
 };
 
+// Exchange of the reduced camera system through peer memory (NVLink / NVSwitch), one process per GPU: every rank owns a
+// cudaMalloc'ed buffer [flags (64 x u64) | parity 0: nranks x x_stride doubles | parity 1: ...], opened on every other
+// rank through CUDA IPC.  k_p2p_push stores this rank's contribution straight into slot [parity][rank] of every peer
+// and then publishes the epoch in the peers' flag words; k_p2p_wait spins (bounded) on the local flags.
+constexpr int P2P_MAX_RANKS = 8;
+struct P2P {
+  bool on = false;
+  void* base = nullptr;              // local buffer
+  size_t bytes = 0;
+  void* peer[P2P_MAX_RANKS] = {};    // base of every rank's buffer as mapped here (own entry = base)
+  unsigned int* done = nullptr;      // CTA counter of k_p2p_push
+  unsigned long long epoch = 0;      // exchanges done since the buffer was (re)allocated; identical on every rank
+};
+
 struct Handle {
   int device = 0;
   int sm_count = 148;
@@ -205,6 +221,7 @@ struct Handle {
   void* comm = nullptr;
   int rank = 0, nranks = 1;
   int64_t n_obs_global = 0;
+  P2P p2p;
   // stats
   b200ba_stats st{};
   bool profile = false;
@@ -236,6 +253,9 @@ int comm_allreduce_sum(Handle* h, double* buf, int64_t count);
 int comm_allreduce_max(Handle* h, double* buf, int64_t count);
 int comm_allgather_i64(Handle* h, const long long* send, long long* recv, int64_t count);
 int comm_allgather_f64(Handle* h, const double* send, double* recv, int64_t count);
+int p2p_setup(Handle* h);      // collective; after setup_problem (needs pb.x_stride); leaves h->p2p.on
+void p2p_release(Handle* h);
+int p2p_exchange(Handle* h);   // xsend -> every rank's receive slots; sets w.xrecv to the slots of this epoch
 
 // ---- ba_setup.cu
 int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam_idx, const int64_t* pt_idx,
