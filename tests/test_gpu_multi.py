@@ -20,14 +20,16 @@ def _gpus():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("xchg", ["0", "1"])
+@pytest.mark.parametrize("xchg", ["0", "1", "p2p"])
 @pytest.mark.parametrize("shape", [(40, 4000, 16000), (300, 30000, 120000)])
 def test_sharded_equals_unsharded(xchg, shape):
+    """xchg: 0 = all-reduce of the packed buffer, 1 = sparse exchange through ncclAllGather, p2p = sparse exchange through
+    peer memory (CUDA-IPC mapped receive slots, k_p2p_push / k_p2p_wait) -- all three must equal the unsharded system."""
     n = _gpus()
     if n < 2:
         pytest.skip("needs at least 2 GPUs")
     world = 4 if n >= 4 else 2
-    env = dict(os.environ, B200BA_XCHG=xchg)
+    env = dict(os.environ, B200BA_XCHG="1" if xchg == "p2p" else xchg, B200BA_P2P="1" if xchg == "p2p" else "0")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
            "127.0.0.1", "--master-port", "29533", os.path.join(ROOT, "tests", "_multi_worker.py")] + [str(v) for v in shape]
     p = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
