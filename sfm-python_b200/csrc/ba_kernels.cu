@@ -90,6 +90,14 @@ __device__ __forceinline__ void load_cam(const double* __restrict__ camprep, int
   for (int k = 0; k < CAMPREP_FIELDS; ++k) cp[k] = camprep[(int64_t)k * C + c];
 }
 
+// R -> cp[0..8], T -> cp[18..20] (the fields project_residual reads); the J_r fields are skipped
+__device__ __forceinline__ void load_rt(const double* __restrict__ camprep, int64_t Cs, int c, double* __restrict__ cp) {
+#pragma unroll
+  for (int k = 0; k < 9; ++k) cp[k] = camprep[(int64_t)k * Cs + c];
+#pragma unroll
+  for (int k = 18; k < 21; ++k) cp[k] = camprep[(int64_t)k * Cs + c];
+}
+
 // ------------------------------------------------------------------ residual
 __global__ void __launch_bounds__(256) k_residual(Problem pb, const double* __restrict__ x,
                                                   const double* __restrict__ camprep, double* __restrict__ r_out,
@@ -97,17 +105,28 @@ __global__ void __launch_bounds__(256) k_residual(Problem pb, const double* __re
   __shared__ double sm[32];
   const double* xp = x + 6 * pb.C;
   double acc = 0.0;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pb.N; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = pb.cam[i], p = pb.pt[i];
+  // The gathers (camera table, point) depend on the index loads: the indices and pixels of the NEXT observation of this
+  // thread are requested before the current one's gathers, so a loop iteration waits for one trip to memory, not two
+  // (ncu: the kernel is latency-bound, long-scoreboard stalls, DRAM at 41 % of peak without this).
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int c = 0, p = 0;
+  double uo = 0.0, vo = 0.0;
+  if (i < pb.N) { c = pb.cam[i]; p = pb.pt[i]; uo = pb.u[i]; vo = pb.v[i]; }
+  while (i < pb.N) {
+    const int64_t in = i + stride;
+    int cn = 0, pn = 0;
+    double un = 0.0, vn = 0.0;
+    if (in < pb.N) { cn = pb.cam[in]; pn = pb.pt[in]; un = pb.u[in]; vn = pb.v[in]; }
     double r0, r1, cp[CAMPREP_FIELDS];
-    load_cam(camprep, pb.Cs, c, cp);
-    project_residual(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i],
-                     r0, r1);
+    load_rt(camprep, pb.Cs, c, cp);   // R and T only: the residual does not read J_r (12 of the 21 gathered fields)
+    project_residual(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], uo, vo, r0, r1);
     acc += r0 * r0 + r1 * r1;
     if (r_out) {
       const int64_t d = pb.perm ? pb.perm[i] : i;
       reinterpret_cast<double2*>(r_out)[d] = make_double2(r0, r1);
     }
+    i = in; c = cn; p = pn; uo = un; vo = vn;
   }
   block_sum<1>(&acc, sm);
   if (threadIdx.x == 0) part[blockIdx.x * 8] = acc;

@@ -21,13 +21,6 @@ __device__ __forceinline__ void point_step(const double* __restrict__ ppp, const
   sums[2] = dp[0] * dp[0] + dp[1] * dp[1] + dp[2] * dp[2];
 }
 
-// R -> cp[0..8], T -> cp[18..20] (the fields project_residual reads); the J_r fields are skipped
-__device__ __forceinline__ void load_rt(const double* __restrict__ camprep, int64_t Cs, int c, double* __restrict__ cp) {
-#pragma unroll
-  for (int k = 0; k < 9; ++k) cp[k] = camprep[(int64_t)k * Cs + c];
-#pragma unroll
-  for (int k = 18; k < 21; ++k) cp[k] = camprep[(int64_t)k * Cs + c];
-}
 // as load_rt, plus the camera's step fields {J_r dw, dT} -> cp[9..14]
 __device__ __forceinline__ void load_step_cam(const double* __restrict__ camprep, const double* __restrict__ cstep, int64_t Cs,
                                               int c, double* __restrict__ cp) {
