@@ -349,6 +349,39 @@ def run_b200(a, rank, world, local_rank):
            "what": f"Engine.set_problem + Engine.solve (host numpy buffers, pinned) with {e2e_iters} LM iterations per step; "
                    f"observations x linearisations / wall time, {a.e2e_steps} steps", "seconds_per_step": dt / a.e2e_steps}
 
+    # ---- the HBM-bound kernels of the path at this workload's size (SURVEY 8d families E1 / E2): residual only
+    #      (40 B/observation) and residual + materialised 2x6 / 2x3 blocks (184 B/observation), CUDA events around each
+    hbm_kernels = None
+    if world == 1:
+        n_loc0 = len(ci)
+        r_t = torch.empty(2 * n_loc0, dtype=torch.float64, device=f"cuda:{local_rank}")
+        jc_t = torch.empty(12 * n_loc0, dtype=torch.float64, device=f"cuda:{local_rank}")
+        jp_t = torch.empty(6 * n_loc0, dtype=torch.float64, device=f"cuda:{local_rank}")
+        for _ in range(3):
+            eng.jacobian_blocks_dev(x_dev.data_ptr(), r_t.data_ptr(), jc_t.data_ptr(), jp_t.data_ptr())
+            eng.residuals_dev(x_dev.data_ptr(), r_t.data_ptr())
+        eng.set_profiling(True)
+        eng.reset_stats()
+        for _ in range(10):
+            eng.jacobian_blocks_dev(x_dev.data_ptr(), r_t.data_ptr(), jc_t.data_ptr(), jp_t.data_ptr())
+            eng.residuals_dev(x_dev.data_ptr(), r_t.data_ptr())
+        sk = eng.stats()
+        eng.set_profiling(False)
+        del r_t, jc_t, jp_t
+        torch.cuda.empty_cache()
+        pk = 6545.3
+        try:
+            pk = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", pk))
+        except Exception:
+            pass
+        bj = 184 * n_loc0 + 48 * n_cam + 24 * (hi - lo)
+        br = 40 * n_loc0 + 48 * n_cam + 24 * (hi - lo)
+        tj, tr = sk["ms_jacobian"] / 10 * 1e-3, sk["ms_residual"] / 10 * 1e-3
+        hbm_kernels = {"k_jacobian": {"bound": "hbm", "ms": tj * 1e3, "achieved": bj / tj / 1e9, "peak": pk, "unit": "GB/s",
+                                      "frac": bj / tj / 1e9 / pk, "bytes_per_obs": 184},
+                       "k_residual": {"bound": "hbm", "ms": tr * 1e3, "achieved": br / tr / 1e9, "peak": pk, "unit": "GB/s",
+                                      "frac": br / tr / 1e9 / pk, "bytes_per_obs": 40,
+                                      "note": "k_cam_prep + k_residual + the partial reduction"}}
     if rank != 0:
         return
     # ---- roofline of the dominant kernel of the step (SURVEY.md 8d family L)
@@ -405,6 +438,8 @@ def run_b200(a, rank, world, local_rank):
            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "roofline_fp64": roof64, "kernel_ms": kern_ms,
            "tiles": {"n_tiles": int(st["n_tiles"]), "pair_slots": int(st["n_pair_slots"]),
                      "self_slots": int(st["n_self_slots"])}}
+    if hbm_kernels:
+        out["roofline_hbm_kernels"] = hbm_kernels
     out.update(lm)
     if not a.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(a.workload, a.seed, a.cpu_sample_obs)

@@ -228,8 +228,17 @@ __global__ void __launch_bounds__(256) k_reproj_err(Problem pb, const double* __
                                                     double* __restrict__ err_out, double* __restrict__ part) {
   __shared__ double sm[32];
   double acc = 0.0;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pb.N; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = pb.cam[i], p = pb.pt[i];
+  // indices and pixels of this thread's next observation are requested ahead of the current gathers (see k_residual)
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  int c = 0, p = 0;
+  double uo = 0.0, vo = 0.0;
+  if (i < pb.N) { c = pb.cam[i]; p = pb.pt[i]; uo = pb.u[i]; vo = pb.v[i]; }
+  while (i < pb.N) {
+    const int64_t in = i + stride;
+    int cn = 0, pn = 0;
+    double un = 0.0, vn = 0.0;
+    if (in < pb.N) { cn = pb.cam[in]; pn = pb.pt[in]; un = pb.u[in]; vn = pb.v[in]; }
     const double* q = Rt + 12 * (int64_t)c;
     const double X0 = X[3 * (int64_t)p], X1 = X[3 * (int64_t)p + 1], X2 = X[3 * (int64_t)p + 2];
     const double z0 = q[0] * X0 + q[1] * X1 + q[2] * X2 + q[9];
@@ -238,10 +247,11 @@ __global__ void __launch_bounds__(256) k_reproj_err(Problem pb, const double* __
     const double p0 = pb.K.k[0] * z0 + pb.K.k[1] * z1 + pb.K.k[2] * z2;
     const double p1 = pb.K.k[3] * z0 + pb.K.k[4] * z1 + pb.K.k[5] * z2;
     const double p2 = pb.K.k[6] * z0 + pb.K.k[7] * z1 + pb.K.k[8] * z2;
-    const double du = p0 / p2 - pb.u[i], dv = p1 / p2 - pb.v[i];
+    const double du = p0 / p2 - uo, dv = p1 / p2 - vo;
     const double e = sqrt(du * du + dv * dv);
     acc += e;
     if (err_out) err_out[pb.perm ? pb.perm[i] : i] = e;
+    i = in; c = cn; p = pn; uo = un; vo = vn;
   }
   block_sum<1>(&acc, sm);
   if (threadIdx.x == 0) part[blockIdx.x * 8] = acc;
