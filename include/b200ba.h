@@ -127,6 +127,14 @@ int b200ba_residuals_dev(b200ba_handle* h, const double* x_dev, double* r_out_de
 int b200ba_pack_cameras(b200ba_handle* h, int64_t n, const double* H /* n x 16 */, double* params /* n x 6 */);
 int b200ba_unpack_cameras(b200ba_handle* h, int64_t n, const double* params /* n x 6 */, double* H /* n x 16 */);
 
+/* Two-view triangulation of SFM._apply_increment (sfm.py:214-221): cv2.triangulatePoints(M1, M2, pts1.T, pts2.T)
+ * followed by X /= X[3] -- the DLT the reference restates as triangulate_points_linear2
+ * (cv2_lite/triangulate_points.py:66-94) -- and, when mask_out is given, the visibility mask
+ * (inv(H1) X)[2] > 0 and (inv(H2) X)[2] > 0 of sfm.py:219-221 (H1, H2: row-major 4x4 rigid poses).
+ * M1, M2: row-major 3x4; pts1, pts2: n x 2; X_out: n x 4 rows [X Y Z 1]; host buffers; no problem needed. */
+int b200ba_triangulate(b200ba_handle* h, int64_t n, const double* M1, const double* M2, const double* pts1,
+                       const double* pts2, const double* H1, const double* H2, double* X_out, unsigned char* mask_out);
+
 /* The per-observation reprojection-error loop of SFM._apply_increment (sfm.py:234-238), which calls
  * calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14) once per observation in Python:
  * err_i = || pi(K (R_c X_p + t_c)) - uv_i ||  over the observations of the problem on the handle, in the pipeline's

@@ -419,6 +419,30 @@ def total_reproj_error(K, Hs, X3d, camera_indices, point_indices, points_2d):
     return e, float(e.sum())
 
 
+# --------------------------------------------------------------------------
+# Two-view triangulation (next row 8f-4; sfm.py:214-221)
+# --------------------------------------------------------------------------
+
+def triangulate_points_linear2(M1, M2, pts1, pts2):
+    """cv2_lite/triangulate_points.py:66-94 (the DLT of cv2.triangulatePoints, sfm.py:216): per point the 4 x 4 system
+    [x1 M1[2] - M1[0]; y1 M1[2] - M1[1]; x2 M2[2] - M2[0]; y2 M2[2] - M2[1]], last right singular vector, X /= X[3].
+    pts are (2, N); returns (4, N).  Batched SVD instead of the reference's Python loop."""
+    M1, M2 = np.asarray(M1, dtype=np.float64), np.asarray(M2, dtype=np.float64)
+    p1, p2 = np.asarray(pts1, dtype=np.float64), np.asarray(pts2, dtype=np.float64)
+    A = np.stack([p1[0][:, None] * M1[2] - M1[0], p1[1][:, None] * M1[2] - M1[1],
+                  p2[0][:, None] * M2[2] - M2[0], p2[1][:, None] * M2[2] - M2[1]], axis=1)      # (N, 4, 4)
+    Vt = np.linalg.svd(A)[2]
+    X = Vt[:, -1, :].T
+    return X / X[3]
+
+
+def visibility_mask(H1, H2, X3d_H):
+    """sfm.py:219-221: both cameras see the point in front of them."""
+    P1 = np.linalg.inv(H1) @ X3d_H
+    P2 = np.linalg.inv(H2) @ X3d_H
+    return (P1[2, :] > 0) & (P2[2, :] > 0)
+
+
 def rms(r):
     r = np.asarray(r)
     return float(np.sqrt(np.mean(r * r)))

@@ -265,6 +265,54 @@ def gen_poses():
     print("pose golden:", allH.shape, "scipy", scipy.__version__, "max angle", np.linalg.norm(params[:, :3], axis=1).max())
 
 
+def gen_triangulate():
+    """Two-view triangulation as at sfm.py:214-221: the REAL cv2.triangulatePoints (OpenCV, the call the reference makes)
+    and the reference's own restatement triangulate_points_linear2 (cv2_lite/triangulate_points.py:66-94, loaded by path)
+    on a seeded two-camera scene with pixel noise, plus the four-point example of the reference's docstring
+    (triangulate_points.py:137-161) and the visibility mask."""
+    import cv2
+    tp = load_by_path("ref_tri", os.path.join(REF, "cv2_lite", "triangulate_points.py"))
+    syn = synthetic()
+    rng = np.random.default_rng(21)
+    K = syn.K_SCEAUX
+    H1 = np.eye(4)
+    H2 = np.eye(4)
+    H2[:3, :3] = O.rodrigues(np.array([[0.02, -0.15, 0.01]]))[0]
+    H2[:3, 3] = [-1.0, 0.05, 0.1]
+    n = 500
+    X = np.stack([rng.uniform(-2, 2, n), rng.uniform(-1.5, 1.5, n), rng.uniform(-3, 9, n)], 1)   # some points behind the cameras
+    X[np.abs(X[:, 2]) < 0.3, 2] = 4.0
+    Xh = np.concatenate([X, np.ones((n, 1))], 1).T
+    M1, M2 = K @ H1[:3], K @ H2[:3]
+    def proj(M):
+        p = M @ Xh
+        return (p[:2] / p[2]).T + 0.5 * rng.standard_normal((n, 2))
+    pts1, pts2 = proj(M1), proj(M2)
+    cv = cv2.triangulatePoints(M1, M2, pts1.T, pts2.T)
+    cv = cv / cv[-1]                                                                 # sfm.py:217
+    ref2 = tp.triangulate_points_linear2(M1, M2, pts1.T, pts2.T)
+    P1 = np.linalg.inv(H1) @ cv
+    P2 = np.linalg.inv(H2) @ cv
+    mask = (P1[2, :] > 0) & (P2[2, :] > 0)                                             # sfm.py:219-221
+    dM1 = np.array([[2.26648588e+03, -1.20335940e+01, 2.30479750e+03, -8.10676693e+03],
+                    [-5.27039708e+02, 2.80897851e+03, 1.18663534e+03, -8.67245706e+02],
+                    [-3.31554792e-01, -8.05176652e-02, 9.39993790e-01, -2.70143322e-01]])
+    dM2 = np.array([[2.57889420e+03, 2.21368015e+01, 1.94884818e+03, -5.51844918e+03],
+                    [-2.65746745e+02, 2.88325548e+03, 1.09199408e+03, -4.01890574e+02],
+                    [-1.92197430e-01, -2.02833813e-02, 9.81146642e-01, -7.57015427e-02]])
+    d1 = np.array([[356.43856812, 1148.45336914], [360.64306641, 1452.07055664], [362.01452637, 1746.91137695],
+                   [380.1892395, 1124.84753418]])
+    d2 = np.array([[238.98179626, 1011.63299561], [251.32275391, 1309.41662598], [263.76693726, 1595.79040527],
+                   [265.42037964, 989.33227539]])
+    dcv = cv2.triangulatePoints(dM1, dM2, d1.T, d2.T)
+    dcv = dcv / dcv[-1]
+    np.savez_compressed(os.path.join(GOLD, "ref_triangulate.npz"), K=K, H1=H1, H2=H2, pts1=pts1, pts2=pts2, X_cv2=cv,
+                        X_ref_linear2=ref2, mask=mask, doc_M1=dM1, doc_M2=dM2, doc_pts1=d1, doc_pts2=d2, doc_X_cv2=dcv,
+                        cv2_version=cv2.__version__)
+    print("triangulate golden: n", n, "visible", int(mask.sum()), "max |cv2 - linear2| rel",
+          np.abs(cv - ref2).max() / np.abs(cv).max(), "cv2", cv2.__version__)
+
+
 def gen_reproj():
     """Reprojection error in the pipeline's R X + t convention: the REAL reference functions reproj_error
     (cv2_lite/solve_pnp.py:9-14) and the loop body of sfm.py:234-238 (calc_reproj_error, sfm.py:38-41, restated in two
@@ -316,6 +364,8 @@ if __name__ == "__main__":
         gen_scipy([int(a) for a in sys.argv[2:]] or [0, 1, 2])
     elif what == "poses":
         gen_poses()
+    elif what == "triangulate":
+        gen_triangulate()
     elif what == "reproj":
         gen_reproj()
     elif what == "fixed":

@@ -200,6 +200,23 @@ class Engine:
         self._check(self.lib.b200ba_unpack_cameras(self.h, len(P), _ptr(P), _ptr(out)))
         return out
 
+    def triangulate(self, M1, M2, pts1, pts2, H1=None, H2=None):
+        """DLT triangulation of ``sfm.py:216-217`` for ``(n, 2)`` point arrays; returns ``X (n, 4)`` rows ``[X Y Z 1]`` and,
+        when the poses ``H1, H2`` are given, the visibility mask of ``sfm.py:219-221``."""
+        M1 = np.ascontiguousarray(M1, dtype=np.float64)
+        M2 = np.ascontiguousarray(M2, dtype=np.float64)
+        p1 = np.ascontiguousarray(pts1, dtype=np.float64).reshape(-1, 2)
+        p2 = np.ascontiguousarray(pts2, dtype=np.float64).reshape(-1, 2)
+        if M1.shape != (3, 4) or M2.shape != (3, 4) or len(p1) != len(p2):
+            raise ValueError("M1, M2 must be 3x4 and the point arrays of equal length")
+        X = np.empty((len(p1), 4), dtype=np.float64)
+        mask = np.empty(len(p1), dtype=np.uint8) if H1 is not None and H2 is not None else None
+        h1 = np.ascontiguousarray(H1, dtype=np.float64) if mask is not None else None
+        h2 = np.ascontiguousarray(H2, dtype=np.float64) if mask is not None else None
+        self._check(self.lib.b200ba_triangulate(self.h, len(p1), _ptr(M1), _ptr(M2), _ptr(p1), _ptr(p2), _ptr(h1), _ptr(h2),
+                                                _ptr(X), _ptr(mask)))
+        return (X, mask.astype(bool)) if mask is not None else X
+
     def normal_equations(self, x, lam, want_S=True):
         x = self._x(x)
         n = 6 * self.n_cam
@@ -353,6 +370,24 @@ def unpack_parameters(x, n_cam, engine=None):
     x = np.asarray(x, dtype=np.float64)
     Hs = (engine or _aux_engine()).unpack_cameras(x[:6 * n_cam])
     return Hs, x[6 * n_cam:].reshape(-1, 3)
+
+
+def triangulate_points(M1, M2, pts1, pts2, engine=None):
+    """``cv2.triangulatePoints(M1, M2, pts1, pts2)`` as called at ``sfm.py:216`` (``pts`` are ``(2, N)``), already divided by
+    the last row (what ``sfm.py:217`` does next): returns ``(4, N)`` with a last row of ones."""
+    p1, p2 = np.asarray(pts1, dtype=np.float64), np.asarray(pts2, dtype=np.float64)
+    if p1.ndim != 2 or p1.shape[0] != 2 or p1.shape != p2.shape:
+        raise ValueError("pts1, pts2 must be (2, N)")
+    return np.ascontiguousarray((engine or _aux_engine()).triangulate(M1, M2, p1.T, p2.T).T)
+
+
+def triangulate_visible(K, H1, H2, pts1, pts2, engine=None):
+    """``sfm.py:214-223`` in one call: ``M = K @ H[:3]``, triangulation, visibility mask; ``pts`` are ``(N, 2)`` as returned by
+    ``edge.pt2ds_pt2ds()``.  Returns ``(X3d[mask] (m, 3), mask (N,))``."""
+    K = np.asarray(K, dtype=np.float64)
+    H1, H2 = np.asarray(H1, dtype=np.float64), np.asarray(H2, dtype=np.float64)
+    X, mask = (engine or _aux_engine()).triangulate(K @ H1[:3], K @ H2[:3], pts1, pts2, H1, H2)
+    return X[mask, :3], mask
 
 
 def gather_observations(track_point_idx, track_cam_id, track_xy, registered_cam_ids):

@@ -220,6 +220,76 @@ __global__ void k_unpack_cameras(int64_t n, const double* __restrict__ params, d
   h[12] = 0.0; h[13] = 0.0; h[14] = 0.0; h[15] = 1.0;
 }
 
+// ------------------------------------------------------------------ two-view triangulation (sfm.py:214-221)
+// cv2.triangulatePoints(M1, M2, pts1.T, pts2.T) as called at sfm.py:216, i.e. the DLT the reference restates as
+// triangulate_points_linear2 (cv2_lite/triangulate_points.py:66-94): per point the 4 x 4 system
+//   A = [x1 M1[2] - M1[0];  y1 M1[2] - M1[1];  x2 M2[2] - M2[0];  y2 M2[2] - M2[1]],   X = right singular vector of the
+// smallest singular value, divided by its last entry (sfm.py:217).  One thread per point; the SVD is a one-sided
+// (Hestenes) Jacobi iteration on the columns of A -- it works on A itself (not A^T A), so the null vector keeps full
+// relative accuracy.  vis1 / vis2 (nullable): third row of inv(H1) / inv(H2); the mask is sfm.py:219-221.
+__global__ void k_triangulate(int64_t n, const double* __restrict__ M1, const double* __restrict__ M2,
+                              const double* __restrict__ pts1, const double* __restrict__ pts2,
+                              const double* __restrict__ vis1, const double* __restrict__ vis2, double* __restrict__ X_out,
+                              unsigned char* __restrict__ mask_out) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double x1 = pts1[2 * i], y1 = pts1[2 * i + 1], x2 = pts2[2 * i], y2 = pts2[2 * i + 1];
+  double A[4][4], V[4][4];   // A[row][col]
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    A[0][k] = x1 * M1[8 + k] - M1[k];
+    A[1][k] = y1 * M1[8 + k] - M1[4 + k];
+    A[2][k] = x2 * M2[8 + k] - M2[k];
+    A[3][k] = y2 * M2[8 + k] - M2[4 + k];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) V[k][j] = (k == j) ? 1.0 : 0.0;
+  }
+  for (int sweep = 0; sweep < 40; ++sweep) {
+    bool rotated = false;
+#pragma unroll
+    for (int p = 0; p < 3; ++p)
+#pragma unroll
+      for (int q = p + 1; q < 4; ++q) {
+        double al = 0.0, be = 0.0, ga = 0.0;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) { al += A[r][p] * A[r][p]; be += A[r][q] * A[r][q]; ga += A[r][p] * A[r][q]; }
+        if (fabs(ga) > 1e-16 * sqrt(al * be) && ga != 0.0) {
+          rotated = true;
+          const double zeta = (be - al) / (2.0 * ga);
+          const double t = (zeta >= 0.0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+          const double c = 1.0 / sqrt(1.0 + t * t), sn = c * t;
+#pragma unroll
+          for (int r = 0; r < 4; ++r) {
+            const double ap = A[r][p], aq = A[r][q];
+            A[r][p] = c * ap - sn * aq; A[r][q] = sn * ap + c * aq;
+            const double vp = V[r][p], vq = V[r][q];
+            V[r][p] = c * vp - sn * vq; V[r][q] = sn * vp + c * vq;
+          }
+        }
+      }
+    if (!rotated) break;
+  }
+  int best = 0;
+  double bn = 1e300;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const double nk = A[0][k] * A[0][k] + A[1][k] * A[1][k] + A[2][k] * A[2][k] + A[3][k] * A[3][k];
+    if (nk < bn) { bn = nk; best = k; }
+  }
+  double X[4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r) X[r] = best == 0 ? V[r][0] : best == 1 ? V[r][1] : best == 2 ? V[r][2] : V[r][3];
+  const double iw = 1.0 / X[3];
+  X[0] *= iw; X[1] *= iw; X[2] *= iw; X[3] = 1.0;
+#pragma unroll
+  for (int r = 0; r < 4; ++r) X_out[4 * i + r] = X[r];
+  if (mask_out) {
+    const double z1 = vis1[0] * X[0] + vis1[1] * X[1] + vis1[2] * X[2] + vis1[3];
+    const double z2 = vis2[0] * X[0] + vis2[1] * X[1] + vis2[2] * X[2] + vis2[3];
+    mask_out[i] = (z1 > 0.0 && z2 > 0.0) ? 1 : 0;
+  }
+}
+
 // ------------------------------------------------------------------ per-observation reprojection error (sfm.py:234-238)
 // The loop of SFM._apply_increment calls calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14)
 // once per observation: || pi(K (R X + t)) - uv ||, the pipeline's R X + t convention (NOT the R (X - T) of the BA

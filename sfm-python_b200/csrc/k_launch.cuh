@@ -116,6 +116,13 @@ void launch_unpack_cameras(Handle* h, int64_t n, const double* params_dev, doubl
   h->st.launches += 1;
 }
 
+void launch_triangulate(Handle* h, int64_t n, const double* M1, const double* M2, const double* pts1, const double* pts2,
+                        const double* vis1, const double* vis2, double* X_out, unsigned char* mask_out) {
+  if (n <= 0) return;
+  k_triangulate<<<cdiv(n, 128), 128, 0, h->stream>>>(n, M1, M2, pts1, pts2, vis1, vis2, X_out, mask_out);
+  h->st.launches += 1;
+}
+
 void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out) {
   const int g = obs_grid(h);
   KernelTimer t(h);

@@ -147,3 +147,38 @@ def test_pack_unpack_cameras_vs_scipy_golden(engine):
     x0 = b200ba.pack_parameters(d["H"][:8], X)
     Hs, Xb = b200ba.unpack_parameters(x0, 8)
     assert np.array_equal(Xb, X) and np.abs(Hs[:, :3, :3] - d["H"][:8, :3, :3]).max() <= 1e-13
+
+
+# ------------------------------------------------------------------ two-view triangulation (sfm.py:214-221)
+def test_triangulate_vs_cv2_golden(engine):
+    """b200ba_triangulate against the REAL cv2.triangulatePoints + X /= X[3] (sfm.py:216-217), the reference's
+    triangulate_points_linear2 and the visibility mask of sfm.py:219-221; also the reference's docstring example."""
+    import b200ba
+    d = load_golden("ref_triangulate.npz")
+    M1, M2 = d["K"] @ d["H1"][:3], d["K"] @ d["H2"][:3]
+    X = b200ba.triangulate_points(M1, M2, d["pts1"].T, d["pts2"].T)
+    assert X.shape == d["X_cv2"].shape and np.array_equal(X[3], np.ones(X.shape[1]))
+    scale = np.abs(d["X_cv2"]).max(axis=0)
+    assert (np.abs(X - d["X_cv2"]).max(axis=0) <= 1e-9 * scale).all()
+    assert (np.abs(X - d["X_ref_linear2"]).max(axis=0) <= 1e-9 * scale).all()
+    X3d, mask = b200ba.triangulate_visible(d["K"], d["H1"], d["H2"], d["pts1"], d["pts2"])
+    assert np.array_equal(mask, d["mask"])
+    assert np.abs(X3d - d["X_cv2"][:3].T[d["mask"]]).max() <= 1e-9 * np.abs(d["X_cv2"]).max()
+    Xd = b200ba.triangulate_points(d["doc_M1"], d["doc_M2"], d["doc_pts1"].T, d["doc_pts2"].T)
+    assert np.abs(Xd - d["doc_X_cv2"]).max() <= 1e-9 * np.abs(d["doc_X_cv2"]).max()
+
+
+def test_triangulate_large_vs_oracle(engine):
+    """200k point pairs against the oracle's batched SVD."""
+    import b200ba
+    d = load_golden("ref_triangulate.npz")
+    rng = np.random.default_rng(8)
+    n = 200000
+    X = np.stack([rng.uniform(-3, 3, n), rng.uniform(-2, 2, n), rng.uniform(2, 12, n), np.ones(n)])
+    M1, M2 = d["K"] @ d["H1"][:3], d["K"] @ d["H2"][:3]
+    p1, p2 = M1 @ X, M2 @ X
+    p1 = p1[:2] / p1[2] + 0.3 * rng.standard_normal((2, n))
+    p2 = p2[:2] / p2[2] + 0.3 * rng.standard_normal((2, n))
+    got = b200ba.triangulate_points(M1, M2, p1, p2)
+    ref = O.triangulate_points_linear2(M1, M2, p1, p2)
+    assert (np.abs(got - ref).max(axis=0) <= 1e-8 * np.abs(ref).max(axis=0)).all()

@@ -155,3 +155,17 @@ def test_gather_observations_matches_reference_iteration():
     tp, tc, tx, ty = map(np.array, zip(*flat))
     ci, pi, uv = b200ba.gather_observations(tp, tc, np.stack([tx, ty], 1), registered)
     assert np.array_equal(ci, camera_indices) and np.array_equal(pi, pt_indices) and np.array_equal(uv, pt2ds)
+
+
+def test_triangulation_oracle_vs_cv2_and_reference():
+    """oracle.triangulate_points_linear2 / visibility_mask against the REAL cv2.triangulatePoints (the call at sfm.py:216)
+    and the reference's triangulate_points_linear2 (ref_triangulate.npz), incl. the reference's docstring example."""
+    d = load_golden("ref_triangulate.npz")
+    M1, M2 = d["K"] @ d["H1"][:3], d["K"] @ d["H2"][:3]
+    X = O.triangulate_points_linear2(M1, M2, d["pts1"].T, d["pts2"].T)
+    scale = np.abs(d["X_cv2"]).max(axis=0)
+    assert (np.abs(X - d["X_cv2"]).max(axis=0) <= 1e-9 * scale).all()
+    assert (np.abs(X - d["X_ref_linear2"]).max(axis=0) <= 1e-9 * scale).all()
+    assert np.array_equal(O.visibility_mask(d["H1"], d["H2"], X), d["mask"])
+    Xd = O.triangulate_points_linear2(d["doc_M1"], d["doc_M2"], d["doc_pts1"].T, d["doc_pts2"].T)
+    assert np.abs(Xd - d["doc_X_cv2"]).max() <= 1e-9 * np.abs(d["doc_X_cv2"]).max()
