@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample-obs", type=int, default=3000)
+    ap.add_argument("--cpu-sample-obs", type=int, default=12000)
     ap.add_argument("--sweep", action="store_true",
                     help="config E: residual + materialised Jacobian blocks, N = 1M..--sweep-max observations, vs the HBM roofline")
     ap.add_argument("--sweep-max", type=int, default=100_000_000)
