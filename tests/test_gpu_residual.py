@@ -182,3 +182,30 @@ def test_triangulate_large_vs_oracle(engine):
     got = b200ba.triangulate_points(M1, M2, p1, p2)
     ref = O.triangulate_points_linear2(M1, M2, p1, p2)
     assert (np.abs(got - ref).max(axis=0) <= 1e-8 * np.abs(ref).max(axis=0)).all()
+
+
+def test_edge_cases_of_the_widened_rows(engine):
+    """Empty inputs and bad arguments of the entries next to the solve: no crash, the reference's behaviour on empties
+    (empty arrays), errors as ValueError."""
+    import b200ba
+    assert engine.pack_cameras(np.zeros((0, 4, 4))).shape == (0, 6)
+    assert engine.unpack_cameras(np.zeros((0, 6))).shape == (0, 4, 4)
+    M = np.hstack([np.eye(3), np.zeros((3, 1))])
+    assert engine.triangulate(M, M, np.zeros((0, 2)), np.zeros((0, 2))).shape == (0, 4)
+    with pytest.raises(ValueError):
+        engine.triangulate(M[:, :3], M, np.zeros((1, 2)), np.zeros((1, 2)))
+    d = load_golden("ref_reproj_error.npz")
+    engine.set_problem(len(d["Hs"]), len(d["X3d"]), d["ci"][:0], d["pi"][:0], d["uv"][:0], d["K"])     # no observations
+    err, tot = engine.reproj_errors(d["Hs"], d["X3d"])
+    assert err.shape == (0,) and tot == 0.0
+    engine.set_problem(len(d["Hs"]), len(d["X3d"]), d["ci"], d["pi"], d["uv"], d["K"])
+    with pytest.raises(ValueError):
+        engine.reproj_errors(d["Hs"][:-1], d["X3d"])
+    with pytest.raises(ValueError):
+        engine.set_fixed_cameras([len(d["Hs"])])                # out of range
+    engine.set_fixed_cameras([0, 0, 1])                          # duplicates are fine
+    engine.set_fixed_cameras(())
+    # identity pose: rotation vector exactly zero (the first registered camera of sfm.py:176)
+    p = engine.pack_cameras(np.eye(4)[None])
+    assert np.array_equal(p, np.zeros((1, 6)))
+    assert np.array_equal(engine.unpack_cameras(p)[0], np.eye(4))
