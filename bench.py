@@ -114,7 +114,14 @@ def reference_step(s, max_nfev=2):
 def cpu_baseline(workload, seed, n_obs_target):
     s = reference_sample(workload, seed, n_obs_target)
     dt, njev, n = reference_step(s)
+    # R2 of SURVEY 8d: the same scipy call with the vectorised numpy residual (the best the scipy path can do on a CPU)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ba_oracle as O
+    t = time.perf_counter()
+    r2 = O.scipy_solve(s["x0"], s["n_cam"], s["n_pts"], s["ci"], s["pi"], s["uv"], s["K"], ftol=1e-10, max_nfev=2)
+    dt2 = time.perf_counter() - t
     return {"value": n * njev / dt, "unit": UNIT, "cores": 1, "kind": "port",
+            "vectorised_residual_value": n * int(r2.njev) / dt2,
             "sample": f"first {s['n_pts']} points / {n} observations / {s['n_cam']} cameras of the workload, scipy TRF "
                       f"max_nfev=2 ({njev} linearisations) with the per-observation residual port, {dt:.1f} s",
             "seconds": dt}
