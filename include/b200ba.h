@@ -127,6 +127,16 @@ int b200ba_residuals_dev(b200ba_handle* h, const double* x_dev, double* r_out_de
 int b200ba_pack_cameras(b200ba_handle* h, int64_t n, const double* H /* n x 16 */, double* params /* n x 6 */);
 int b200ba_unpack_cameras(b200ba_handle* h, int64_t n, const double* params /* n x 6 */, double* H /* n x 16 */);
 
+/* Perspective-n-point for the cameras of a new edge: cv2.solvePnP(pt3ds, pt2ds, K, zeros) at sfm.py:207-208, the
+ * reference's restatement solve_pnp (cv2_lite/solve_pnp.py:17-66): DLT on normalised image points + non-linear
+ * refinement of (rvec, tvec) on the reprojection error, R X + t convention (H_from_rtvec, transforms.py:18-23).
+ * n_problems independent problems in one launch (one CTA each): counts[k] points of problem k, X (sum counts x 3) and
+ * uv (sum counts x 2) concatenated; guess (nullable, n_problems x 6 [rvec | tvec]) skips the DLT (useExtrinsicGuess);
+ * out: n_problems x 9 = rvec(3) tvec(3) cost iterations status (1 converged, 0 iteration limit, -1 not finite).
+ * Non-planar point sets only (the DLT needs >= 6 points in general position). */
+int b200ba_solve_pnp(b200ba_handle* h, int64_t n_problems, const int64_t* counts, const double* X, const double* uv,
+                     const double* K, const double* guess, int32_t max_iter, double* out);
+
 /* Two-view triangulation of SFM._apply_increment (sfm.py:214-221): cv2.triangulatePoints(M1, M2, pts1.T, pts2.T)
  * followed by X /= X[3] -- the DLT the reference restates as triangulate_points_linear2
  * (cv2_lite/triangulate_points.py:66-94) -- and, when mask_out is given, the visibility mask

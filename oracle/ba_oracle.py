@@ -443,6 +443,48 @@ def visibility_mask(H1, H2, X3d_H):
     return (P1[2, :] > 0) & (P2[2, :] > 0)
 
 
+# --------------------------------------------------------------------------
+# PnP (next row 8f-4; cv2.solvePnP at sfm.py:207-208, restated by cv2_lite/solve_pnp.py:17-66)
+# --------------------------------------------------------------------------
+
+def solve_pnp_linear(point3ds, point2ds, K):
+    """cv2_lite/solve_pnp.py:17-42: DLT on normalised image points, rotation part orthogonalised by an SVD, sign from
+    the determinant (t is NOT rescaled there -- a quirk of the reference that only matters for the starting point)."""
+    n = len(point3ds)
+    ph = np.hstack((point2ds, np.ones((n, 1))))
+    nrm = (np.linalg.inv(K) @ ph.T)[:2].T
+    A = np.zeros((2 * n, 12))
+    X, Y, Z = point3ds[:, 0], point3ds[:, 1], point3ds[:, 2]
+    u, v = nrm[:, 0], nrm[:, 1]
+    o, z = np.ones(n), np.zeros(n)
+    A[0::2] = np.stack([X, Y, Z, o, z, z, z, z, -u * X, -u * Y, -u * Z, -u], 1)
+    A[1::2] = np.stack([z, z, z, z, X, Y, Z, o, -v * X, -v * Y, -v * Z, -v], 1)
+    h = np.linalg.svd(A)[2][-1].reshape(3, 4)
+    U, _, Vt = np.linalg.svd(h[:, :3])
+    R, t = U @ Vt, h[:, 3]
+    if np.linalg.det(R) < 0:
+        R, t = -R, -t
+    return R, t
+
+
+def solve_pnp(point3ds, point2ds, K, x0=None):
+    """cv2_lite/solve_pnp.py:45-66: DLT start, then scipy least_squares on reproj_error over (rvec, tvec).  Returns
+    (rvec (3,), tvec (3,), cost).  rvec <-> R through scipy Rotation (the reference's matrix_to_rvec / rvec_to_matrix are
+    plain Rodrigues maps)."""
+    from scipy.optimize import least_squares
+    from scipy.spatial.transform import Rotation as Rot
+    point3ds, point2ds = np.asarray(point3ds, dtype=np.float64), np.asarray(point2ds, dtype=np.float64)
+    if x0 is None:
+        R, t = solve_pnp_linear(point3ds, point2ds, K)
+        x0 = np.hstack((Rot.from_matrix(R).as_rotvec(), t))
+
+    def fun(p):
+        return reproj_error(point3ds, point2ds, K, Rot.from_rotvec(p[:3]).as_matrix(), p[3:6]).ravel()
+
+    res = least_squares(fun, x0, xtol=1e-14, ftol=1e-14, gtol=1e-14)
+    return res.x[:3], res.x[3:6], float(res.cost)
+
+
 def rms(r):
     r = np.asarray(r)
     return float(np.sqrt(np.mean(r * r)))

@@ -265,6 +265,45 @@ def gen_poses():
     print("pose golden:", allH.shape, "scipy", scipy.__version__, "max angle", np.linalg.norm(params[:, :3], axis=1).max())
 
 
+def gen_pnp():
+    """PnP as at sfm.py:207-208: the REAL cv2.solvePnP and the reference's cv2_lite.solve_pnp.solve_pnp on the
+    reference's own 9-point example (solve_pnp.py:70-83) and on seeded scenes (60 and 800 points, 0.5 px noise)."""
+    import cv2
+    sys.path.insert(0, REF)
+    import cv2_lite.solve_pnp as sp
+    syn = synthetic()
+    K = syn.K_SCEAUX
+    rng = np.random.default_rng(31)
+    cases = {}
+    p3 = np.array([[-2.83510726, 0.35871423, 7.39620667], [-2.64956519, 1.26203440, 7.24983088],
+                   [-2.67895385, -0.01053622, 7.470429], [-2.49225235, 0.81401947, 7.36628308],
+                   [-2.31513876, -0.16642927, 7.48943918], [-2.40576114, -1.25461447, 8.02639394],
+                   [-2.12475213, 0.15831901, 7.43070466], [-1.88875539, 1.02978915, 8.18975227],
+                   [-1.70972510, -0.60470877, 8.44642688]])
+    p2 = np.array([[232.86323547, 1230.31469727], [294.15100098, 1622.02612305], [312.4229126, 1076.39611816],
+                   [377.7600708, 1423.75268555], [470.68951416, 1014.42590332], [477.48834229, 604.61303711],
+                   [544.51257324, 1148.95483398], [672.24969482, 1470.36743164], [754.92327881, 871.83178711]])
+    cases["doc9"] = (p3, p2)
+    for name, n in (("s60", 60), ("s800", 800)):
+        w = rng.standard_normal(3) * 0.2
+        R = O.rodrigues(w[None])[0]
+        t = np.array([0.3, -0.2, 0.5]) + 0.1 * rng.standard_normal(3)
+        X = np.stack([rng.uniform(-3, 3, n), rng.uniform(-2, 2, n), rng.uniform(4, 12, n)], 1)
+        p = (K @ (R @ X.T + t[:, None])).T
+        cases[name] = (X, p[:, :2] / p[:, 2:3] + 0.5 * rng.standard_normal((n, 2)))
+    out = {"K": K, "cv2_version": cv2.__version__}
+    for name, (X, uv) in cases.items():
+        ok, rv, tv = cv2.solvePnP(X, uv, K, np.zeros((1, 5)))
+        ok2, rv2, tv2 = sp.solve_pnp(X, uv, K)
+        cost_cv = 0.5 * float(np.sum(sp.reproj_error(X, uv, K, cv2.Rodrigues(rv)[0], tv.ravel()) ** 2))
+        cost_ref = 0.5 * float(np.sum(sp.reproj_error(X, uv, K, cv2.Rodrigues(rv2)[0], tv2.ravel()) ** 2))
+        out.update({f"{name}_X": X, f"{name}_uv": uv, f"{name}_cv2": np.hstack([rv.ravel(), tv.ravel()]),
+                    f"{name}_ref": np.hstack([rv2.ravel(), tv2.ravel()]), f"{name}_cost_cv2": cost_cv, f"{name}_cost_ref": cost_ref})
+        print(f"[pnp {name}] n {len(X)} cv2 {np.round(np.hstack([rv.ravel(), tv.ravel()]), 6)} cost {cost_cv:.9f} | reference "
+              f"{np.round(np.hstack([rv2.ravel(), tv2.ravel()]), 6)} cost {cost_ref:.9f}")
+    np.savez_compressed(os.path.join(GOLD, "ref_pnp.npz"), **out)
+
+
 def gen_triangulate():
     """Two-view triangulation as at sfm.py:214-221: the REAL cv2.triangulatePoints (OpenCV, the call the reference makes)
     and the reference's own restatement triangulate_points_linear2 (cv2_lite/triangulate_points.py:66-94, loaded by path)
@@ -364,6 +403,8 @@ if __name__ == "__main__":
         gen_scipy([int(a) for a in sys.argv[2:]] or [0, 1, 2])
     elif what == "poses":
         gen_poses()
+    elif what == "pnp":
+        gen_pnp()
     elif what == "triangulate":
         gen_triangulate()
     elif what == "reproj":

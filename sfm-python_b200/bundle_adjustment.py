@@ -200,6 +200,21 @@ class Engine:
         self._check(self.lib.b200ba_unpack_cameras(self.h, len(P), _ptr(P), _ptr(out)))
         return out
 
+    def solve_pnp_batch(self, problems, K, guesses=None, max_iter=100):
+        """Independent PnP problems ``[(points3d (n, 3), points2d (n, 2)), ...]`` in one launch; returns ``(m, 9)`` rows
+        ``rvec(3) tvec(3) cost iterations status`` (``cv2.solvePnP`` of ``sfm.py:207-208``, ``R X + t`` convention)."""
+        counts = np.asarray([len(p[0]) for p in problems], dtype=np.int64)
+        X = np.ascontiguousarray(np.concatenate([np.asarray(p[0], dtype=np.float64).reshape(-1, 3) for p in problems]))
+        uv = np.ascontiguousarray(np.concatenate([np.asarray(p[1], dtype=np.float64).reshape(-1, 2) for p in problems]))
+        if len(X) != counts.sum() or len(uv) != counts.sum():
+            raise ValueError("points3d and points2d differ in length")
+        Kc = np.ascontiguousarray(K, dtype=np.float64)
+        g = None if guesses is None else np.ascontiguousarray(guesses, dtype=np.float64).reshape(len(problems), 6)
+        out = np.empty((len(problems), 9), dtype=np.float64)
+        self._check(self.lib.b200ba_solve_pnp(self.h, len(problems), _ptr(counts), _ptr(X), _ptr(uv), _ptr(Kc), _ptr(g),
+                                              int(max_iter), _ptr(out)))
+        return out
+
     def triangulate(self, M1, M2, pts1, pts2, H1=None, H2=None):
         """DLT triangulation of ``sfm.py:216-217`` for ``(n, 2)`` point arrays; returns ``X (n, 4)`` rows ``[X Y Z 1]`` and,
         when the poses ``H1, H2`` are given, the visibility mask of ``sfm.py:219-221``."""
@@ -370,6 +385,15 @@ def unpack_parameters(x, n_cam, engine=None):
     x = np.asarray(x, dtype=np.float64)
     Hs = (engine or _aux_engine()).unpack_cameras(x[:6 * n_cam])
     return Hs, x[6 * n_cam:].reshape(-1, 3)
+
+
+def solve_pnp(point3ds, point2ds, K, dist_coeffs=None, engine=None, **kw):
+    """``cv2.solvePnP(point3ds, point2ds, K, np.zeros((1, 5)))`` as called at ``sfm.py:207-208`` (and the reference's
+    ``cv2_lite.solve_pnp.solve_pnp``): returns ``(success, rvec (3, 1), tvec (3, 1))``.  Distortion must be zero."""
+    if dist_coeffs is not None and np.any(np.asarray(dist_coeffs) != 0):
+        raise NotImplementedError("lens distortion is not part of the reference's pipeline (zeros at sfm.py:207)")
+    o = (engine or _aux_engine()).solve_pnp_batch([(point3ds, point2ds)], K)[0]
+    return bool(o[8] >= 0 and np.isfinite(o[6])), o[:3].reshape(3, 1).copy(), o[3:6].reshape(3, 1).copy()
 
 
 def triangulate_points(M1, M2, pts1, pts2, engine=None):

@@ -268,6 +268,9 @@ void launch_residual(Handle* h, const double* x, const double* camprep, double* 
                      int scal_slot);
 void launch_pack_cameras(Handle* h, int64_t n, const double* H_dev, double* params_dev);
 void launch_unpack_cameras(Handle* h, int64_t n, const double* params_dev, double* H_dev);
+// probs_dev: n_problems x {const double* X, const double* uv, int n, pad} (device pointers), out_dev: n_problems x 9
+void launch_pnp(Handle* h, int n_problems, const void* probs_dev, const double* K_dev, const double* guess_dev, int max_iter,
+                double* out_dev);
 void launch_triangulate(Handle* h, int64_t n, const double* M1, const double* M2, const double* pts1, const double* pts2,
                         const double* vis1, const double* vis2, double* X_out, unsigned char* mask_out);
 void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out /*nullable, caller order*/);

@@ -220,6 +220,8 @@ __global__ void k_unpack_cameras(int64_t n, const double* __restrict__ params, d
   h[12] = 0.0; h[13] = 0.0; h[14] = 0.0; h[15] = 1.0;
 }
 
+#include "k_pnp.cuh"
+
 // ------------------------------------------------------------------ two-view triangulation (sfm.py:214-221)
 // cv2.triangulatePoints(M1, M2, pts1.T, pts2.T) as called at sfm.py:216, i.e. the DLT the reference restates as
 // triangulate_points_linear2 (cv2_lite/triangulate_points.py:66-94): per point the 4 x 4 system

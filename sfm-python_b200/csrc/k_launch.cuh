@@ -116,6 +116,13 @@ void launch_unpack_cameras(Handle* h, int64_t n, const double* params_dev, doubl
   h->st.launches += 1;
 }
 
+void launch_pnp(Handle* h, int n_problems, const void* probs_dev, const double* K_dev, const double* guess_dev, int max_iter,
+                double* out_dev) {
+  if (n_problems <= 0) return;
+  k_pnp<<<n_problems, PNP_T, 0, h->stream>>>(reinterpret_cast<const PnpProblem*>(probs_dev), K_dev, guess_dev, max_iter, out_dev);
+  h->st.launches += 1;
+}
+
 void launch_triangulate(Handle* h, int64_t n, const double* M1, const double* M2, const double* pts1, const double* pts2,
                         const double* vis1, const double* vis2, double* X_out, unsigned char* mask_out) {
   if (n <= 0) return;

@@ -209,3 +209,37 @@ def test_edge_cases_of_the_widened_rows(engine):
     p = engine.pack_cameras(np.eye(4)[None])
     assert np.array_equal(p, np.zeros((1, 6)))
     assert np.array_equal(engine.unpack_cameras(p)[0], np.eye(4))
+
+
+# ------------------------------------------------------------------ PnP (sfm.py:207-208)
+@pytest.mark.parametrize("name", ["doc9", "s60", "s800"])
+def test_solve_pnp_vs_cv2_golden(engine, name):
+    """b200ba_solve_pnp against the REAL cv2.solvePnP and the reference's solve_pnp: same pose within 1e-5 (the bar of the
+    reference's own doctest, np.allclose), reprojection cost not above either, and equal to the oracle's minimum."""
+    import b200ba
+    d = load_golden("ref_pnp.npz")
+    X, uv, K = d[f"{name}_X"], d[f"{name}_uv"], d["K"]
+    ok, rvec, tvec = b200ba.solve_pnp(X, uv, K, np.zeros((1, 5)))
+    assert ok and rvec.shape == (3, 1) and tvec.shape == (3, 1)
+    got = np.hstack([rvec.ravel(), tvec.ravel()])
+    for ref in (d[f"{name}_cv2"], d[f"{name}_ref"]):
+        assert np.abs(got - ref).max() <= 1e-5 * np.abs(ref).max(), (got, ref)
+    R = O.rodrigues(rvec.T)[0]
+    cost = 0.5 * float(np.sum(O.reproj_error(X, uv, K, R, tvec.ravel()) ** 2))
+    assert cost <= float(d[f"{name}_cost_cv2"]) * (1 + 1e-9) and cost <= float(d[f"{name}_cost_ref"]) * (1 + 1e-9)
+    _, _, cost_o = O.solve_pnp(X, uv, K)
+    assert abs(cost - cost_o) <= 1e-9 * cost_o
+
+
+def test_solve_pnp_batch_and_guess(engine):
+    """Two problems in one launch (the two cameras of an edge, sfm.py:207-208) equal the single calls; a start from
+    cv2's answer (useExtrinsicGuess) stays there."""
+    d = load_golden("ref_pnp.npz")
+    probs = [(d["s60_X"], d["s60_uv"]), (d["s800_X"], d["s800_uv"])]
+    out = engine.solve_pnp_batch(probs, d["K"])
+    for k, name in enumerate(("s60", "s800")):
+        assert out[k, 8] == 1.0
+        assert np.abs(out[k, :6] - d[f"{name}_cv2"]).max() <= 1e-5 * np.abs(d[f"{name}_cv2"]).max()
+    g = engine.solve_pnp_batch(probs, d["K"], guesses=np.stack([d["s60_cv2"], d["s800_cv2"]]))
+    assert np.abs(g[:, :6] - out[:, :6]).max() <= 1e-6
+    assert (g[:, 7] <= out[:, 7]).all()

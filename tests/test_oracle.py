@@ -169,3 +169,15 @@ def test_triangulation_oracle_vs_cv2_and_reference():
     assert np.array_equal(O.visibility_mask(d["H1"], d["H2"], X), d["mask"])
     Xd = O.triangulate_points_linear2(d["doc_M1"], d["doc_M2"], d["doc_pts1"].T, d["doc_pts2"].T)
     assert np.abs(Xd - d["doc_X_cv2"]).max() <= 1e-9 * np.abs(d["doc_X_cv2"]).max()
+
+
+@pytest.mark.parametrize("name", ["doc9", "s60", "s800"])
+def test_pnp_oracle_vs_cv2_and_reference(name):
+    """oracle.solve_pnp (DLT + scipy refinement, solve_pnp.py:17-66) against the REAL cv2.solvePnP (sfm.py:207-208) and
+    the reference's solve_pnp on its own 9-point example and seeded scenes (ref_pnp.npz)."""
+    d = load_golden("ref_pnp.npz")
+    rv, tv, cost = O.solve_pnp(d[f"{name}_X"], d[f"{name}_uv"], d["K"])
+    got = np.hstack([rv, tv])
+    assert np.abs(got - d[f"{name}_cv2"]).max() <= 1e-5 * np.abs(d[f"{name}_cv2"]).max()
+    assert np.abs(got - d[f"{name}_ref"]).max() <= 1e-5 * np.abs(d[f"{name}_ref"]).max()
+    assert cost <= float(d[f"{name}_cost_cv2"]) * (1 + 1e-9) and cost <= float(d[f"{name}_cost_ref"]) * (1 + 1e-9)
