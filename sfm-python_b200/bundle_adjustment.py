@@ -576,9 +576,33 @@ def least_squares(fun, x0, jac="2-point", bounds=None, method="trf", ftol=1e-8, 
                          verbose=verbose, solver=solver, fixed_camera_indices=fixed)
 
 
-def install(sfm_module):
-    """Rebind the three names inside an imported ``sfm_lite.sfm`` module."""
+class _Cv2Proxy:
+    """Stands in for the ``cv2`` name inside ``sfm_lite.sfm``: ``solvePnP`` (``sfm.py:207-208``) and ``triangulatePoints``
+    (``sfm.py:216``) go to the GPU library, every other attribute (SIFT, matcher, ``findFundamentalMat`` ...) to the real
+    module."""
+
+    def __init__(self, real):
+        self._real = real
+
+    def __getattr__(self, name):
+        return getattr(self._real, name)
+
+    @staticmethod
+    def solvePnP(objectPoints, imagePoints, cameraMatrix, distCoeffs=None, *a, **kw):
+        return solve_pnp(np.asarray(objectPoints, dtype=np.float64).reshape(-1, 3),
+                         np.asarray(imagePoints, dtype=np.float64).reshape(-1, 2), cameraMatrix, distCoeffs)
+
+    @staticmethod
+    def triangulatePoints(projMatr1, projMatr2, projPoints1, projPoints2):
+        return triangulate_points(projMatr1, projMatr2, projPoints1, projPoints2)
+
+
+def install(sfm_module, geometry=False):
+    """Rebind the three names inside an imported ``sfm_lite.sfm`` module.  ``geometry=True`` also routes
+    the module's ``cv2.solvePnP`` / ``cv2.triangulatePoints`` calls (``sfm.py:207-216``) to the library."""
     sfm_module.least_squares = least_squares
     sfm_module.compute_residuals = compute_residuals
     sfm_module.create_sparsity_matrix = create_sparsity_matrix
+    if geometry and hasattr(sfm_module, "cv2") and not isinstance(sfm_module.cv2, _Cv2Proxy):
+        sfm_module.cv2 = _Cv2Proxy(sfm_module.cv2)
     return sfm_module

@@ -78,3 +78,22 @@ def test_local_problem_and_split_x():
     assert pil.min() == 0 and pil.max() == 29 and np.array_equal(pb.point_indices[sel] - 20, pil)
     xl = b200ba.dist.split_x(pb.x0, 6, 20, 50)
     assert len(xl) == 36 + 90 and np.array_equal(xl[36:], pb.x0[36 + 60:36 + 150])
+
+
+def test_install_rebinds_names_and_cv2_proxy_delegates():
+    """b200ba.install on a stand-in for the imported sfm_lite.sfm module: the three BA names are rebound; with
+    geometry=True the module's cv2 name becomes a proxy that keeps every other cv2 attribute (no GPU call here)."""
+    import types
+
+    import b200ba
+    fake_cv2 = types.SimpleNamespace(SIFT_create=lambda: "sift", NORM_L2=4, solvePnP=lambda *a: "cv2", triangulatePoints=lambda *a: "cv2")
+    mod = types.SimpleNamespace(least_squares=None, compute_residuals=None, create_sparsity_matrix=None, cv2=fake_cv2)
+    b200ba.install(mod)
+    assert mod.least_squares is b200ba.least_squares and mod.compute_residuals is b200ba.compute_residuals
+    assert mod.create_sparsity_matrix is b200ba.create_sparsity_matrix and mod.cv2 is fake_cv2
+    b200ba.install(mod, geometry=True)
+    assert mod.cv2.SIFT_create() == "sift" and mod.cv2.NORM_L2 == 4
+    assert mod.cv2.solvePnP is not fake_cv2.solvePnP and mod.cv2.triangulatePoints is not fake_cv2.triangulatePoints
+    proxy = mod.cv2
+    b200ba.install(mod, geometry=True)
+    assert mod.cv2 is proxy            # idempotent
