@@ -455,8 +455,9 @@ __global__ void __launch_bounds__(CHB_T) k_cholesky_blocked(int n, double* __res
 }  // namespace
 
 int pcg_grid(Handle* h) {
-  int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg, PCG_T, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  static int per_sm = 0;   // queried once: the occupancy call sits on the path of every camera solve otherwise
+  if (per_sm == 0 &&
+      (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg, PCG_T, 0) != cudaSuccess || per_sm < 1)) per_sm = 1;
   const int64_t C = h->pb.C;
   int64_t need = std::max<int64_t>((C + (PCG_T / 32) - 1) / (PCG_T / 32), 1);
   return (int)std::min<int64_t>(need, (int64_t)per_sm * h->sm_count);
@@ -540,8 +541,9 @@ int launch_pcg2(Handle* h, double rtol, int max_iter) {
   g.cam_agg = pb.cam_agg; g.agg_off = pb.agg_off; g.agg_cams = pb.agg_cams; g.sp_rowptr = pb.sp_rowptr; g.sp_col = pb.sp_col;
   g.G = w.tl_G; g.SP = w.tl_SP; g.Ainv = w.tl_A; g.rc = w.tl_rc; g.zc = w.tl_zc; g.uf = w.tl_uf; g.prof = w.tl_prof;
   void* args[] = {&g};
-  int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg2, PCG_T, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  static int per_sm = 0;
+  if (per_sm == 0 &&
+      (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg2, PCG_T, 0) != cudaSuccess || per_sm < 1)) per_sm = 1;
   const int64_t need = std::max<int64_t>((pb.C + (PCG_T / 32) - 1) / (PCG_T / 32), 1);
   const int grid = (int)std::min<int64_t>(std::min<int64_t>(need, (int64_t)per_sm * h->sm_count), pcg_grid(h));
   BA_CUDA(h, cudaLaunchCooperativeKernel((void*)k_pcg2, dim3(grid), dim3(PCG_T), args, 0, h->stream));
