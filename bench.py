@@ -389,6 +389,42 @@ def run_b200(a, rank, world, local_rank):
                        "k_residual": {"bound": "hbm", "ms": tr * 1e3, "achieved": br / tr / 1e9, "peak": pk, "unit": "GB/s",
                                       "frac": br / tr / 1e9 / pk, "bytes_per_obs": 40,
                                       "note": "k_cam_prep + k_residual + the partial reduction"}}
+    # ---- BASELINE configs[0]: the nine global BA calls of the SceauxCastle run (frozen problems, tests/golden) through the
+    #      drop-in call of sfm.py:264-268, host arrays in, result.x out; beside it the reference's own times for the same
+    #      calls as recorded when the goldens were made (real reference residual + scipy on calls 0-2, scipy with the
+    #      vectorised residual on all nine; another machine's CPU, quoted for orientation only)
+    config_a = None
+    gold = os.path.join(ROOT, "tests", "golden")
+    if world == 1 and os.path.exists(os.path.join(gold, "sceaux_ba_0.npz")):
+        calls, per_call, ref_vec, ref_real = [], [], [], []
+        rr = np.load(os.path.join(gold, "sceaux_scipy_ref.npz"))
+        for k in range(9):
+            fn = os.path.join(gold, f"sceaux_ba_{k}.npz")
+            if not os.path.exists(fn):
+                break
+            d = np.load(fn)
+            calls.append((d["x0"], (int(d["n_cam"]), int(d["n_pts"]), d["ci"], d["pi"], d["uv"], d["K"]), float(d["ftol"])))
+            ref_vec.append(float(d["scipy_t"]))
+            if f"t_{k}" in rr.files:
+                ref_real.append(float(rr[f"t_{k}"]))
+        def replay():
+            out = []
+            for x0, args, ftol in calls:
+                t0 = time.perf_counter()
+                mask = b200ba.create_sparsity_matrix(args[0], args[1], len(args[2]), args[2], args[3])
+                res = b200ba.least_squares(b200ba.compute_residuals, x0, jac_sparsity=mask, verbose=0, x_scale="jac",
+                                           ftol=ftol, method="trf", args=args)
+                out.append((time.perf_counter() - t0, float(res.cost)))
+            return out
+        replay()
+        per_call = replay()
+        config_a = {"what": "SceauxCastle incremental SfM, the 9 frozen global BA calls (3-7 cameras, 563-3034 observations) "
+                            "through b200ba.least_squares with host arrays (set_problem + LM solve + download per call)",
+                    "calls": len(per_call), "total_ms": 1e3 * sum(t for t, _ in per_call),
+                    "per_call_ms": [round(1e3 * t, 3) for t, _ in per_call],
+                    "reference_seconds_real_residual_calls_0_2": ref_real,
+                    "reference_seconds_vectorised_residual": ref_vec,
+                    "reference_note": "scipy times recorded on the CPU of the machine that made the goldens"}
     if rank != 0:
         return
     # ---- roofline of the dominant kernel of the step (SURVEY.md 8d family L)
@@ -447,6 +483,8 @@ def run_b200(a, rank, world, local_rank):
                      "self_slots": int(st["n_self_slots"])}}
     if hbm_kernels:
         out["roofline_hbm_kernels"] = hbm_kernels
+    if config_a:
+        out["config_A_replay"] = config_a
     out.update(lm)
     if not a.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(a.workload, a.seed, a.cpu_sample_obs)
