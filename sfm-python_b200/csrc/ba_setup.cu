@@ -338,6 +338,101 @@ struct Tmp {  // scratch freed (stream-ordered, back into the handle's pool) at 
   if (!var) return B200BA_OOM
 
 
+// ------------------------------------------------------------------ greedy packing on the device
+// Consecutive items with prefix offsets off[0..n] (non-decreasing, off[n] = total) are packed greedily into bins of at
+// most `cap`: a bin that starts at offset s ends at the largest item boundary <= s + cap, or -- when the first item alone
+// is larger -- after that item.  This is the host loop "close the bin when the next item would overflow it", restated
+// without the loop-carried dependence: nxt[p] (the item that starts the next bin) is a binary search per item, the bin
+// starts are the orbit of item 0 under nxt, and the orbit is enumerated by pointer doubling (J_k = nxt^(2^k)): bin i
+// starts at the item reached by the jumps of the set bits of i.  O(n log n) work in log n parallel passes instead of
+// n dependent steps on one host core (config D: 4 M points, 8-10 ms on the host).
+__global__ void k_gb_next(int n, const int* __restrict__ off, int cap, int* __restrict__ nxt) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p > n) return;
+  const int total = off[n], s = off[p];
+  if (s >= total) { nxt[p] = n; return; }
+  int lo = p, hi = n + 1;                 // last index j in [p, n] with off[j] <= s + cap
+  while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (off[mid] <= s + cap) lo = mid; else hi = mid; }
+  int j = lo;
+  if (off[j] <= s) {                      // the first item alone overflows the bin: first index with off > s
+    lo = p; hi = n;                       // off[n] = total > s
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (off[mid] <= s) lo = mid; else hi = mid; }
+    j = hi;
+  }
+  nxt[p] = j;
+}
+
+__global__ void k_gb_double(int m, const int* __restrict__ prev, int* __restrict__ next) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < m) next[p] = prev[prev[p]];
+}
+
+// number of bins = 1 + number of jumps from item 0 that do not yet reach the end
+__global__ void k_gb_count(int n, const int* __restrict__ off, const int* __restrict__ J, int K, int* __restrict__ out) {
+  if (blockIdx.x || threadIdx.x) return;
+  const int total = off[n];
+  if (total <= 0) { *out = 0; return; }
+  int p = 0, cnt = 0;
+  for (int k = K - 1; k >= 0; --k) {
+    const int q = J[(int64_t)k * (n + 1) + p];
+    if (off[q] < total) { p = q; cnt += 1 << k; }
+  }
+  *out = cnt + 1;
+}
+
+// bin_item[i] = first item of bin i (i < n_bins), bin_item[n_bins] = n;  bin_off[i] = off[bin_item[i]]
+__global__ void k_gb_starts(int n_bins, int n, const int* __restrict__ off, const int* __restrict__ J, int K,
+                            int* __restrict__ bin_item, int* __restrict__ bin_off) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > n_bins) return;
+  int p = 0;
+  if (i == n_bins) p = n;
+  else
+    for (int k = 0; k < K; ++k)
+      if ((i >> k) & 1) p = J[(int64_t)k * (n + 1) + p];
+  if (bin_item) bin_item[i] = p;
+  bin_off[i] = off[p];
+}
+
+__global__ void k_max_degree(int P, const int* __restrict__ off, int* __restrict__ out) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  int d = (p < P) ? off[p + 1] - off[p] : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) d = max(d, __shfl_xor_sync(0xffffffffu, d, o));
+  if ((threadIdx.x & 31) == 0 && d > 0) atomicMax(out, d);
+}
+
+// bins of at most `cap` over the items of off[0..n]; *bin_off_out (problem lifetime, n_bins + 1 offsets) and, if asked
+// for, *bin_item_out (problem lifetime, n_bins + 1 item indices); returns the bin count through *n_bins_out
+static int greedy_bins(Handle* h, Tmp& tmp, const int* d_off, int n, int cap, int* n_bins_out, int** bin_off_out,
+                       int** bin_item_out) {
+  cudaStream_t st = h->stream;
+  const int T = 256;
+  int K = 1;
+  while (((int64_t)1 << K) <= (int64_t)n + 1 && K < 31) ++K;
+  TMP_ALLOC(d_J, int, (int64_t)K * (n + 1));
+  TMP_ALLOC(d_cnt, int, 1);
+  k_gb_next<<<(n + 1 + T - 1) / T, T, 0, st>>>(n, d_off, cap, d_J);
+  for (int k = 1; k < K; ++k)
+    k_gb_double<<<(n + 1 + T - 1) / T, T, 0, st>>>(n + 1, d_J + (int64_t)(k - 1) * (n + 1), d_J + (int64_t)k * (n + 1));
+  k_gb_count<<<1, 32, 0, st>>>(n, d_off, d_J, K, d_cnt);
+  int n_bins = 0;
+  BA_CUDA(h, cudaMemcpyAsync(&n_bins, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
+  BA_CUDA(h, cudaStreamSynchronize(st));
+  *n_bins_out = n_bins;
+  *bin_off_out = (int*)dalloc(h, (size_t)(n_bins + 1) * sizeof(int));
+  if (!*bin_off_out) return B200BA_OOM;
+  int* items = nullptr;
+  if (bin_item_out) {
+    items = (int*)dalloc(h, (size_t)(n_bins + 1) * sizeof(int));
+    if (!items) return B200BA_OOM;
+    *bin_item_out = items;
+  }
+  k_gb_starts<<<(n_bins + 1 + T - 1) / T, T, 0, st>>>(n_bins, n, d_off, d_J, K, items, *bin_off_out);
+  BA_CUDA(h, cudaGetLastError());
+  return 0;
+}
+
 // Slots of a tile-grouped entry list.  Input: the (tile, id) cells of the list in sorted order (cellkey = tile * M + id,
 // cnt = entries per cell; both with room for n_cell + 1 elements).  Every cell is cut into slots of <= SLOT_CAP entries;
 // the slots of a tile are ordered by decreasing entry count (lanes of a warp finish together); grp_* lists the slots
@@ -485,27 +580,17 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
 
   mark("2 point-major order");
-  // ---- 3. warp tiles (host greedy packing of whole points into <= 32 observations)
-  std::vector<int> h_pt_off(P + 1, 0);
-  BA_CUDA(h, cudaMemcpyAsync(h_pt_off.data(), pb.pt_off, (P + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
-  BA_CUDA(h, cudaStreamSynchronize(st));
+  // ---- 3. warp tiles: greedy packing of whole points into <= 32 observations (a point with more is its own tile),
+  //         CTA tiles: greedy packing of warp tiles into <= tile_obs observations -- both on the device (greedy_bins)
   {
-    std::vector<int> wt;
-    wt.reserve(N / 24 + 16);
-    wt.push_back(0);
-    int start = 0, max_deg = 0;
-    for (int64_t p = 0; p < P; ++p) {
-      int e = h_pt_off[p + 1];
-      max_deg = std::max(max_deg, e - h_pt_off[p]);
-      if (e - start > 32) {
-        if (h_pt_off[p] > start) wt.push_back(h_pt_off[p]);  // close the tile before this point
-        start = wt.back();
-        if (e - start > 32) { wt.push_back(e); start = e; }  // a point with > 32 observations: its own tile
-      }
+    int max_deg = 0;
+    {
+      TMP_ALLOC(d_md, int, 1);
+      BA_CUDA(h, cudaMemsetAsync(d_md, 0, sizeof(int), st));
+      if (P > 0) k_max_degree<<<nblk(P, T), T, 0, st>>>((int)P, pb.pt_off, d_md);
+      BA_CUDA(h, cudaMemcpyAsync(&max_deg, d_md, sizeof(int), cudaMemcpyDeviceToHost, st));
     }
-    if ((int)N > start) wt.push_back((int)N);
-    pb.n_wt = (int)wt.size() - 1;
-    if (int rc = upload(h, &pb.wt_off, wt)) return rc;
+    if (int rc = greedy_bins(h, tmp, pb.pt_off, (int)P, 32, &pb.n_wt, &pb.wt_off, nullptr)) return rc;   // syncs: max_deg is in
     // CTA tiles: runs of warp tiles (whole points) with at most tile_obs observations (records fit shared memory)
     const char* e_fused = getenv("B200BA_FUSED");        // 0: unfused A/B path (k_lin_points + k_cam_side + k_schur_tiles)
     const char* e_tile = getenv("B200BA_TILE_OBS");      // tuning sweeps
@@ -520,24 +605,22 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     const char* force_stream = getenv("B200BA_SCHUR_STREAM");
     pb.schur_tiles = max_deg <= tile_obs && !(force_stream && atoi(force_stream));
     if (pb.schur_tiles) {
-      std::vector<int> stv, stw;
-      stv.push_back(0); stw.push_back(0);
-      int ts = 0;
-      for (size_t k = 1; k < wt.size(); ++k)
-        if (wt[k] - ts > tile_obs) { stv.push_back(wt[k - 1]); stw.push_back((int)k - 1); ts = wt[k - 1]; }
-      if ((int)N > ts) { stv.push_back((int)N); stw.push_back((int)wt.size() - 1); }
-      pb.n_st = (int)stv.size() - 1;
+      int n_st = 0;
+      int* st_off = nullptr;
+      int* st_wt = nullptr;
+      if (int rc = greedy_bins(h, tmp, pb.wt_off, pb.n_wt, tile_obs, &n_st, &st_off, &st_wt)) return rc;
+      pb.n_st = n_st;
       pb.tile_obs = tile_obs;
       if ((double)(pb.n_st + 1) * (double)C * (double)C >= 4.0e18) pb.schur_tiles = false;  // key would overflow
       else {
         pb.fused = want_fused;
-        if (int rc = upload(h, &pb.st_off, stv)) return rc;
-        if (int rc = upload(h, &pb.st_wt_off, stw)) return rc;
+        pb.st_off = st_off;
+        pb.st_wt_off = st_wt;
       }
     }
   }
 
-  mark("3 warp/CTA tiles (host)");
+  mark("3 warp/CTA tiles");
   // ---- 4. camera-sorted permutation and chunks
   DEV_ALLOC(pb.cperm, int, N);
   DEV_ALLOC(pb.cam_off, int, C + 1);

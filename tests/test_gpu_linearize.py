@@ -131,3 +131,45 @@ def test_fused_is_bit_reproducible():
     b = eng.normal_equations(pb.x0, 1e-4)
     assert np.array_equal(a["S"], b["S"]) and np.array_equal(a["b"], b["b"]) and a["cost"] == b["cost"]
     eng.close()
+
+
+def test_device_tile_construction_equals_the_greedy_loop(engine):
+    """Warp tiles are built on the device by pointer doubling (ba_setup.cu greedy_bins); they must equal the sequential
+    greedy rule 'close the tile when the next point would push it past 32 observations, a larger point is its own
+    tile' on a ragged problem: degrees 1..70, runs of unobserved points, one camera."""
+    rng = np.random.default_rng(12)
+    n_pts = 5000
+    deg = rng.integers(1, 9, n_pts)
+    deg[rng.choice(n_pts, 40, replace=False)] = rng.integers(33, 71, 40)      # points with more than a warp of observations
+    deg[rng.choice(n_pts, 300, replace=False)] = 0                              # unobserved points
+    deg[:3] = 0
+    deg[-2:] = 0
+    pi = np.repeat(np.arange(n_pts), deg)
+    n = len(pi)
+    ci = rng.integers(0, 6, n)
+    uv = rng.uniform(0, 2000, (n, 2))
+    K = np.array([[2900.0, 0, 1400], [0, 2900, 1000], [0, 0, 1]])
+    engine.set_problem(6, n_pts, ci, pi, uv, K)
+    off = np.concatenate([[0], np.cumsum(deg)])
+    wt, start = [0], 0
+    for p in range(n_pts):                                   # the rule, literally
+        e = off[p + 1]
+        if e - start > 32:
+            if off[p] > start:
+                wt.append(off[p])
+            start = wt[-1]
+            if e - start > 32:
+                wt.append(e)
+                start = e
+    if n > start:
+        wt.append(n)
+    got = engine.debug_fetch("wt_off", len(wt) + 8, dtype=np.int32)
+    assert len(got) == len(wt) and np.array_equal(got, np.asarray(wt))
+    # and the residual on this ragged layout still matches the oracle
+    x = np.concatenate([rng.normal(0, 0.05, 36), rng.uniform(-1, 1, (n_pts, 2)).ravel()[:0]])
+    cams = rng.normal(0, 0.05, (6, 6))
+    pts = np.stack([rng.uniform(-1, 1, n_pts), rng.uniform(-1, 1, n_pts), rng.uniform(5, 9, n_pts)], 1)
+    x = np.concatenate([cams.ravel(), pts.ravel()])
+    r = engine.residuals(x)
+    r_ref = O.residuals(x, 6, n_pts, ci, pi, uv, K)
+    assert np.abs(r - r_ref).max() <= 1e-9 * np.abs(r_ref).max()
