@@ -210,6 +210,8 @@ struct Handle {
   int device = 0;
   int sm_count = 148;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;   // set_problem: upload of the pixel array underneath the index pipeline
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
   cudaMemPool_t pool = nullptr;   // stream-ordered pool that keeps freed blocks: re-running set_problem costs no cudaMalloc
   std::string err;
   bool has_problem = false;

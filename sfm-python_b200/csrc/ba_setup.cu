@@ -31,14 +31,23 @@ __global__ void k_check_convert(int64_t N, int64_t C, int64_t P, const int64_t* 
 }
 
 __global__ void k_gather_obs(int64_t N, const int* __restrict__ perm, const int* __restrict__ cam_in,
-                             const double* __restrict__ uv, int* __restrict__ cam, double* __restrict__ u,
-                             double* __restrict__ v) {
+                             int* __restrict__ cam) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= N) return;
   int64_t s = perm ? perm[i] : i;
   cam[i] = cam_in[s];
-  u[i] = uv[2 * s];
-  v[i] = uv[2 * s + 1];
+}
+
+// pixels into point-major order; runs at the END of set_problem: their upload travels on a second stream underneath
+// the index pipeline (tiles, camera permutation, pair entries need indices only)
+__global__ void k_gather_uv(int64_t N, const int* __restrict__ perm, const double* __restrict__ uv, double* __restrict__ u,
+                            double* __restrict__ v) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  int64_t s = perm ? perm[i] : i;
+  const double2 p = reinterpret_cast<const double2*>(uv)[s];
+  u[i] = p.x;
+  v[i] = p.y;
 }
 
 // off[q] = first index i with key[i] >= q, for q in [0, M]; keys sorted ascending.
@@ -322,7 +331,10 @@ struct Tmp {  // scratch freed (stream-ordered, back into the handle's pool) at 
   Handle* h;
   std::vector<void*> p;
   explicit Tmp(Handle* hh) : h(hh) {}
-  ~Tmp() { for (void* q : p) pool_free(h, q); }
+  ~Tmp() {
+    if (h->stream2) cudaStreamSynchronize(h->stream2);   // an early return must not free d_uv under a running upload
+    for (void* q : p) pool_free(h, q);
+  }
   void* get(size_t bytes) {
     void* q = pool_alloc(h, std::max<size_t>(bytes, 16));
     if (q) p.push_back(q);
@@ -547,7 +559,11 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   if (N > 0) {
     BA_CUDA(h, cudaMemcpyAsync(d_cam64, cam_idx, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));
     BA_CUDA(h, cudaMemcpyAsync(d_pt64, pt_idx, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));
-    BA_CUDA(h, cudaMemcpyAsync(d_uv, uv, 2 * N * sizeof(double), cudaMemcpyHostToDevice, st));
+    // the pixel array (half of the upload) goes on the second stream; nothing needs it before k_gather_uv at the end
+    BA_CUDA(h, cudaEventRecord(h->ev_a, st));                 // d_uv is a stream-ordered allocation of `st`
+    BA_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_a, 0));
+    BA_CUDA(h, cudaMemcpyAsync(d_uv, uv, 2 * N * sizeof(double), cudaMemcpyHostToDevice, h->stream2));
+    BA_CUDA(h, cudaEventRecord(h->ev_b, h->stream2));
     k_check_convert<<<nblk(N, T), T, 0, st>>>(N, C, P, d_cam64, d_pt64, d_cam_in, d_pt_in, d_iota, d_flags);
   }
   int flags = 0;
@@ -575,7 +591,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     BA_CUDA(h, cudaMemcpyAsync(pb.pt, d_pt_in, N * sizeof(int), cudaMemcpyDeviceToDevice, st));
   }
   if (N > 0) {
-    k_gather_obs<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_cam_in, d_uv, pb.cam, pb.u, pb.v);
+    k_gather_obs<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_cam_in, pb.cam);
     k_offsets<<<nblk(N, T), T, 0, st>>>(N, (int)P, pb.pt, pb.pt_off);
   }
 
@@ -1059,6 +1075,11 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     }
   }
   mark("10 dataflow blobs");
+  if (N > 0) {
+    BA_CUDA(h, cudaStreamWaitEvent(st, h->ev_b, 0));
+    k_gather_uv<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_uv, pb.u, pb.v);
+  }
+  mark("11 pixels");
   BA_CUDA(h, cudaStreamSynchronize(st));
   BA_CUDA(h, cudaGetLastError());
   h->st.schur_entries = pb.n_ent;
