@@ -393,6 +393,41 @@ def gen_synthB():
                         lm_cost=lm["cost"], lm_rms=lm["rms"], x0_sum=float(pb.x0.sum()))
 
 
+def gen_configB():
+    """BASELINE.md section 3 R2 on the repo's own config B (49 / 7776 / 31843): scipy TRF with the sfm.py:266-268 kwargs and
+    the vectorised residual, run to the end (about 40 min of CPU), with a (seconds, cost) trace of every residual
+    evaluation for time-to-cost; beside it the oracle LM minimum from the same start and the arbiter (scipy restarted
+    from the oracle-LM point with ftol = xtol = 1e-15 must not lower the cost by 1e-6)."""
+    syn = synthetic()
+    pb = syn.make_config("B")
+    args = pb.args()
+    trace = []
+    t0 = time.time()
+
+    def fun(x, *a):
+        r = O.residuals(x, *a)
+        trace.append((time.time() - t0, 0.5 * float(r @ r)))
+        return r
+
+    sc = O.scipy_solve(pb.x0, *args, ftol=1e-10, fun=fun)
+    secs = time.time() - t0
+    tr = np.asarray(trace)
+    reach = tr[tr[:, 1] <= sc.cost * (1 + 1e-6)]
+    ttc = float(reach[0, 0]) if len(reach) else secs
+    print("scipy R2: cost", sc.cost, "status", sc.status, "nfev", sc.nfev, "njev", sc.njev, "seconds", secs, "time-to-cost", ttc)
+    t1 = time.time()
+    lm = O.lm_solve(pb.x0, *args, ftol=1e-10)
+    lm_secs = time.time() - t1
+    arb = O.scipy_solve(lm["x"], *args, ftol=1e-15, xtol=1e-15, max_nfev=6)
+    print("oracle LM: cost", lm["cost"], "iterations", lm["nit"], "seconds", lm_secs, "arbiter cost", arb.cost)
+    # thin the trace: every 16th evaluation is plenty for a time-to-cost curve
+    np.savez_compressed(os.path.join(GOLD, "configB_scipy.npz"), seed=0, x0_sum=float(pb.x0.sum()), scipy_cost=sc.cost,
+                        scipy_rms=O.rms(sc.fun), scipy_status=sc.status, scipy_nfev=sc.nfev, scipy_njev=sc.njev,
+                        scipy_optimality=sc.optimality, scipy_seconds=secs, scipy_time_to_cost=ttc, scipy_x=sc.x,
+                        trace=tr[::16], lm_cost=lm["cost"], lm_rms=lm["rms"], lm_iterations=lm["nit"],
+                        lm_seconds=lm_secs, arbiter_from_lm_cost=arb.cost, scipy_version=__import__("scipy").__version__)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "residual"
     if what == "residual":
@@ -413,3 +448,5 @@ if __name__ == "__main__":
         gen_fixed([int(a) for a in sys.argv[2:]] or [0, 1, 2])
     elif what == "synthB":
         gen_synthB()
+    elif what == "configB":
+        gen_configB()

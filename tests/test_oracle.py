@@ -1,9 +1,12 @@
 """CPU: the numpy oracle pinned to outputs of the REAL reference (tests/golden, made by oracle/make_golden.py)."""
+import os
+import sys
+
 import numpy as np
 import pytest
 
 import ba_oracle as O
-from conftest import golden_args, load_golden
+from conftest import ROOT, golden_args, load_golden
 
 FIX = ["ref_residual_small.npz", "ref_residual_int_unsorted.npz", "ref_residual_pnp9.npz", "ref_residual_B2000.npz",
        "ref_residual_angles_skewK.npz"]
@@ -181,3 +184,20 @@ def test_pnp_oracle_vs_cv2_and_reference(name):
     assert np.abs(got - d[f"{name}_cv2"]).max() <= 1e-5 * np.abs(d[f"{name}_cv2"]).max()
     assert np.abs(got - d[f"{name}_ref"]).max() <= 1e-5 * np.abs(d[f"{name}_ref"]).max()
     assert cost <= float(d[f"{name}_cost_cv2"]) * (1 + 1e-9) and cost <= float(d[f"{name}_cost_ref"]) * (1 + 1e-9)
+
+
+def test_configB_golden_is_consistent():
+    """tests/golden/configB_scipy.npz (full scipy R2 solve of config B): the stored scipy solution reproduces the stored
+    cost through the oracle residual, scipy stopped above the oracle LM minimum, and the arbiter could not go lower."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("b200ba_synthetic_t", os.path.join(ROOT, "sfm-python_b200", "synthetic.py"))
+    syn = importlib.util.module_from_spec(spec)
+    sys.modules["b200ba_synthetic_t"] = syn
+    spec.loader.exec_module(syn)
+    g = load_golden("configB_scipy.npz")
+    pb = syn.make_config("B")
+    assert abs(float(pb.x0.sum()) - float(g["x0_sum"])) <= 1e-9 * abs(float(g["x0_sum"]))
+    r = O.residuals(g["scipy_x"], *pb.args())
+    assert abs(0.5 * float(r @ r) - float(g["scipy_cost"])) <= 1e-12 * float(g["scipy_cost"])
+    assert float(g["lm_cost"]) <= float(g["scipy_cost"])
+    assert float(g["lm_cost"]) - float(g["arbiter_from_lm_cost"]) <= 1e-6 * float(g["lm_cost"])
