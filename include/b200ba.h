@@ -180,6 +180,15 @@ int b200ba_lm_step(b200ba_handle* h, const double* x, double lambda, int solver,
  * Call after b200ba_set_problem (which clears the set); n = 0 frees every camera.  On every rank of a multi-GPU job. */
 int b200ba_set_fixed_cameras(b200ba_handle* h, const int64_t* cam_idx, int64_t n);
 
+/* Robust loss of the solve: the `loss=` / `f_scale=` keywords of scipy.optimize.least_squares at the call of sfm.py:266
+ * (the reference leaves scipy's default 'linear').  scipy's exact scaling is reproduced per residual component:
+ * z = (f / f_scale)^2, cost = 0.5 f_scale^2 sum rho(z), J <- sqrt(max(rho' + 2 rho'' z, eps)) J, f <- rho' f / sqrt(...)
+ * (scipy _lsq/least_squares.py construct_loss_function, _lsq/common.py scale_for_robust_loss_function).
+ * loss: 0 linear, 1 soft_l1, 2 huber, 3 cauchy, 4 arctan.  Call after b200ba_set_problem (which resets it to linear);
+ * b200ba_residuals / b200ba_jacobian_blocks stay the plain residual and blocks (scipy's `fun` and `jac`); b200ba_solve,
+ * b200ba_normal_equations and b200ba_lm_step use the scaled ones.  On every rank of a multi-GPU job. */
+int b200ba_set_loss(b200ba_handle* h, int loss, double f_scale);
+
 /* Preconditioner of the reduced-camera PCG (the reference's scipy step has no counterpart; scipy's LSMR is
  * unpreconditioned): 0 = block-Jacobi only, 1 = automatic (default: block-Jacobi until a solve needs more than 24
  * iterations, then the two-level preconditioner with a lagged coarse operator), 2 = two-level from the first solve,

@@ -206,16 +206,65 @@ def dense_jacobian(x, n_cameras, n_points, camera_indices, point_indices, K):
     return J
 
 
+
+# --------------------------------------------------------------------------
+# Robust loss (scipy's loss= / f_scale= keywords of the call at sfm.py:266; the reference keeps 'linear')
+# restated from scipy _lsq/least_squares.py (soft_l1 / huber / cauchy / arctan, construct_loss_function) and
+# _lsq/common.py scale_for_robust_loss_function; pinned against scipy itself in tests/golden/robust_scipy.npz.
+# --------------------------------------------------------------------------
+
+def robust_rho(z, loss):
+    """rho(z), rho'(z), rho''(z) for z = (f / f_scale)^2, elementwise."""
+    z = np.asarray(z, dtype=np.float64)
+    if loss == "linear":
+        return z, np.ones_like(z), np.zeros_like(z)
+    if loss == "soft_l1":
+        t = 1.0 + z
+        return 2.0 * (np.sqrt(t) - 1.0), t ** -0.5, -0.5 * t ** -1.5
+    if loss == "huber":
+        m = z <= 1.0
+        zs = np.where(m, 1.0, z)
+        return (np.where(m, z, 2.0 * np.sqrt(zs) - 1.0), np.where(m, 1.0, zs ** -0.5),
+                np.where(m, 0.0, -0.5 * zs ** -1.5))
+    if loss == "cauchy":
+        t = 1.0 + z
+        return np.log1p(z), 1.0 / t, -1.0 / t ** 2
+    if loss == "arctan":
+        t = 1.0 + z * z
+        return np.arctan(z), 1.0 / t, -2.0 * z / t ** 2
+    raise ValueError(loss)
+
+
+def robust_cost(r, loss="linear", f_scale=1.0):
+    """0.5 * f_scale^2 * sum(rho((r / f_scale)^2)): scipy's OptimizeResult.cost under a robust loss."""
+    r = np.asarray(r, dtype=np.float64)
+    if loss == "linear":
+        return 0.5 * float(np.sum(r * r))
+    return 0.5 * f_scale ** 2 * float(np.sum(robust_rho((r / f_scale) ** 2, loss)[0]))
+
+
+def robust_scale(r, loss, f_scale):
+    """(row factors of J, scaled residual) of scale_for_robust_loss_function for residual components r (any shape)."""
+    z = (r / f_scale) ** 2
+    _, r1, r2 = robust_rho(z, loss)
+    js = np.sqrt(np.maximum(r1 + 2.0 * r2 * z, np.finfo(float).eps))
+    return js, r * r1 / js
+
 # --------------------------------------------------------------------------
 # Normal equations + point-block Schur complement (SURVEY 8 a7/a8)
 # --------------------------------------------------------------------------
 
-def normal_blocks(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
+def normal_blocks(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, loss="linear", f_scale=1.0):
     """U (C,6,6), V (P,3,3), gc (C,6), gp (P,3), cost = 0.5 sum r^2, plus per-observation Jc, Jp, r."""
     ci = np.asarray(camera_indices)
     pi = np.asarray(point_indices)
     r = residuals(x, n_cameras, n_points, ci, pi, points_2d, K).reshape(-1, 2)
     Jc, Jp = jacobian_blocks(x, n_cameras, n_points, ci, pi, K)
+    cost = robust_cost(r, loss, f_scale)
+    if loss != "linear":
+        js, r = robust_scale(r, loss, f_scale)
+        Jc = Jc * js[:, :, None]
+        Jp = Jp * js[:, :, None]
     U = np.zeros((n_cameras, 6, 6))
     V = np.zeros((n_points, 3, 3))
     gc = np.zeros((n_cameras, 6))
@@ -224,10 +273,10 @@ def normal_blocks(x, n_cameras, n_points, camera_indices, point_indices, points_
     np.add.at(V, pi, np.einsum("nri,nrj->nij", Jp, Jp))
     np.add.at(gc, ci, np.einsum("nri,nr->ni", Jc, r))
     np.add.at(gp, pi, np.einsum("nri,nr->ni", Jp, r))
-    return dict(U=U, V=V, gc=gc, gp=gp, cost=0.5 * float(np.sum(r * r)), Jc=Jc, Jp=Jp, r=r)
+    return dict(U=U, V=V, gc=gc, gp=gp, cost=cost, Jc=Jc, Jp=Jp, r=r)
 
 
-def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam):
+def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam, loss="linear", f_scale=1.0):
     """Dense reduced camera system with Marquardt damping  (H + lam diag H) d = -g.
 
     S = U* - sum_p W_p V_p*^-1 W_p^T,  b = -gc + sum_p W_p V_p*^-1 gp  (SURVEY 8 a8).
@@ -235,7 +284,7 @@ def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2
     """
     ci = np.asarray(camera_indices)
     pi = np.asarray(point_indices)
-    nb = normal_blocks(x, n_cameras, n_points, ci, pi, points_2d, K)
+    nb = normal_blocks(x, n_cameras, n_points, ci, pi, points_2d, K, loss, f_scale)
     U, V, gc, gp, Jc, Jp = nb["U"], nb["V"], nb["gc"], nb["gp"], nb["Jc"], nb["Jp"]
     Us = U.copy()
     Vs = V.copy()
@@ -265,12 +314,13 @@ def schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2
     return dict(S=S, b=b, Vinv=Vinv, W=W, **nb)
 
 
-def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam, fixed_cameras=()):
+def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam, fixed_cameras=(), loss="linear",
+            f_scale=1.0):
     """One damped Gauss-Newton step via the Schur complement; returns (delta, predicted_reduction, sys).
 
     ``fixed_cameras``: the ``fixed_camera_indices`` hook of bundle_adjustment.py:6,13 -- those cameras' Jacobian
     columns are masked out in the reference, i.e. rows/columns of the reduced system are deleted (delta_c = 0)."""
-    s = schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam)
+    s = schur_system(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K, lam, loss, f_scale)
     ci = np.asarray(camera_indices)
     pi = np.asarray(point_indices)
     for c in fixed_cameras:
@@ -292,7 +342,8 @@ def lm_step(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
 
 
 def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, K,
-             ftol=1e-10, xtol=1e-8, gtol=1e-8, max_iter=100, lam0=1e-4, verbose=0, fixed_cameras=()):
+             ftol=1e-10, xtol=1e-8, gtol=1e-8, max_iter=100, lam0=1e-4, verbose=0, fixed_cameras=(), loss="linear",
+             f_scale=1.0):
     """Reference LM loop (numpy twin of the engine's b200ba_solve).
 
     Marquardt damping lam*diag(H); accept iff the cost decreases; Nielsen update
@@ -302,12 +353,12 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
     x = np.array(x0, dtype=np.float64)
     args = (n_cameras, n_points, camera_indices, point_indices, points_2d, K)
     r = residuals(x, *args)
-    cost = 0.5 * float(r @ r)
+    cost = robust_cost(r, loss, f_scale)
     lam, nu = lam0, 2.0
     status, nfev, it = 0, 1, 0
     while it < max_iter:
         it += 1
-        delta, pred, s = lm_step(x, *args, lam, fixed_cameras)
+        delta, pred, s = lm_step(x, *args, lam, fixed_cameras, loss, f_scale)
         g = np.concatenate([s["gc"].reshape(-1), s["gp"].reshape(-1)])
         gnorm = float(np.max(np.abs(g)))
         if gnorm < gtol:
@@ -316,7 +367,7 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
         x_new = x + delta
         r_new = residuals(x_new, *args)
         nfev += 1
-        cost_new = 0.5 * float(r_new @ r_new)
+        cost_new = robust_cost(r_new, loss, f_scale)
         actual = cost - cost_new
         rho = actual / pred if pred > 0 else -1.0
         step_norm = float(np.linalg.norm(delta))
@@ -344,7 +395,7 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
             lam *= nu
             nu *= 2.0
     r = residuals(x, *args)
-    return dict(x=x, cost=0.5 * float(r @ r), fun=r, status=status, nit=it, nfev=nfev,
+    return dict(x=x, cost=robust_cost(r, loss, f_scale), fun=r, status=status, nit=it, nfev=nfev,
                 rms=float(np.sqrt(np.mean(r * r))))
 
 

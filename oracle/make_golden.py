@@ -428,6 +428,41 @@ def gen_configB():
                         lm_seconds=lm_secs, arbiter_from_lm_cost=arb.cost, scipy_version=__import__("scipy").__version__)
 
 
+def gen_robust(ks=(0, 1, 2)):
+    """scipy's robust losses on the frozen SceauxCastle BA calls with 5 % gross outliers injected into the pixels (seeded):
+    least_squares(..., loss=L, f_scale=2.0) with the sfm.py:266-268 kwargs -- through the REAL reference residual and mask on
+    call 0, through the vectorised oracle residual on the later calls -- next to the oracle LM with the same loss."""
+    ref = ref_ba()
+    from scipy.optimize import least_squares
+    out = {}
+    f_scale = 2.0
+    for k in ks:
+        d = np.load(os.path.join(GOLD, f"sceaux_ba_{k}.npz"))
+        n_cam, n_pts, ci, pi, K = int(d["n_cam"]), int(d["n_pts"]), d["ci"], d["pi"], d["K"]
+        rng = np.random.default_rng([77, k])
+        uv = d["uv"].copy()
+        bad = rng.choice(len(ci), size=max(len(ci) // 20, 1), replace=False)
+        uv[bad] += rng.integers(-150, 151, size=(len(bad), 2)).astype(uv.dtype)
+        out[f"uv_{k}"] = uv
+        args = (n_cam, n_pts, ci, pi, uv, K)
+        for loss in ("soft_l1", "huber", "cauchy"):
+            t = time.time()
+            if k == 0:
+                mask = ref.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi)
+                sc = least_squares(ref.compute_residuals, d["x0"], jac_sparsity=mask, verbose=0, x_scale="jac",
+                                   ftol=1e-10, method="trf", loss=loss, f_scale=f_scale, args=args)
+            else:
+                sc = O.scipy_solve(d["x0"], *args, ftol=1e-10, loss=loss, f_scale=f_scale)
+            lm = O.lm_solve(d["x0"], *args, ftol=1e-10, loss=loss, f_scale=f_scale, max_iter=200)
+            print(k, loss, "scipy", sc.cost, sc.status, sc.nfev, "lm", lm["cost"], lm["status"], lm["nit"], time.time() - t)
+            out[f"cost_{k}_{loss}"] = sc.cost
+            out[f"status_{k}_{loss}"] = sc.status
+            out[f"nfev_{k}_{loss}"] = sc.nfev
+            out[f"lm_cost_{k}_{loss}"] = lm["cost"]
+            out[f"real_reference_residual_{k}"] = int(k == 0)
+    np.savez_compressed(os.path.join(GOLD, "robust_scipy.npz"), f_scale=f_scale, **out)
+
+
 if __name__ == "__main__":
     what = sys.argv[1] if len(sys.argv) > 1 else "residual"
     if what == "residual":
@@ -448,5 +483,7 @@ if __name__ == "__main__":
         gen_fixed([int(a) for a in sys.argv[2:]] or [0, 1, 2])
     elif what == "synthB":
         gen_synthB()
+    elif what == "robust":
+        gen_robust()
     elif what == "configB":
         gen_configB()

@@ -72,6 +72,7 @@ SIGNATURES = {
     "b200ba_solve_io": (C.c_int, [_P, _P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_solve_dev": (C.c_int, [_P, _P, C.POINTER(Options), C.POINTER(Result)]),
     "b200ba_set_two_level": (C.c_int, [_P, C.c_int]),
+    "b200ba_set_loss": (C.c_int, [_P, C.c_int, C.c_double]),
     "b200ba_set_fixed_cameras": (C.c_int, [_P, _P, C.c_int64]),
     "b200ba_get_stats": (C.c_int, [_P, C.POINTER(Stats)]),
     "b200ba_reset_stats": (C.c_int, [_P]),

@@ -21,6 +21,8 @@ import numpy as np
 
 from . import _lib
 
+LOSSES = {"linear": 0, "soft_l1": 1, "huber": 2, "cauchy": 3, "arctan": 4}
+
 MESSAGES = {
     0: "The maximum number of function evaluations is exceeded.",
     1: "`gtol` termination condition is satisfied.",
@@ -88,6 +90,7 @@ class Engine:
         self._pinned = _PinnedPool(self.lib)
         self.n_cam = self.n_pts = self.n_obs = 0
         self.fixed = ()
+        self.loss = ("linear", 1.0)
         self.rank, self.nranks = 0, 1
 
     # -- lifetime
@@ -139,6 +142,7 @@ class Engine:
                                                 _ptr(Kc)))
         self.n_cam, self.n_pts, self.n_obs = int(n_cam), int(n_pts), len(ci)
         self.fixed = ()
+        self.loss = ("linear", 1.0)
         return self
 
     @property
@@ -318,6 +322,13 @@ class Engine:
         self._check(self.lib.b200ba_set_fixed_cameras(self.h, _ptr(idx) if len(idx) else C.c_void_p(0), len(idx)))
         self.fixed = tuple(int(i) for i in idx)
 
+    def set_loss(self, loss="linear", f_scale=1.0):
+        """Robust loss of the next solves (scipy's ``loss=`` / ``f_scale=``); reset to linear by ``set_problem``."""
+        if loss not in LOSSES:
+            raise ValueError(f"`loss` must be one of {sorted(LOSSES)}")
+        self._check(self.lib.b200ba_set_loss(self.h, LOSSES[loss], float(f_scale)))
+        self.loss = (loss, float(f_scale))
+
     def set_two_level(self, mode):
         """PCG preconditioner: 0 block-Jacobi, 1 automatic (default), 2 two-level from the first solve."""
         self._check(self.lib.b200ba_set_two_level(self.h, int(mode)))
@@ -348,19 +359,31 @@ _cache = {"key": None, "engine": None}
 
 
 def _problem_key(n_cam, n_pts, ci, pi, uv, K):
-    ci, pi, uv = np.asarray(ci), np.asarray(pi), np.asarray(uv)
-    return (int(n_cam), int(n_pts), len(ci), int(ci.sum()), int(pi.sum()), float(np.asarray(uv, dtype=np.float64).sum()),
-            int((ci[::7] * 31 + pi[::7]).sum()) if len(ci) else 0, np.asarray(K, dtype=np.float64).tobytes())
+    """Content digest of the problem (blake2b over the index, pixel and K bytes): two different problems never share a
+    key, so a cached device problem is only reused for the very same arrays."""
+    import hashlib
+    h = hashlib.blake2b(digest_size=16)
+    for a, dt in ((ci, np.int64), (pi, np.int64), (uv, None), (K, np.float64)):
+        a = np.ascontiguousarray(a) if dt is None else np.ascontiguousarray(a, dtype=dt)
+        h.update(str((a.dtype.str, a.shape)).encode())
+        h.update(memoryview(a).cast("B"))
+    return (int(n_cam), int(n_pts), h.digest())
 
 
 def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K):
     """The engine holding this problem on the device (uploaded once, reused by later calls)."""
     key = _problem_key(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
     if _cache["key"] != key or _cache["engine"] is None:
-        eng = _cache["engine"] or Engine()
+        eng = _cache["engine"] or _new_engine()
+        _cache["key"] = None                       # a failed upload leaves no stale key behind
+        _cache["engine"] = eng
         eng.set_problem(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
-        _cache["engine"], _cache["key"] = eng, key
+        _cache["key"] = key
     return _cache["engine"]
+
+
+def _new_engine():
+    return Engine()
 
 
 def compute_residuals(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
@@ -537,14 +560,18 @@ def _is_ba_residual(fun):
 
 
 def bundle_adjust(x0, n_cam, n_pts, camera_indices, point_indices, points_2d, K, ftol=1e-10, xtol=1e-8, gtol=1e-8,
-                  max_nfev=None, verbose=0, solver="auto", engine=None, fixed_camera_indices=(), **engine_opts):
+                  max_nfev=None, verbose=0, solver="auto", engine=None, fixed_camera_indices=(), loss="linear", f_scale=1.0,
+                  **engine_opts):
     """Global bundle adjustment of ``x0`` (layout of ``sfm.py:255-257``) on the GPU; returns :class:`BAResult`.
 
-    ``fixed_camera_indices``: cameras held fixed, the hook of ``bundle_adjustment.py:6,13``."""
+    ``fixed_camera_indices``: cameras held fixed, the hook of ``bundle_adjustment.py:6,13``; ``loss`` / ``f_scale``: scipy's
+    robust-loss keywords (``result.cost`` is then ``0.5 * f_scale**2 * sum(rho((fun / f_scale)**2))`` like scipy's)."""
     eng = engine or engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
     fixed = tuple(sorted(int(i) for i in fixed_camera_indices))
     if fixed != tuple(sorted(getattr(eng, "fixed", ()))):
         eng.set_fixed_cameras(fixed)
+    if (loss, float(f_scale)) != getattr(eng, "loss", ("linear", 1.0)):
+        eng.set_loss(loss, f_scale)
     x, r = eng.solve(x0, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev, verbose=verbose, solver=solver,
                      **engine_opts)
     res = BAResult(x=x, cost=r.cost, optimality=r.optimality, nfev=int(r.nfev), njev=int(r.njev), status=int(r.status),
@@ -566,14 +593,55 @@ def least_squares(fun, x0, jac="2-point", bounds=None, method="trf", ftol=1e-8, 
     if not _is_ba_residual(fun) or len(args) != 6:
         raise TypeError("b200ba.least_squares only solves the bundle-adjustment problem of sfm_lite: pass "
                         "compute_residuals and args=(n_cam, n_points, camera_indices, point_indices, points_2d, K)")
-    if loss != "linear":
-        raise NotImplementedError("only loss='linear' (the reference's setting) is implemented")
     n_cam, n_pts, ci, pi, uv, K = args
     solver = extra.pop("solver", "auto")
-    # a mask built with fixed_camera_indices (bundle_adjustment.py:6,13) carries the cameras whose columns are absent
-    fixed = tuple(int(i) for i in getattr(jac_sparsity, "fixed", ()))
+    # keywords that would change scipy's answer are honoured or refused, never ignored
+    if kwargs:
+        raise NotImplementedError("`kwargs` for the residual function are not supported (the BA residual takes none)")
+    if callable(jac) or jac not in ("2-point", "3-point", "cs"):
+        raise NotImplementedError("a user Jacobian is not supported: the engine always uses its analytic blocks")
+    if method not in ("trf", "lm", "dogbox"):
+        raise ValueError("`method` must be 'trf', 'dogbox' or 'lm'")
+    if bounds is not None:
+        lo, hi = bounds
+        if np.any(np.asarray(lo, dtype=np.float64) > -np.inf) or np.any(np.asarray(hi, dtype=np.float64) < np.inf):
+            raise NotImplementedError("bounds are not supported (the reference call at sfm.py:266 passes none)")
+    if not (isinstance(x_scale, str) and x_scale == "jac"):
+        raise NotImplementedError("only x_scale='jac' (the reference's setting; Marquardt scaling) is implemented")
+    if tr_solver not in (None, "lsmr", "exact"):
+        raise ValueError("`tr_solver` must be None, 'exact' or 'lsmr'")
+    if extra:
+        raise TypeError(f"unexpected keyword arguments {sorted(extra)}")
+    if loss not in LOSSES:
+        raise ValueError(f"`loss` must be one of {sorted(LOSSES)}")
     return bundle_adjust(x0, n_cam, n_pts, ci, pi, uv, K, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev,
-                         verbose=verbose, solver=solver, fixed_camera_indices=fixed)
+                         verbose=verbose, solver=solver, fixed_camera_indices=_fixed_from_mask(jac_sparsity, n_cam),
+                         loss=loss, f_scale=f_scale)
+
+
+def _fixed_from_mask(mask, n_cam):
+    """Cameras whose six columns are absent from ``jac_sparsity``: the lazy mask carries the set; for a real scipy mask
+    (``create_sparsity_matrix`` of the reference returns a ``lil_matrix``) the all-zero camera column groups are read."""
+    if mask is None:
+        return ()
+    if hasattr(mask, "fixed"):
+        return tuple(int(i) for i in mask.fixed)
+    try:
+        from scipy.sparse import issparse
+        m = mask.tocsc() if issparse(mask) else None
+    except Exception:
+        m = None
+    if m is None:
+        m = np.asarray(mask)
+        nnz_col = (m != 0).sum(axis=0)
+    else:
+        nnz_col = np.diff(m.indptr)
+    cam_cols = np.asarray(nnz_col).ravel()[:6 * int(n_cam)].reshape(int(n_cam), 6)
+    zero = (cam_cols == 0).all(axis=1)
+    partial = (cam_cols == 0).any(axis=1) & ~zero
+    if partial.any():
+        raise NotImplementedError("jac_sparsity masks single camera parameters; only whole cameras can be held fixed")
+    return tuple(int(i) for i in np.flatnonzero(zero))
 
 
 class _Cv2Proxy:

@@ -448,9 +448,11 @@ int fetch_scalars(Handle* h) {
   BA_CUDA(h, cudaStreamSynchronize(h->stream));
   int flow_err = 0;
   memcpy(&flow_err, w.h_scal + S_FLOW_ERR, sizeof(int));
-  if (flow_err) return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
   int p2p_err = 0;
   memcpy(&p2p_err, w.h_scal + S_P2P_ERR, sizeof(int));
+  // the error words are reported once and cleared, so one transient timeout does not fail every later call on the handle
+  if (flow_err || p2p_err) cudaMemsetAsync(w.scal + S_P2P_ERR, 0, 2 * sizeof(double), h->stream);
+  if (flow_err) return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
   if (p2p_err) return fail(h, B200BA_NCCL, "peer-memory exchange: the contribution of rank " + std::to_string(p2p_err - 1) +
                                            " did not arrive (results invalid)");
   return 0;
@@ -462,7 +464,10 @@ int check_flow_error(Handle* h) {
   int flow_err = 0;
   BA_CUDA(h, cudaMemcpyAsync(&flow_err, h->w.scal + S_FLOW_ERR, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
   BA_CUDA(h, cudaStreamSynchronize(h->stream));
-  if (flow_err) return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
+  if (flow_err) {
+    cudaMemsetAsync(h->w.scal + S_FLOW_ERR, 0, sizeof(double), h->stream);   // reported once
+    return fail(h, B200BA_CUDA, "k_lin_flow: a dependency wait timed out (results invalid)");
+  }
   return 0;
 }
 

@@ -26,6 +26,7 @@ constexpr int FLOW_META_CAP = 8192;   // staged tile metadata (slot descriptors 
 constexpr int FLOW_IDX_BYTES = (FLOW_TILE + 8) * 4;  // staged cam[] / pt[] window incl. alignment slack
 constexpr int NSCAL = 32;          // device scalar slots
 constexpr int DENSE_MAX_CAM = 512; // dense S export / Cholesky limit
+constexpr int MAX_DEVICES = 64;    // per-device caches of function attributes / occupancy
 
 // scalar slots (device array `scal`); "sum" slots are all-reduced with ncclSum
 enum Scal {
@@ -57,6 +58,7 @@ struct Problem {
   int64_t C = 0, P = 0, N = 0;
   int64_t Cs = 0;           // row stride of the field-major camera prep table (C rounded up to even: 16-byte rows)
   Intrinsics K;
+  Loss loss{0, 1.0, 1.0};   // robust loss of the solve (b200ba_set_loss); linear by default
   // observations, point-major (sorted by point, stable)
   double* u = nullptr;      // [N]
   double* v = nullptr;      // [N]

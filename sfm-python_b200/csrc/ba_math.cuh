@@ -115,11 +115,75 @@ BA_HD void project_jac(const double* __restrict__ cp, const Intrinsics& K, doubl
   }
 }
 
+
+// Robust loss of scipy.optimize.least_squares (the `loss=` / `f_scale=` keywords of the call at sfm.py:266; the reference
+// leaves the default 'linear').  scipy applies rho to every residual COMPONENT: z = (f / C)^2,
+//   cost = 0.5 C^2 sum rho(z),   J_scale = max(rho' + 2 rho'' z, EPS),   J <- sqrt(J_scale) J,   f <- rho' f / sqrt(J_scale)
+// (scipy _lsq/least_squares.py construct_loss_function, _lsq/common.py scale_for_robust_loss_function).
+struct Loss {
+  int kind;       // 0 linear, 1 soft_l1, 2 huber, 3 cauchy, 4 arctan
+  double c2;      // f_scale^2
+  double inv_c2;
+};
+
+// one residual component: returns C^2 rho(z), scales r in place, js = sqrt(J_scale) (row factor of the Jacobian)
+BA_HD double robust_component(const Loss& L, double& r, double& js) {
+  const double z = r * r * L.inv_c2;
+  double rho0, rho1, rho2;
+  if (L.kind == 1) {            // soft_l1
+    const double t = 1.0 + z, st = sqrt(t);
+    rho0 = 2.0 * (st - 1.0); rho1 = 1.0 / st; rho2 = -0.5 / (t * st);
+  } else if (L.kind == 2) {     // huber
+    if (z <= 1.0) { rho0 = z; rho1 = 1.0; rho2 = 0.0; }
+    else { const double sz = sqrt(z); rho0 = 2.0 * sz - 1.0; rho1 = 1.0 / sz; rho2 = -0.5 / (z * sz); }
+  } else if (L.kind == 3) {     // cauchy
+    const double t = 1.0 + z;
+    rho0 = log1p(z); rho1 = 1.0 / t; rho2 = -1.0 / (t * t);
+  } else {                      // arctan
+    const double t = 1.0 + z * z;
+    rho0 = atan(z); rho1 = 1.0 / t; rho2 = -2.0 * z / (t * t);
+  }
+  double w = rho1 + 2.0 * rho2 * z;
+  if (w < 2.220446049250313e-16) w = 2.220446049250313e-16;
+  js = sqrt(w);
+  r *= rho1 / js;
+  return L.c2 * rho0;
+}
+
+// cost term only (trial point): C^2 (rho(z0) + rho(z1)); linear: r0^2 + r1^2
+BA_HD double robust_cost2(const Loss& L, double r0, double r1) {
+  if (L.kind == 0) return r0 * r0 + r1 * r1;
+  double j;
+  return robust_component(L, r0, j) + robust_component(L, r1, j);
+}
+
+// scale the residual and the rows of both Jacobian blocks of one observation in place; returns the cost term
+BA_HD double apply_loss(const Loss& L, double& r0, double& r1, double* __restrict__ Jc, double* __restrict__ Jp) {
+  if (L.kind == 0) return r0 * r0 + r1 * r1;
+  double j0, j1;
+  const double c = robust_component(L, r0, j0) + robust_component(L, r1, j1);
+#pragma unroll
+  for (int k = 0; k < 6; ++k) { Jc[k] *= j0; Jc[6 + k] *= j1; }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { Jp[k] *= j0; Jp[3 + k] *= j1; }
+  return c;
+}
+
+// residual + Jacobian blocks of one observation with the loss applied; cost2 = the observation's term of 2 * cost
+BA_HD void project_jac_loss(const double* __restrict__ cp, const Intrinsics& K, const Loss& L, double X0, double X1, double X2,
+                            double uo, double vo, double& r0, double& r1, double* __restrict__ Jc, double* __restrict__ Jp,
+                            double& cost2) {
+  project_jac(cp, K, X0, X1, X2, uo, vo, r0, r1, Jc, Jp);
+  cost2 = apply_loss(L, r0, r1, Jc, Jp);
+}
+
 // sum-term of the back-substitution for one observation: s3 = J_X^T (Jc dc) without forming Jc.
 // Jc dc = J_w dw + J_T dT = -J_X ([Y]x J_r dw + dT) = -J_X q,  q = Y x m + dT  with m = J_r(w) dw per CAMERA
 // (cs = {m, dT}, k_cam_prep); per observation only J_X = B R is needed (2x3).
+// With a robust loss the rows carry the weights J_scale of the residual at x (uo, vo needed); linear: weights 1.
 BA_HD void project_step(const double* __restrict__ R, const double* __restrict__ T, const double* __restrict__ cs,
-                        const Intrinsics& K, double X0, double X1, double X2, double* __restrict__ s3) {
+                        const Intrinsics& K, const Loss& L, double X0, double X1, double X2, double uo, double vo,
+                        double* __restrict__ s3) {
   const double y0 = X0 - T[0], y1 = X1 - T[1], y2 = X2 - T[2];
   const double z0 = R[0] * y0 + R[1] * y1 + R[2] * y2;
   const double z1 = R[3] * y0 + R[4] * y1 + R[5] * y2;
@@ -142,7 +206,12 @@ BA_HD void project_step(const double* __restrict__ R, const double* __restrict__
     const double a0 = b0 * R[0] + b1 * R[3] + b2 * R[6];
     const double a1 = b0 * R[1] + b1 * R[4] + b2 * R[7];
     const double a2 = b0 * R[2] + b1 * R[5] + b2 * R[8];
-    const double t = -(a0 * q0 + a1 * q1 + a2 * q2);
+    double t = -(a0 * q0 + a1 * q1 + a2 * q2);
+    if (L.kind != 0) {
+      double rr = q - (row == 0 ? uo : vo), js;
+      robust_component(L, rr, js);
+      t *= js * js;
+    }
     s3[0] = fma(a0, t, s3[0]); s3[1] = fma(a1, t, s3[1]); s3[2] = fma(a2, t, s3[2]);
   }
 }

@@ -455,7 +455,10 @@ __global__ void __launch_bounds__(CHB_T) k_cholesky_blocked(int n, double* __res
 }  // namespace
 
 int pcg_grid(Handle* h) {
-  static int per_sm = 0;   // queried once: the occupancy call sits on the path of every camera solve otherwise
+  // queried once per device (function attributes and occupancy are per device/context: a process may hold handles on
+  // several GPUs); the occupancy call sits on the path of every camera solve otherwise
+  static int per_sm_dev[MAX_DEVICES] = {};
+  int& per_sm = per_sm_dev[h->device % MAX_DEVICES];
   if (per_sm == 0 &&
       (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg, PCG_T, 0) != cudaSuccess || per_sm < 1)) per_sm = 1;
   const int64_t C = h->pb.C;
@@ -509,7 +512,8 @@ int launch_tl_build(Handle* h, bool rebuild_coarse) {
   h->st.launches += 1;
   if (rebuild_coarse) {
     const size_t smem = (size_t)TL_K * pb.ncp * sizeof(double);
-    static bool attr = false;
+    static bool attr_dev[MAX_DEVICES] = {};
+    bool& attr = attr_dev[h->device % MAX_DEVICES];
     if (!attr) { cudaFuncSetAttribute(k_tl_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); attr = true; }
     const double one = 1.0;
     BA_CUDA(h, cudaMemcpyAsync(h->w.scal + S_TL_OK, &one, sizeof(double), cudaMemcpyHostToDevice, st));
@@ -541,7 +545,8 @@ int launch_pcg2(Handle* h, double rtol, int max_iter) {
   g.cam_agg = pb.cam_agg; g.agg_off = pb.agg_off; g.agg_cams = pb.agg_cams; g.sp_rowptr = pb.sp_rowptr; g.sp_col = pb.sp_col;
   g.G = w.tl_G; g.SP = w.tl_SP; g.Ainv = w.tl_A; g.rc = w.tl_rc; g.zc = w.tl_zc; g.uf = w.tl_uf; g.prof = w.tl_prof;
   void* args[] = {&g};
-  static int per_sm = 0;
+  static int per_sm_dev[MAX_DEVICES] = {};
+  int& per_sm = per_sm_dev[h->device % MAX_DEVICES];
   if (per_sm == 0 &&
       (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pcg2, PCG_T, 0) != cudaSuccess || per_sm < 1)) per_sm = 1;
   const int64_t need = std::max<int64_t>((pb.C + (PCG_T / 32) - 1) / (PCG_T / 32), 1);
@@ -557,7 +562,8 @@ int launch_cholesky(Handle* h) {
   if (!w.dense) return fail(h, B200BA_BAD_ARG, "dense Cholesky needs n_cam <= 512");
   launch_densify(h, w.dense);
   if (n <= CHB_MAX_N) {
-    static bool attr = false;
+    static bool attr_dev[MAX_DEVICES] = {};
+    bool& attr = attr_dev[h->device % MAX_DEVICES];
     if (!attr) { cudaFuncSetAttribute(k_cholesky_blocked, cudaFuncAttributeMaxDynamicSharedMemorySize, CHB_SMEM); attr = true; }
     k_cholesky_blocked<<<1, CHB_T, CHB_SMEM, h->stream>>>(n, w.dense, w.b, w.dc, w.scal);
   } else {

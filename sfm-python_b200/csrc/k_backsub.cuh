@@ -56,7 +56,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       const double uo = pb.u[i], vo = pb.v[i];
       double r0, r1, s3[3], cp[CAMPREP_FIELDS];
       load_step_cam(camprep, cstep, pb.Cs, c, cp);
-      project_step(cp, cp + 18, cp + 9, pb.K, X0, X1, X2, s3);
+      project_step(cp, cp + 18, cp + 9, pb.K, pb.loss, X0, X1, X2, uo, vo, s3);
       if (!valid) s3[0] = s3[1] = s3[2] = 0.0;
       const SegInfo s = seg_info(p, valid, lane);
       seg_allsum<3>(s3, s, lane);
@@ -66,7 +66,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
       load_rt(camprep_n, pb.Cs, c, cp);
       project_residual(cp, pb.K, N0, N1, N2, uo, vo, r0, r1);
       if (valid) {
-        acc[0] += r0 * r0 + r1 * r1;
+        acc[0] += robust_cost2(pb.loss, r0, r1);
         if (lane == s.first) {
           xnp[3 * (int64_t)p] = N0; xnp[3 * (int64_t)p + 1] = N1; xnp[3 * (int64_t)p + 2] = N2;
           acc[1] += sums[0]; acc[2] += sums[1]; acc[3] += sums[2];
@@ -81,7 +81,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
         const int c = pb.cam[i];
         double t3[3], cp[CAMPREP_FIELDS];
         load_step_cam(camprep, cstep, pb.Cs, c, cp);
-        project_step(cp, cp + 18, cp + 9, pb.K, X0, X1, X2, t3);
+        project_step(cp, cp + 18, cp + 9, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], t3);
         s3[0] += t3[0]; s3[1] += t3[1]; s3[2] += t3[2];
       }
       s3[0] = warp_sum(s3[0]); s3[1] = warp_sum(s3[1]); s3[2] = warp_sum(s3[2]);
@@ -92,7 +92,7 @@ k_backsub_trial(Problem pb, const double* __restrict__ x, double* __restrict__ x
         double r0, r1, cp[CAMPREP_FIELDS];
         load_rt(camprep_n, pb.Cs, pb.cam[i], cp);
         project_residual(cp, pb.K, N0, N1, N2, pb.u[i], pb.v[i], r0, r1);
-        acc[0] += r0 * r0 + r1 * r1;
+        acc[0] += robust_cost2(pb.loss, r0, r1);
       }
       if (lane == 0) {
         xnp[3 * (int64_t)p] = N0; xnp[3 * (int64_t)p + 1] = N1; xnp[3 * (int64_t)p + 2] = N2;

@@ -139,6 +139,7 @@ __device__ __forceinline__ void flow_issue_meta(const FlowCtx& c, int t, int k) 
 __device__ __forceinline__ bool flow_wait_bar(unsigned long long* bar, int gen, int* err) {
   int spins = 0;
   while (!mbar_try_wait(bar, (unsigned)(gen & 1))) {
+    if (spins > 64) __nanosleep(64);
     if (++spins > FLOW_SPIN_LIMIT) { *err = 1; return false; }
   }
   return true;
@@ -244,7 +245,8 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       const double X0 = xp[3 * p], X1 = xp[3 * p + 1], X2 = xp[3 * p + 2];
       double r0, r1, Jc[12], Jp[6], vals[9], cp[CAMPREP_FIELDS];
       get_cam(c, cp);
-      project_jac(cp, pb.K, X0, X1, X2, uo, vo, r0, r1, Jc, Jp);
+      double c2;
+      project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, uo, vo, r0, r1, Jc, Jp, c2);
       point_products(Jp, r0, r1, vals);
       if (!valid) {
 #pragma unroll
@@ -261,7 +263,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       z[2] = Li[3] * vals[6] + Li[4] * vals[7] + Li[5] * vals[8];
       if (FLOW_PROF) { const long long cc = clock64(); tA3 += cc - cA; cA = cc; }
       if (valid) {
-        cost2 += r0 * r0 + r1 * r1;
+        cost2 += c2;
         store_record(rec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
         if (lane == sg.first) gmax = fmax(gmax, fmax(fabs(vals[6]), fmax(fabs(vals[7]), fabs(vals[8]))));
       }
@@ -269,7 +271,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       // below must not wait for them)
       flow_signal_A(cost2, gmax);
       if (valid && lane == sg.first) store_point(pp, gp, p, Li, z, vals);
-      if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; tA += c2 - c1; }
+      if (FLOW_PROF) { const long long ce = clock64(); tW += c1 - c0; tA += ce - c1; }
       return true;
     } else {
       const int p = s_pt[a - a0];
@@ -280,11 +282,12 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       for (int i = a + lane; i < b; i += 32) {
         double r0, r1, Jc[12], Jp[6], v9[9], cp[CAMPREP_FIELDS];
         get_cam(s_cam[i - a0], cp);
-        project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+        double c2;
+        project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
         point_products(Jp, r0, r1, v9);
 #pragma unroll
         for (int q2 = 0; q2 < 9; ++q2) vals[q2] += v9[q2];
-        cost2 += r0 * r0 + r1 * r1;
+        cost2 += c2;
       }
 #pragma unroll
       for (int q2 = 0; q2 < 9; ++q2) vals[q2] = warp_sum(vals[q2]);
@@ -300,12 +303,13 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       for (int i = a + lane; i < b; i += 32) {
         double r0, r1, Jc[12], Jp[6], cp[CAMPREP_FIELDS];
         get_cam(s_cam[i - a0], cp);
-        project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+        double c2;
+        project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
         store_record(rec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
       }
     }
     flow_signal_A(cost2, gmax);
-    if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; tA += c2 - c1; }
+    if (FLOW_PROF) { const long long ce = clock64(); tW += c1 - c0; tA += ce - c1; }
     return true;
   };
 
@@ -354,7 +358,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       // last consumer of tile k: its metadata slot is free -> stage the blob of tile k + 2
       if (old + 1 == tgtBC && k + 2 < K) flow_issue_meta(cx, tile_of(k + 2), k + 2);
     }
-    if (FLOW_PROF) { const long long c2 = clock64(); tW += c1 - c0; if (r < nC) tC += c2 - c1; else tB += c2 - c1; }
+    if (FLOW_PROF) { const long long ce = clock64(); tW += c1 - c0; if (r < nC) tC += ce - c1; else tB += ce - c1; }
     return true;
   };
 

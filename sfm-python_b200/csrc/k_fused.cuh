@@ -179,7 +179,8 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
         const int c = pb.cam[i], p = pb.pt[i];
         double r0, r1, Jc[12], Jp[6], vals[9], cp[CAMPREP_FIELDS];
         load_cam(camprep, pb.Cs, c, cp);
-        project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+        double c2;
+        project_jac_loss(cp, pb.K, pb.loss, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
         point_products(Jp, r0, r1, vals);
         if (!valid) {
 #pragma unroll
@@ -193,7 +194,7 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
         z[1] = Li[1] * vals[6] + Li[2] * vals[7];
         z[2] = Li[3] * vals[6] + Li[4] * vals[7] + Li[5] * vals[8];
         if (valid) {
-          cost2 += r0 * r0 + r1 * r1;
+          cost2 += c2;
           store_record(srec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
           if (lane == s.first) {
             store_point(pp, gp, p, Li, z, vals);
@@ -210,11 +211,12 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
         for (int i = a + lane; i < b; i += 32) {
           double r0, r1, Jc[12], Jp[6], v9[9], cp[CAMPREP_FIELDS];
           load_cam(camprep, pb.Cs, pb.cam[i], cp);
-          project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+          double c2;
+        project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
           point_products(Jp, r0, r1, v9);
 #pragma unroll
           for (int k = 0; k < 9; ++k) vals[k] += v9[k];
-          cost2 += r0 * r0 + r1 * r1;
+          cost2 += c2;
         }
 #pragma unroll
         for (int k = 0; k < 9; ++k) vals[k] = warp_sum(vals[k]);
@@ -230,7 +232,8 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
         for (int i = a + lane; i < b; i += 32) {
           double r0, r1, Jc[12], Jp[6], cp[CAMPREP_FIELDS];
           load_cam(camprep, pb.Cs, pb.cam[i], cp);
-          project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+          double c2;
+        project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
           store_record(srec + FREC * (i - a0), Jc, Jp, Li, z, r0, r1);
         }
       }

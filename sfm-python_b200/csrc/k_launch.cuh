@@ -158,7 +158,8 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
   cudaStream_t st = h->stream;
   KernelTimer t(h);
   if (pb.fused) {
-    static bool attr_set = false;
+    static bool attr_dev[MAX_DEVICES] = {};   // function attributes are per device: one flag per ordinal
+    bool& attr_set = attr_dev[h->device % MAX_DEVICES];
     if (!attr_set) {
       cudaFuncSetAttribute(k_lin_fused<256, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_TILE_2CTA * FUSED_REC_BYTES);
       cudaFuncSetAttribute(k_lin_fused<512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FUSED_TILE_1CTA * FUSED_REC_BYTES);
@@ -168,7 +169,8 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
     const int fg = fused_grid(h);
     t.begin();
     if (pb.flow) {
-      static bool flow_attr = false;
+      static bool flow_dev[MAX_DEVICES] = {};
+      bool& flow_attr = flow_dev[h->device % MAX_DEVICES];
       if (!flow_attr) {
         cudaFuncSetAttribute(k_lin_flow, cudaFuncAttributeMaxDynamicSharedMemorySize, FlowSmem::TOTAL);
         flow_attr = true;
@@ -222,7 +224,10 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
   k_cam_side<<<cg, 256, 0, st>>>(pb, x, w.camprep, w.rr, w.cpart);
   k_cam_reduce<<<cdiv(pb.C * 33, 256), 256, 0, st>>>((int)pb.C, pb.cam_choff, w.cpart, w.U, w.gc, w.b, w.udiag);
   t.end(&h->st.ms_camera_blocks);
-  static int schur_mode = -1;
+  static int schur_dev[MAX_DEVICES];
+  static bool schur_init = false;
+  if (!schur_init) { for (int i = 0; i < MAX_DEVICES; ++i) schur_dev[i] = -1; schur_init = true; }
+  int& schur_mode = schur_dev[h->device % MAX_DEVICES];
   if (schur_mode < 0) {
     cudaFuncSetAttribute(k_schur<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);
     cudaFuncSetAttribute(k_schur<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SCH_SMEM);

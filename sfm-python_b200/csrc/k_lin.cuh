@@ -109,7 +109,8 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
       const int c = pb.cam[i], p = pb.pt[i];
       double r0, r1, Jc[12], Jp[6], vals[9], cp[CAMPREP_FIELDS];
       load_cam(camprep, pb.Cs, c, cp);
-      project_jac(cp, pb.K, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+      double c2;
+        project_jac_loss(cp, pb.K, pb.loss, xp[3 * p], xp[3 * p + 1], xp[3 * p + 2], pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
       point_products(Jp, r0, r1, vals);
       if (!valid) {
 #pragma unroll
@@ -124,7 +125,7 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
       z[2] = Li[3] * vals[6] + Li[4] * vals[7] + Li[5] * vals[8];
       obs_outputs(Jc, Jp, Li, z, r0, r1, Yv, rt0, rt1);
       if (valid) {
-        cost2 += r0 * r0 + r1 * r1;
+        cost2 += c2;
         double2* o = reinterpret_cast<double2*>(rr + 4 * (int64_t)i);
         o[0] = make_double2(r0, r1);
         o[1] = make_double2(rt0, rt1);
@@ -144,11 +145,12 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
       for (int i = a + lane; i < b; i += 32) {
         double r0, r1, Jc[12], Jp[6], v9[9], cp[CAMPREP_FIELDS];
         load_cam(camprep, pb.Cs, pb.cam[i], cp);
-        project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+        double c2;
+        project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
         point_products(Jp, r0, r1, v9);
 #pragma unroll
         for (int k = 0; k < 9; ++k) vals[k] += v9[k];
-        cost2 += r0 * r0 + r1 * r1;
+        cost2 += c2;
       }
 #pragma unroll
       for (int k = 0; k < 9; ++k) vals[k] = warp_sum(vals[k]);
@@ -167,7 +169,8 @@ k_lin_points(Problem pb, const double* __restrict__ x, const double* __restrict_
         const int i = base + (valid ? lane : 0);
         double r0, r1, Jc[12], Jp[6], Yv[18], rt0, rt1, cp[CAMPREP_FIELDS];
         load_cam(camprep, pb.Cs, pb.cam[i], cp);
-        project_jac(cp, pb.K, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp);
+        double c2;
+        project_jac_loss(cp, pb.K, pb.loss, X0, X1, X2, pb.u[i], pb.v[i], r0, r1, Jc, Jp, c2);
         obs_outputs(Jc, Jp, Li, z, r0, r1, Yv, rt0, rt1);
         if (valid) {
           double2* o = reinterpret_cast<double2*>(rr + 4 * (int64_t)i);

@@ -97,3 +97,61 @@ def test_install_rebinds_names_and_cv2_proxy_delegates():
     proxy = mod.cv2
     b200ba.install(mod, geometry=True)
     assert mod.cv2 is proxy            # idempotent
+
+
+def _ba_args(n=40):
+    rng = np.random.default_rng(0)
+    ci = rng.integers(0, 4, n)
+    pi = np.sort(rng.integers(0, 10, n))
+    return (4, 10, ci, pi, rng.uniform(0, 100, (n, 2)), np.eye(3))
+
+
+def test_least_squares_refuses_what_it_would_otherwise_ignore():
+    """Keywords that change scipy's answer are honoured or refused before any device work."""
+    import b200ba
+    args = _ba_args()
+    x0 = np.zeros(6 * 4 + 3 * 10)
+    f = b200ba.compute_residuals
+    with pytest.raises(NotImplementedError):
+        b200ba.least_squares(f, x0, args=args, bounds=(np.zeros_like(x0), np.ones_like(x0)))
+    with pytest.raises(NotImplementedError):
+        b200ba.least_squares(f, x0, args=args, jac=lambda x, *a: None)
+    with pytest.raises(NotImplementedError):
+        b200ba.least_squares(f, x0, args=args, x_scale=2.0)
+    with pytest.raises(NotImplementedError):
+        b200ba.least_squares(f, x0, args=args, kwargs={"a": 1})
+    with pytest.raises(ValueError):
+        b200ba.least_squares(f, x0, args=args, loss="tukey")
+    with pytest.raises(ValueError):
+        b200ba.least_squares(f, x0, args=args, method="newton")
+    with pytest.raises(TypeError):
+        b200ba.least_squares(f, x0, args=args, frobnicate=1)
+
+
+def test_fixed_cameras_are_read_from_a_real_scipy_mask():
+    """A mask built by the reference's create_sparsity_matrix(..., fixed_camera_indices) is a lil_matrix without the
+    cameras' columns: the drop-in derives the fixed set from the all-zero column groups."""
+    import ba_oracle as O
+    import b200ba
+    n_cam, n_pts, ci, pi, uv, K = _ba_args()
+    B = b200ba.bundle_adjustment
+    assert B._fixed_from_mask(O.sparsity(n_cam, n_pts, len(ci), ci, pi, (2,)).tolil(), n_cam) == (2,)
+    assert B._fixed_from_mask(O.sparsity(n_cam, n_pts, len(ci), ci, pi).tolil(), n_cam) == ()
+    assert B._fixed_from_mask(b200ba.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi, (1, 3)), n_cam) == (1, 3)
+    assert B._fixed_from_mask(None, n_cam) == ()
+    half = O.sparsity(n_cam, n_pts, len(ci), ci, pi).tolil()
+    half[:, 6] = 0
+    with pytest.raises(NotImplementedError):
+        B._fixed_from_mask(half, n_cam)
+
+
+def test_problem_key_is_a_content_digest():
+    """Two problems that differ only by swapped pixel rows (same sums) must not share a cached device problem."""
+    import b200ba
+    n_cam, n_pts, ci, pi, uv, K = _ba_args()
+    key = b200ba.bundle_adjustment._problem_key
+    uv2 = uv.copy()
+    uv2[[0, 1]] = uv2[[1, 0]]
+    assert key(n_cam, n_pts, ci, pi, uv, K) == key(n_cam, n_pts, ci.copy(), pi.copy(), uv.copy(), K)
+    assert key(n_cam, n_pts, ci, pi, uv, K) != key(n_cam, n_pts, ci, pi, uv2, K)
+    assert key(n_cam, n_pts, ci, pi, uv, K) != key(n_cam, n_pts, ci, pi, uv.astype(np.int64), K)

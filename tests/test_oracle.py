@@ -201,3 +201,27 @@ def test_configB_golden_is_consistent():
     assert abs(0.5 * float(r @ r) - float(g["scipy_cost"])) <= 1e-12 * float(g["scipy_cost"])
     assert float(g["lm_cost"]) <= float(g["scipy_cost"])
     assert float(g["lm_cost"]) - float(g["arbiter_from_lm_cost"]) <= 1e-6 * float(g["lm_cost"])
+
+
+@pytest.mark.parametrize("loss", ["soft_l1", "huber", "cauchy", "arctan"])
+def test_robust_scaling_matches_scipy(loss):
+    """The oracle's rho / scaling restatement against scipy's own construct_loss_function and
+    scale_for_robust_loss_function (the code path behind loss= at sfm.py:266)."""
+    from scipy.optimize._lsq.common import scale_for_robust_loss_function
+    from scipy.optimize._lsq.least_squares import construct_loss_function
+    rng = np.random.default_rng(3)
+    f = np.concatenate([rng.standard_normal(200) * 4.0, [0.0, 1e-9, 2.5, -2.5, 1e4]])
+    J = rng.standard_normal((len(f), 5))
+    for C in (0.7, 2.5):
+        lf = construct_loss_function(len(f), loss, C)
+        Js, fs = scale_for_robust_loss_function(J.copy(), f.copy(), lf(f))
+        js, r = O.robust_scale(f, loss, C)
+        # where rho' + 2 rho'' z cancels to rounding noise (huber's linear part, far outliers) scipy's row factor is
+        # sqrt(noise or eps) ~ 1e-8: only the products J_s^T J_s (~ 0) and J_s^T f_s = J^T rho' f are meaningful there
+        ok = js > 1e-6
+        assert np.abs(Js - J * js[:, None])[ok].max() <= 1e-13 * np.abs(Js).max()
+        assert np.abs(fs - r)[ok].max() <= 1e-12 * np.abs(fs[ok]).max()
+        assert np.abs(Js - J * js[:, None]).max() <= 1e-7 * np.abs(J).max()
+        g_s, g_o = Js * fs[:, None], (J * js[:, None]) * r[:, None]
+        assert np.abs(g_s - g_o).max() <= 1e-12 * np.abs(g_s).max()
+        assert abs(lf(f, cost_only=True) - O.robust_cost(f, loss, C)) <= 1e-13 * O.robust_cost(f, loss, C)
