@@ -120,6 +120,23 @@ int b200ba_residuals(b200ba_handle* h, const double* x, double* r_out, double* c
 /* same with DEVICE pointers (torch tensor .data_ptr()); r_out_dev may be NULL */
 int b200ba_residuals_dev(b200ba_handle* h, const double* x_dev, double* r_out_dev, double* cost_out);
 
+/* Allocation-free variant of b200ba_residuals.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arithmetic as b200ba_residuals (k_cam_prep + the residual kernel), but it needs no b200ba_set_problem and makes no
+ * cudaMalloc / cudaFree / pool allocation: its scratch (per-camera R, J_r, T table + per-CTA cost partials) is a
+ * file-scope static __device__ array of 0.77 MB that every GPU loading the library holds until exit.
+ * LIMIT: n_cam <= 4096 (B200BA_NOALLOC_MAX_CAM); larger problems are refused with B200BA_BAD_ARG and a message.
+ * All array arguments are DEVICE pointers except K (9 host doubles): cam_idx_dev / pt_idx_dev int32 (n_obs), uv_dev
+ * n_obs x 2, x_dev the parameter vector (6 n_cam + 3 n_pts), r_out_dev 2 n_obs in the CALLER's observation order (may be
+ * NULL), cost_out_dev one double = 0.5 sum r^2 (may be NULL).  Out-of-range indices yield NaN residuals, not an error.
+ * The scratch is shared by all calls on a device and keeps the last call's contents (nothing needs pre-clearing: every
+ * slot read is rewritten by the same call); calls that overlap on one GPU (other streams / handles / threads) RACE.
+ * Runs on the handle's stream and synchronises it before returning. */
+#define B200BA_NOALLOC_MAX_CAM 4096
+int b200ba_residuals_noalloc(b200ba_handle* h, int64_t n_cam, int64_t n_pts, int64_t n_obs, const int32_t* cam_idx_dev,
+                             const int32_t* pt_idx_dev, const double* uv_dev, const double* K, const double* x_dev,
+                             double* r_out_dev, double* cost_out_dev);
+
 /* Pose <-> parameter conversion at the boundary.  pack = sfm.py:252-257: for each of n row-major
  * 4x4 poses H, params = [Rot.from_matrix(H[:3,:3]).as_rotvec() (3) | H[:3,3] (3)]; unpack = sfm.py:273-278:
  * H = [[Rot.from_rotvec(w).as_matrix(), T], [0 0 0 1]].  Restates scipy.spatial.transform's arithmetic (orthogonality

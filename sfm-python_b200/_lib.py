@@ -55,6 +55,7 @@ SIGNATURES = {
     "b200ba_set_problem": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64, _P, _P, _P, _P]),
     "b200ba_residuals": (C.c_int, [_P, _P, _P, _D]),
     "b200ba_residuals_dev": (C.c_int, [_P, _P, _P, _D]),
+    "b200ba_residuals_noalloc": (C.c_int, [_P, C.c_int64, C.c_int64, C.c_int64, _P, _P, _P, _P, _P, _P, _P]),
     "b200ba_pack_cameras": (C.c_int, [_P, C.c_int64, _P, _P]),
     "b200ba_unpack_cameras": (C.c_int, [_P, C.c_int64, _P, _P]),
     "b200ba_solve_pnp": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P, _P, C.c_int32, _P]),

@@ -291,6 +291,17 @@ class Engine:
                                                   C.c_void_p(int(r_dev_ptr) if r_dev_ptr else 0), C.byref(cost)))
         return cost.value
 
+    def residuals_noalloc(self, n_cam, n_pts, n_obs, cam_dev_ptr, pt_dev_ptr, uv_dev_ptr, K, x_dev_ptr, r_dev_ptr=0,
+                          cost_dev_ptr=0):
+        """``b200ba_residuals_noalloc``: residual + cost from DEVICE arrays (int32 indices) with the scratch in a static
+        device array -- no allocation on the call path, no ``set_problem``; at most 4096 cameras (no reference
+        counterpart; for callers that cannot call cudaMalloc)."""
+        Kc = np.ascontiguousarray(K, dtype=np.float64)
+        self._check(self.lib.b200ba_residuals_noalloc(
+            self.h, int(n_cam), int(n_pts), int(n_obs), C.c_void_p(int(cam_dev_ptr) or None), C.c_void_p(int(pt_dev_ptr) or None),
+            C.c_void_p(int(uv_dev_ptr) or None), _ptr(Kc), C.c_void_p(int(x_dev_ptr) or None),
+            C.c_void_p(int(r_dev_ptr) or None), C.c_void_p(int(cost_dev_ptr) or None)))
+
     def jacobian_blocks_dev(self, x_dev_ptr, r_dev_ptr, jc_dev_ptr, jp_dev_ptr):
         self._check(self.lib.b200ba_jacobian_blocks_dev(self.h, C.c_void_p(int(x_dev_ptr)),
                                                         C.c_void_p(int(r_dev_ptr) if r_dev_ptr else 0),

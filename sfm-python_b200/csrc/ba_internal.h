@@ -287,6 +287,10 @@ void launch_backsub_trial(Handle* h, double lambda);
 void launch_cam_dots(Handle* h);
 void launch_densify(Handle* h, double* dense /*6C x 6C*/);
 double measure_fp64_peak(Handle* h);
+// k_noalloc.cuh: residual + cost with all scratch in a static device array (no allocation on the call path)
+int noalloc_setup(Handle* h);   // once per device, device current: cudaGetSymbolAddress of the scratch array
+int residuals_noalloc(Handle* h, int64_t C, int64_t P, int64_t N, const int* cam_dev, const int* pt_dev, const double* uv_dev,
+                      const double* K, const double* x_dev, double* r_out_dev, double* cost_out_dev);
 
 // ---- ba_solve.cu
 int launch_pcg(Handle* h, double rtol, int max_iter);

@@ -379,5 +379,6 @@ __global__ void __launch_bounds__(JT) k_jacobian(Problem pb, const double* __res
 }  // namespace
 
 #include "k_launch.cuh"
+#include "k_noalloc.cuh"
 
 }  // namespace b200ba
