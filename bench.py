@@ -329,6 +329,43 @@ def run_b200(a, rank, world, local_rank):
     lm["converge"] = {"ms": float(cv.item()), "lm_iters": int(rc.n_iter), "pcg_iters": int(rc.pcg_iters),
                       "status": int(rc.status), "cost": rc.cost, "rms_px": rc.rms}
 
+    # ---- parity inside the bench (outside every timed region): the cost the LM loop reported at x0 against the ORACLE's
+    #      residual on the same arrays (each rank its shard, summed), so a wrong kernel cannot produce a bench line
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ba_oracle as O
+    r_or = O.residuals(pb.x0, n_cam, hi - lo, ci, pil, uv, pb.K)
+    c_or = torch.tensor([0.5 * float(r_or @ r_or)], device=f"cuda:{local_rank}", dtype=torch.float64)
+    del r_or
+    if td:
+        td.all_reduce(c_or)
+    cost_oracle = float(c_or.item())
+    cost_err = abs(res.initial_cost - cost_oracle) / cost_oracle
+    if cost_err > 1e-9:
+        raise RuntimeError(f"parity: cost at x0 {res.initial_cost!r} differs from the oracle's {cost_oracle!r} ({cost_err:.2e})")
+    lm["cost_initial_oracle"] = cost_oracle
+    lm["cost_initial_rel_err"] = cost_err
+
+    # ---- multi-GPU parity (N > 1): the sharded reduced camera system / b / cost of a 300-camera problem against an
+    #      unsharded engine on rank 0 and against the oracle's cost, max relative error -> "shard_parity"
+    shard_parity = None
+    if world > 1:
+        sp = b200ba.synthetic.make_problem(300, 30000, 120000, seed=3)
+        dba.set_problem(*sp.args())
+        slo, shi = dba.range
+        ne = dba.engine.normal_equations(bd.split_x(sp.x0, 300, slo, shi), 1e-3)
+        if rank == 0:
+            one = b200ba.Engine(local_rank)
+            one.set_problem(*sp.args())
+            ref = one.normal_equations(sp.x0, 1e-3)
+            one.close()
+            r_sp = O.residuals(sp.x0, *sp.args())
+            shard_parity = max(np.abs(ne["S"] - ref["S"]).max() / np.abs(ref["S"]).max(),
+                               np.abs(ne["b"] - ref["b"]).max() / np.abs(ref["b"]).max(),
+                               abs(ne["cost"] - ref["cost"]) / ref["cost"],
+                               abs(ne["cost"] - 0.5 * float(r_sp @ r_sp)) / ne["cost"])
+        barrier()
+        eng.set_problem(n_cam, hi - lo, ci_h, pi_h, uv_h, pb.K)
+
     # ---- e2e: the public host API with host buffers; every step uploads the problem and x0, solves, downloads x
     e2e_iters = 5
     def e2e_step():
@@ -481,6 +518,8 @@ def run_b200(a, rank, world, local_rank):
            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "roofline_fp64": roof64, "kernel_ms": kern_ms,
            "tiles": {"n_tiles": int(st["n_tiles"]), "pair_slots": int(st["n_pair_slots"]),
                      "self_slots": int(st["n_self_slots"])}}
+    if shard_parity is not None:
+        out["shard_parity"] = shard_parity
     if hbm_kernels:
         out["roofline_hbm_kernels"] = hbm_kernels
     if config_a:

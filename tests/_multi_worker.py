@@ -14,6 +14,8 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 import torch.distributed as td  # noqa: E402
 
+sys.path.insert(0, os.path.join(ROOT, "oracle"))
+import ba_oracle as O  # noqa: E402
 import b200ba  # noqa: E402
 from b200ba import dist as bd  # noqa: E402
 
@@ -48,9 +50,22 @@ def main():
     t0 = t.clone()
     td.broadcast(t0, src=0)
     same = bool(torch.equal(t, t0))
+    # and against the ORACLE (not only sharded-CUDA vs unsharded-CUDA): cost, camera gradient and b from the vectorised
+    # numpy blocks; the dense reduced system itself on the small shape (the oracle's Schur loop is per point)
+    nb = O.normal_blocks(pb.x0, *pb.args())
+    err_oc = abs(ne["cost"] - nb["cost"]) / nb["cost"]
+    err_og = np.abs(ne["grad"][:6 * n_cam] - nb["gc"].ravel()).max() / np.abs(nb["gc"]).max()
+    err_oS = 0.0
+    if n_cam <= 64:
+        so = O.schur_system(pb.x0, *pb.args(), lam)
+        err_oS = max(np.abs(ne["S"] - so["S"]).max() / np.abs(so["S"]).max(), np.abs(ne["b"] - so["b"]).max() / np.abs(so["b"]).max())
+    chk = 0.5 * float(np.sum(O.residuals(res.x, *pb.args()) ** 2))
+    err_ox = abs(chk - res.cost) / res.cost
     ok = err_S < 1e-11 and err_b < 1e-11 and err_c < 1e-13 and err_lm < 1e-8 and same
+    ok = ok and err_oc < 1e-12 and err_og < 1e-9 and err_oS < 1e-9 and err_ox < 1e-9
     print(f"rank {rank}/{world} xchg={os.environ.get('B200BA_XCHG', 'auto')} S {err_S:.2e} b {err_b:.2e} cost {err_c:.2e} "
-          f"lm {err_lm:.2e} ({res.cost:.6f} vs {r1.cost:.6f}) identical={same} {'OK' if ok else 'FAIL'}", flush=True)
+          f"lm {err_lm:.2e} ({res.cost:.6f} vs {r1.cost:.6f}) identical={same} | vs oracle: cost {err_oc:.2e} g_c {err_og:.2e} "
+          f"S,b {err_oS:.2e} cost(x*) {err_ox:.2e} {'OK' if ok else 'FAIL'}", flush=True)
     td.barrier()
     td.destroy_process_group()
     sys.exit(0 if ok else 1)
