@@ -93,6 +93,7 @@ typedef struct b200ba_stats {
   double ms_jacobian;     /* k_jacobian alone (config E sweep) */
   int64_t n_tl_builds;    /* rebuilds of the coarse operator of the two-level PCG preconditioner */
   double ms_reproj;       /* k_reproj_err alone */
+  double ms_residual_kernel;  /* k_residual alone (ms_residual also covers k_cam_prep and the partial reduction) */
 } b200ba_stats;
 
 int b200ba_version(void);

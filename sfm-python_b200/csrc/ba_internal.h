@@ -229,7 +229,8 @@ struct Handle {
   // stats
   b200ba_stats st{};
   bool profile = false;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;   // PhaseTimer
+  cudaEvent_t ev2 = nullptr, ev3 = nullptr;   // KernelTimer (may run inside a PhaseTimer bracket)
   // two-level preconditioner state of the running solve (identical on every rank: driven by PCG iteration counts)
   int tl_mode = 1;            // 0 block-Jacobi only, 1 automatic, 2 two-level from the first solve, rebuilt every solve
   bool tl_built = false;      // G / A_c^-1 hold a coarse operator of this solve

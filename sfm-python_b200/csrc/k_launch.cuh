@@ -77,13 +77,13 @@ int partial_capacity(const Handle* h) {
 struct KernelTimer {
   Handle* h; bool on;
   explicit KernelTimer(Handle* h_) : h(h_), on(h_->profile) {}
-  void begin() { if (on) cudaEventRecord(h->ev0, h->stream); }
+  void begin() { if (on) cudaEventRecord(h->ev2, h->stream); }
   void end(double* acc) {
     if (!on) return;
-    cudaEventRecord(h->ev1, h->stream);
-    cudaEventSynchronize(h->ev1);
+    cudaEventRecord(h->ev3, h->stream);
+    cudaEventSynchronize(h->ev3);
     float ms = 0.f;
-    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    cudaEventElapsedTime(&ms, h->ev2, h->ev3);
     *acc += ms;
   }
 };
@@ -98,7 +98,10 @@ void launch_cam_prep(Handle* h, const double* x_cams, const double* dc, double* 
 
 void launch_residual(Handle* h, const double* x, const double* camprep, double* r_out, int scal_slot) {
   const int g = obs_grid(h);
+  KernelTimer t(h);
+  t.begin();
   k_residual<<<g, 256, 0, h->stream>>>(h->pb, x, camprep, r_out, h->w.part);
+  t.end(&h->st.ms_residual_kernel);
   Slots sl{};
   sl.s[0] = scal_slot;
   k_reduce_partials2<<<1, 256, 0, h->stream>>>(g, 1, 1, h->w.part, h->w.scal, h->w.scal, sl);

@@ -80,12 +80,12 @@ __global__ void __launch_bounds__(512) k_mixed(int iters, int mix, double* sink)
 template <int NCH, int REC>
 __global__ void __launch_bounds__(512) k_dmma_gather(int entries, int n_rec, double* sink) {
   extern __shared__ double rec[];
-  for (int i = threadIdx.x; i < n_rec * REC; i += blockDim.x) rec[i] = 1e-3 * (i % 97);
+  for (int i = threadIdx.x; i < n_rec * REC; i += blockDim.x) rec[i] = (i % REC) < 18 ? 1e-3 * (i % 97) : 0.0;
   __syncthreads();
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int row = lane >> 2, col = lane & 3;
   const bool in = row < 6 && col < 3;
-  const int off = in ? 3 * row + col : 0;
+  const int off = in ? 3 * row + col : (REC > 18 ? 18 : 0);   // REC > 18: padding lanes read the record's zero pad (no branch)
   double c[NCH][2];
 #pragma unroll
   for (int k = 0; k < NCH; ++k) c[k][0] = c[k][1] = 0.0;
@@ -94,9 +94,10 @@ __global__ void __launch_bounds__(512) k_dmma_gather(int entries, int n_rec, dou
 #pragma unroll
     for (int k = 0; k < NCH; ++k) {
       st = st * 1664525u + 1013904223u;                 // same sequence in every lane: warp-uniform record ids
-      const int ri = (st >> 8) % n_rec, rj = (st >> 20) % n_rec;
-      const double a = in ? rec[ri * REC + off] : 0.0;
-      const double b = in ? rec[rj * REC + off] : 0.0;
+      const int ri = (st >> 8) & (n_rec - 1), rj = (st >> 20) & (n_rec - 1);   // n_rec is a power of two
+      double a, b;
+      if (REC > 18) { a = rec[ri * REC + off]; b = rec[rj * REC + off]; }
+      else { a = in ? rec[ri * REC + off] : 0.0; b = in ? rec[rj * REC + off] : 0.0; }
       dmma(c[k][0], c[k][1], a, b);
     }
   }
@@ -167,6 +168,13 @@ int main() {
     rep("gather+DMMA 1 chain  stride 18", time_ms([&] { k_dmma_gather<1, 18><<<blocks, threads, n_rec * 18 * 8>>>(entries, n_rec, sink); }));
     rep("gather+DMMA 2 chains stride 18", time_ms([&] { k_dmma_gather<2, 18><<<blocks, threads, n_rec * 18 * 8>>>(entries, n_rec, sink); }));
     rep("gather+DMMA 4 chains stride 18", time_ms([&] { k_dmma_gather<4, 18><<<blocks, threads, n_rec * 18 * 8>>>(entries, n_rec, sink); }));
+    cudaFuncSetAttribute(k_dmma_gather<1, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_dmma_gather<2, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(k_dmma_gather<8, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    rep("gather+DMMA 1 chain  stride 20", time_ms([&] { k_dmma_gather<1, 20><<<blocks, threads, n_rec * 20 * 8>>>(entries, n_rec, sink); }));
+    rep("gather+DMMA 2 chains stride 20", time_ms([&] { k_dmma_gather<2, 20><<<blocks, threads, n_rec * 20 * 8>>>(entries, n_rec, sink); }));
+    rep("gather+DMMA 8 chains stride 20", time_ms([&] { k_dmma_gather<8, 20><<<blocks, threads, n_rec * 20 * 8>>>(entries, n_rec, sink); }));
+    rep("gather+DMMA 4 chains stride 20, 256 thr", time_ms([&] { k_dmma_gather<4, 20><<<blocks, 256, n_rec * 20 * 8>>>(entries * 2, n_rec, sink); }));
     rep("gather+DMMA 4 chains stride 20", time_ms([&] { k_dmma_gather<4, 20><<<blocks, threads, n_rec * 20 * 8>>>(entries, n_rec, sink); }));
   }
   cudaError_t e = cudaDeviceSynchronize();
