@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200ba.so")
+# B200BA_LIB: load another build of the same library (kernel A/B experiments, tools/ab_variants.sh); default in-tree build
+LIB_PATH = os.environ.get("B200BA_LIB") or os.path.join(_HERE, "libb200ba.so")
 
 STATUS = {0: "OK", -1: "BAD_ARG", -2: "CUDA", -3: "NCCL", -4: "NOT_FINITE", -5: "OOM", -6: "INDEX_RANGE",
           -7: "NO_PROBLEM"}

@@ -432,7 +432,7 @@ static int greedy_bins(Handle* h, Tmp& tmp, const int* d_off, int n, int cap, in
   BA_CUDA(h, cudaMemcpyAsync(&n_bins, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, st));
   BA_CUDA(h, cudaStreamSynchronize(st));
   *n_bins_out = n_bins;
-  *bin_off_out = (int*)dalloc(h, (size_t)(n_bins + 1) * sizeof(int));
+  *bin_off_out = (int*)dalloc(h, (size_t)(n_bins + 1 + 8) * sizeof(int));   // + slack: staged as 16-byte aligned windows
   if (!*bin_off_out) return B200BA_OOM;
   int* items = nullptr;
   if (bin_item_out) {

@@ -21,6 +21,7 @@ constexpr int FLOW_THREADS = 512;
 constexpr int FLOW_WARPS = FLOW_THREADS / 32;
 constexpr int FLOW_SPI = 32 / FG;  // slots per item
 constexpr int FLOW_MAX_WT = 2 * FLOW_TILE / 32 + 4;  // warp tiles per tile: two consecutive ones hold > 32 observations
+constexpr int FLOW_WTO_INTS = 48;                    // staged wt_off window: FLOW_MAX_WT + 1 offsets + alignment slack, 16-byte units
 
 struct FlowSmem {
   // byte offsets inside the dynamic shared memory block
@@ -29,13 +30,14 @@ struct FlowSmem {
   static constexpr int IDXC = CAMP + 2 * CAMPREP_FIELDS * FLOW_CAM_SPAN * 8; // [2][FLOW_IDX_BYTES] cam window
   static constexpr int IDXP = IDXC + 2 * FLOW_IDX_BYTES;                     // [2][FLOW_IDX_BYTES] pt window
   static constexpr int META = IDXP + 2 * FLOW_IDX_BYTES;                     // [2][FLOW_META_CAP]
-  static constexpr int BAR = META + 2 * FLOW_META_CAP;                       // 4 mbarriers: inA[2], meta[2]
-  static constexpr int INFO = BAR + 4 * 8;                                   // [2][4] int4: staged tile_info of the A tile
+  static constexpr int BAR = META + 2 * FLOW_META_CAP;                       // 8 mbarriers: inA[2], meta[2], doneA[2], doneBC[2]
+  static constexpr int INFO = BAR + 8 * 8;                                   // [2][4] int4: staged tile_info of the A tile
   static constexpr int CTR = INFO + 2 * 64;                                  // q_next, doneA[2], doneBC[2], error
   static constexpr int RED = CTR + 8 * 4;                                    // [2][FLOW_MAX_WT][2] doubles: (sum r^2, max |g_p|)
   static constexpr int TSUM = RED + 2 * FLOW_MAX_WT * 2 * 8;                 // [64][2] doubles: tile sums, ring by k % 64
-  static constexpr int WST = TSUM + 64 * 2 * 8;                              // [FLOW_WARPS][4] int4: per-warp walk state
-  static constexpr int TOTAL = WST + FLOW_WARPS * 64;
+  static constexpr int WST = TSUM + 64 * 2 * 8;                              // [FLOW_WARPS][6] int4: per-warp walk state ring
+  static constexpr int WTO = WST + FLOW_WARPS * 96;                          // [2][FLOW_WTO_INTS] staged wt_off window
+  static constexpr int TOTAL = WTO + 2 * FLOW_WTO_INTS * 4;
 };
 static_assert(FlowSmem::TOTAL <= 232448, "dataflow kernel shared memory exceeds the 227 KB opt-in limit");
 
@@ -55,6 +57,9 @@ __device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned coun
 }
 __device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(unsigned long long* bar, unsigned parity) {
   unsigned ok;
@@ -76,6 +81,21 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, unsign
 
 #ifndef FLOW_PROF
 #define FLOW_PROF 0
+#endif
+#ifndef FLOW_MBAR_DEPS
+#define FLOW_MBAR_DEPS 1   // item dependencies wait on mbarriers (hardware-suspended try_wait) instead of polling counters
+#endif
+#ifndef FLOW_POLL_NS
+#define FLOW_POLL_NS 32
+#endif
+#ifndef FLOW_COOP_POINT_STORE
+#define FLOW_COOP_POINT_STORE 1
+#endif
+#ifndef FLOW_WALK_RING
+#define FLOW_WALK_RING 0   // walk state prefetched with cp.async (0: blocking global load at every step boundary)
+#endif
+#ifndef FLOW_STAGE_WTO
+#define FLOW_STAGE_WTO 0   // the tile's warp-tile offsets staged in shared memory with the other inputs
 #endif
 constexpr int FLOW_SPIN_LIMIT = 1 << 24;  // bail out instead of hanging the GPU if a dependency never resolves
 
@@ -102,8 +122,12 @@ __device__ __forceinline__ void flow_issue_inA(const FlowCtx& c, int t, int k) {
   const int cmin = i1.z, cspan = (pb.tile_info[4 * t].w & 2) ? i1.w : 0;
   unsigned long long* bar = c.bars + j;
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
-  mbar_expect_tx(bar, 2 * ib + (unsigned)(CAMPREP_FIELDS * cspan * 8) + 64u);
+  const int wt0a = i2.z & ~3;
+  const int nA = pb.tile_info[4 * t].x;
+  const unsigned wb = (FLOW_STAGE_WTO && nA + 1 <= FLOW_MAX_WT + 1) ? (unsigned)(((i2.z + nA + 1 - wt0a) * 4 + 15) & ~15) : 0u;
+  mbar_expect_tx(bar, 2 * ib + (unsigned)(CAMPREP_FIELDS * cspan * 8) + 64u + wb);
   bulk_g2s(c.sm + FlowSmem::INFO + j * 64, pb.tile_info + 4 * t, 64u, bar);
+  if (wb) bulk_g2s(c.sm + FlowSmem::WTO + j * (FLOW_WTO_INTS * 4), pb.wt_off + wt0a, wb, bar);
   bulk_g2s(c.sm + FlowSmem::IDXC + j * FLOW_IDX_BYTES, pb.cam + a0a, ib, bar);
   bulk_g2s(c.sm + FlowSmem::IDXP + j * FLOW_IDX_BYTES, pb.pt + a0a, ib, bar);
   if (cspan > 0) {
@@ -148,7 +172,7 @@ __device__ __forceinline__ bool flow_wait_bar(unsigned long long* bar, int gen, 
 __device__ __forceinline__ bool flow_wait_ctr(const int* ctr, int target, int* err) {
   int spins = 0;
   while (ld_acquire_s(ctr) < target) {
-    __nanosleep(32);
+    __nanosleep(FLOW_POLL_NS);
     if (++spins > FLOW_SPIN_LIMIT) { *err = 1; return false; }
   }
   return true;
@@ -172,7 +196,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
   if (threadIdx.x == 0) {
     for (int i = 0; i < 8; ++i) ctr[i] = 0;
     for (int i = 0; i < 128; ++i) reinterpret_cast<double*>(fsm + FlowSmem::TSUM)[i] = 0.0;
-    for (int i = 0; i < 4; ++i) mbar_init(bars + i, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(bars + i, 1);
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   __syncthreads();
@@ -190,7 +214,9 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
     const int j = kk & 1, t = tile_of(kk);
     // record buffer j was last read by the B / C items of tile kk - 2; the staged inputs of tile kk must have landed
     const long long c0 = FLOW_PROF ? clock64() : 0;
-    bool ok = flow_wait_ctr(&ctr[3 + j], tgtBC_prev, &ctr[5]) && flow_wait_bar(bars + j, kk >> 1, &ctr[5]);
+    bool ok = (FLOW_MBAR_DEPS ? (kk < 2 || flow_wait_bar(bars + 6 + j, (kk - 2) >> 1, &ctr[5]))
+                              : flow_wait_ctr(&ctr[3 + j], tgtBC_prev, &ctr[5])) &&
+              flow_wait_bar(bars + j, kk >> 1, &ctr[5]);
     ok = __all_sync(FULL, ok);
     if (!ok) return false;
     const long long c1 = FLOW_PROF ? clock64() : 0;
@@ -203,7 +229,10 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
     const bool cams_staged = (i0.w & 2) != 0;
     const int cmin = i1.z;
     double* rec = reinterpret_cast<double*>(fsm + FlowSmem::REC) + j * (FLOW_TILE * FREC);
-    const int a = pb.wt_off[wt], b = pb.wt_off[wt + 1], n = b - a;
+    // the tile's warp-tile offsets come from the staged window (one dependent trip to global memory less per item)
+    const int* s_wto = reinterpret_cast<const int*>(fsm + FlowSmem::WTO + j * (FLOW_WTO_INTS * 4)) + (i2.z & 3);
+    const bool wto_staged = FLOW_STAGE_WTO && i0.x <= FLOW_MAX_WT;
+    const int a = wto_staged ? s_wto[r] : pb.wt_off[wt], b = wto_staged ? s_wto[r + 1] : pb.wt_off[wt + 1], n = b - a;
     double cost2 = 0.0, gmax = 0.0;
     auto get_cam = [&](int c, double* cp) {
       if (cams_staged) {
@@ -232,6 +261,7 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
           ts[0] += s2;
           ts[1] = fmax(ts[1], m2);
           add_release_s(&ctr[1 + j], 1);  // now the consumers of the tile may start (and, later, reuse of tred)
+          if (FLOW_MBAR_DEPS) mbar_arrive(bars + 4 + j);
           // last A item of tile kk: its staging slot is free -> stage the inputs of tile kk + 2
           if (kk + 2 < K) flow_issue_inA(cx, tile_of(kk + 2), kk + 2);
         }
@@ -270,7 +300,9 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       // the records are complete: signal first, write the per-point outputs to global memory afterwards (the fence
       // below must not wait for them)
       flow_signal_A(cost2, gmax);
-      if (valid && lane == sg.first) store_point(pp, gp, p, Li, z, vals);
+      if (FLOW_COOP_POINT_STORE) {
+        if (valid) store_point_coop(pp, gp, p, Li, z, vals, lane - sg.first, sg.last - sg.first + 1);
+      } else if (valid && lane == sg.first) store_point(pp, gp, p, Li, z, vals);
       if (FLOW_PROF) { const long long ce = clock64(); tW += c1 - c0; tA += ce - c1; }
       return true;
     } else {
@@ -318,7 +350,8 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
     constexpr bool STAGED = decltype(staged_tag)::value;  // blob in shared memory (LDS) or too large: global memory
     const int j = k & 1, t = tile_of(k);
     const long long c0 = FLOW_PROF ? clock64() : 0;
-    bool ok = flow_wait_ctr(&ctr[1 + j], tgtA, &ctr[5]) && flow_wait_bar(bars + 2 + j, k >> 1, &ctr[5]);
+    bool ok = (FLOW_MBAR_DEPS ? flow_wait_bar(bars + 4 + j, k >> 1, &ctr[5]) : flow_wait_ctr(&ctr[1 + j], tgtA, &ctr[5])) &&
+              flow_wait_bar(bars + 2 + j, k >> 1, &ctr[5]);
     ok = __all_sync(FULL, ok);
     if (!ok) return false;
     __threadfence_block();
@@ -356,7 +389,10 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
     if (lane == 0) {
       const int old = add_release_s(&ctr[3 + j], 1);
       // last consumer of tile k: its metadata slot is free -> stage the blob of tile k + 2
-      if (old + 1 == tgtBC && k + 2 < K) flow_issue_meta(cx, tile_of(k + 2), k + 2);
+      if (old + 1 == tgtBC) {
+        if (FLOW_MBAR_DEPS) mbar_arrive(bars + 6 + j);   // the record buffer of tile k is free for the A items of tile k + 2
+        if (k + 2 < K) flow_issue_meta(cx, tile_of(k + 2), k + 2);
+      }
     }
     if (FLOW_PROF) { const long long ce = clock64(); tW += c1 - c0; if (r < nC) tC += ce - c1; else tB += ce - c1; }
     return true;
@@ -371,11 +407,26 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
   // per-warp walk state in shared memory (keeps 16 registers free for the item bodies): [0] / [1] = tile_info[.][0] of
   // the even / odd tile of the current pair, [2] / [3] = the pair after it, loaded one pair ahead so that the walk
   // never waits on global memory
-  int4* wst = reinterpret_cast<int4*>(fsm + FlowSmem::WST) + 4 * wid;
+  // ring of three pairs: [0] / [1] current, [2] / [3] next (arrived), [4] / [5] in flight (cp.async, no registers held,
+  // no stall on the global load when a step boundary is crossed)
+  int4* wst = reinterpret_cast<int4*>(fsm + FlowSmem::WST) + 6 * wid;
+  auto walk_fetch = [&](int slot, int k) {   // lane 0 only
+    if (k < K && !FLOW_WALK_RING) {
+      wst[slot] = pb.tile_info[4 * tile_of(k)];
+    } else if (k < K) {
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(smem_u32(wst + slot)), "l"(pb.tile_info + 4 * tile_of(k))
+                   : "memory");
+    } else {
+      wst[slot] = zero4;
+    }
+  };
   if (lane == 0) {
     wst[0] = zero4; wst[1] = zero4;
     wst[2] = K > 0 ? pb.tile_info[4 * tile_of(0)] : zero4;
     wst[3] = K > 1 ? pb.tile_info[4 * tile_of(1)] : zero4;
+    walk_fetch(4, 2);
+    walk_fetch(5, 3);
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
   }
   __syncwarp();
   // cumulative completion targets per buffer parity (A targets count the items plus the finisher's extra signal)
@@ -397,10 +448,14 @@ k_lin_flow(const __grid_constant__ Problem pb, const double* __restrict__ x, con
       if (!(s & 1)) {
         __syncwarp();
         if (lane == 0) {
+          asm volatile("cp.async.wait_group 0;\n" ::: "memory");   // issued one pair of steps ago: long since landed
           wst[0] = wst[2];
           wst[1] = wst[3];
-          wst[2] = (2 * m + 2 < K) ? pb.tile_info[4 * tile_of(2 * m + 2)] : zero4;
-          wst[3] = (2 * m + 3 < K) ? pb.tile_info[4 * tile_of(2 * m + 3)] : zero4;
+          wst[2] = wst[4];
+          wst[3] = wst[5];
+          walk_fetch(4, 2 * m + 4);
+          walk_fetch(5, 2 * m + 5);
+          asm volatile("cp.async.commit_group;\n" ::: "memory");
         }
         __syncwarp();
         n0 = wst[0].x;

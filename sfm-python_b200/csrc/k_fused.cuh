@@ -17,7 +17,10 @@ constexpr int FREC = 22;    // doubles per observation record
 #ifndef B200BA_FG
 #define B200BA_FG 2
 #endif
-constexpr int FG = B200BA_FG;  // lanes cooperating on one slot (2 or 4)
+constexpr int FG = B200BA_FG;
+#ifndef FLOW_STORE_INTERLEAVE
+#define FLOW_STORE_INTERLEAVE 1
+#endif  // lanes cooperating on one slot (2 or 4)
 constexpr int DPART = 40;   // doubles per self-slot partial: N (21) | diag U (6) | g_c (6) | b_c (6) | pad
 
 __device__ __forceinline__ void store_record(double* __restrict__ rec, const double* Jc, const double* Jp,
@@ -77,6 +80,24 @@ __device__ __forceinline__ void slot_reduce_store(const double* acc, double* __r
     static_assert(FG == 2 || FG == 4, "FG must be 2 or 4");
     const bool odd = g & 1;
     double q[NV / 2];
+#if FLOW_STORE_INTERLEAVE
+    // the two lanes of a slot take alternate 16-byte chunks of the partial (even / odd pairs of values), so together
+    // they fill whole 32-byte sectors with every store instruction instead of two half-used ones 144 bytes apart
+    static_assert(NV % 4 == 0, "interleaved store needs whole chunk pairs");
+#pragma unroll
+    for (int c = 0; c < NV / 4; ++c)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const double mine = odd ? acc[4 * c + 2 + h] : acc[4 * c + h];
+        const double give = odd ? acc[4 * c + h] : acc[4 * c + 2 + h];
+        q[2 * c + h] = mine + __shfl_xor_sync(FULL, give, 1);
+      }
+    if (active) {
+      double2* o = reinterpret_cast<double2*>(dst) + (g & 1);
+#pragma unroll
+      for (int c = 0; c < NV / 4; ++c) o[2 * c] = make_double2(q[2 * c], q[2 * c + 1]);
+    }
+#else
 #pragma unroll
     for (int k = 0; k < NV / 2; ++k) {
       const double mine = odd ? acc[NV / 2 + k] : acc[k];
@@ -88,6 +109,7 @@ __device__ __forceinline__ void slot_reduce_store(const double* acc, double* __r
 #pragma unroll
       for (int k = 0; k < NV / 2; ++k) o[k] = q[k];
     }
+#endif
   }
 }
 

@@ -80,6 +80,30 @@ __device__ __forceinline__ void store_point(double* __restrict__ pp, double* __r
   gp[3 * (int64_t)p] = vals[6]; gp[3 * (int64_t)p + 1] = vals[7]; gp[3 * (int64_t)p + 2] = vals[8];
 }
 
+// The same outputs written by the first lanes of the point's run together (every lane of the run holds identical Li, z,
+// vals after the segmented all-sum): lanes j = 0, 1 write alternate 16-byte chunks of pp[p] (whole 32-byte sectors per
+// store instruction, 3 instructions instead of 12 scattered 8-byte ones), lanes j < 3 one value of gp[p] each.
+// j = lane - first lane of the run, n = run length; n == 1 falls back to one lane writing everything.
+__device__ __forceinline__ void store_point_coop(double* __restrict__ pp, double* __restrict__ gp, int p, const double* Li,
+                                                 const double* z, const double* vals, int j, int n) {
+  if (n < 2) {
+    if (j == 0) store_point(pp, gp, p, Li, z, vals);
+    return;
+  }
+  if (j < 2) {
+    const bool odd = j & 1;
+    double2* o = reinterpret_cast<double2*>(pp + 12 * (int64_t)p) + j;
+    o[0] = odd ? make_double2(Li[2], Li[3]) : make_double2(Li[0], Li[1]);
+    o[2] = odd ? make_double2(z[0], z[1]) : make_double2(Li[4], Li[5]);
+    o[4] = odd ? make_double2(vals[2], vals[5]) : make_double2(z[2], vals[0]);
+  }
+  if (j < 3) {
+    const double v = j == 0 ? vals[6] : (j == 1 ? vals[7] : vals[8]);
+    gp[3 * (int64_t)p + j] = v;
+    if (n == 2 && j == 0) gp[3 * (int64_t)p + 2] = vals[8];
+  }
+}
+
 // stage one warp's Y rows through shared memory and store them as one contiguous run
 __device__ __forceinline__ void store_Y(double* sY /*[32*19]*/, const double* Yv, bool valid, int lane, int n,
                                         double* __restrict__ Ydst /* = Y + 18*a */) {
