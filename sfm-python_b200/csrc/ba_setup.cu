@@ -286,6 +286,73 @@ __global__ void k_tile_info(int n_st, long long C, const int* __restrict__ st_of
   units[t] = u;
 }
 
+// Bank-aware entry order.  The slot kernels read per-observation records (22 doubles, stride 11 x 16 bytes) with 16-byte
+// loads; the eight lanes of a quarter-warp (4 consecutive slots x 2 lanes, lane g of a slot takes entries g, g + 2, ...)
+// collide in shared memory exactly when two of their records have the same index modulo 8.  The order of the entries
+// INSIDE a slot is free (it only fixes the order of a sum), so it is chosen greedily here: round by round, every lane
+// takes the remaining entry of its slot whose record classes are the least used in this round.  One thread per group of
+// four slots; random order gives about 2.4 shared-memory wavefronts per ideal one, this order about 1.5.
+template <class E>
+__device__ __forceinline__ int entry_cost(E v, unsigned mi, unsigned mj);
+template <>
+__device__ __forceinline__ int entry_cost<unsigned>(unsigned v, unsigned mi, unsigned mj) {
+  return (int)((mi >> (4 * ((v >> 16) & 7))) & 15u) + (int)((mj >> (4 * (v & 7))) & 15u);
+}
+template <>
+__device__ __forceinline__ int entry_cost<unsigned short>(unsigned short v, unsigned mi, unsigned) {
+  return (int)((mi >> (4 * (v & 7))) & 15u);
+}
+template <class E>
+__device__ __forceinline__ void entry_mark(E v, unsigned& mi, unsigned& mj);
+template <>
+__device__ __forceinline__ void entry_mark<unsigned>(unsigned v, unsigned& mi, unsigned& mj) {
+  mi += 1u << (4 * ((v >> 16) & 7));
+  mj += 1u << (4 * (v & 7));
+}
+template <>
+__device__ __forceinline__ void entry_mark<unsigned short>(unsigned short v, unsigned& mi, unsigned&) {
+  mi += 1u << (4 * (v & 7));
+}
+
+template <class E>
+__global__ void k_bank_order(int n_st, const int* __restrict__ tile_slot_off, const int* __restrict__ slot_a,
+                             const int* __restrict__ slot_n, long long a_shift_unused, E* __restrict__ ent) {
+  (void)a_shift_unused;
+  for (int t = blockIdx.x; t < n_st; t += gridDim.x) {
+    const int ps = tile_slot_off[t], np = tile_slot_off[t + 1] - ps;
+    for (int qg = threadIdx.x; 4 * qg < np; qg += blockDim.x) {
+      const int s0 = ps + 4 * qg, ns = min(4, np - 4 * qg);
+      int a[4], n[4], maxn = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        a[k] = k < ns ? slot_a[s0 + k] : 0;
+        n[k] = k < ns ? slot_n[s0 + k] : 0;
+        maxn = max(maxn, n[k]);
+      }
+      for (int e0 = 0; e0 < maxn; e0 += 2) {
+        unsigned mi = 0, mj = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          for (int g = 0; g < 2; ++g) {
+            const int e = e0 + g;
+            if (e >= n[k]) break;
+            E* base = ent + a[k];
+            int best = e, bestc = 1 << 20;
+            E bestv = base[e];
+            for (int c = e; c < n[k]; ++c) {
+              const E v = base[c];
+              const int cost = entry_cost<E>(v, mi, mj);
+              if (cost < bestc) { bestc = cost; best = c; bestv = v; if (cost == 0) break; }
+            }
+            if (best != e) { base[best] = base[e]; base[e] = bestv; }
+            entry_mark<E>(bestv, mi, mj);
+          }
+        }
+      }
+    }
+  }
+}
+
 // one CTA per tile: pack the tile's slot descriptors and entries into its blob
 __global__ void k_blob_fill(int n_st, const int* __restrict__ blob_off, int4* __restrict__ info,
                             const int* __restrict__ slot_a, const int* __restrict__ slot_n,
@@ -1052,6 +1119,15 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     pb.n_dslot = sl.n_slot; pb.dslot_a = sl.slot_a; pb.dslot_n = sl.slot_n;
     pb.tile_dslot_off = sl.tile_off; pb.cam_dslot_off = sl.grp_off; pb.cam_dslots = sl.grp_slots;
     mark("9 self slots");
+    {
+      const char* e_bo = getenv("B200BA_BANK_ORDER");   // 0: keep the sorted entry order (A/B measurements)
+      if (!(e_bo && atoi(e_bo) == 0) && pb.n_st > 0 && pb.schur_tiles) {
+        const int g = (int)std::min<int64_t>(pb.n_st, 65535 * 16);
+        if (n_ent > 0) k_bank_order<unsigned><<<g, 32, 0, st>>>(pb.n_st, pb.tile_slot_off, pb.slot_a, pb.slot_n, 0, pb.tent);
+        if (N > 0) k_bank_order<unsigned short><<<g, 32, 0, st>>>(pb.n_st, pb.tile_dslot_off, pb.dslot_a, pb.dslot_n, 0, pb.dent);
+        mark("9b bank-aware entry order");
+      }
+    }
     // ---- 10. dataflow kernel: per-tile info + contiguous metadata blobs (bulk-copied to shared memory per tile)
     const char* e_flow = getenv("B200BA_FLOW");
     if (pb.tile_obs <= FLOW_TILE && !(e_flow && atoi(e_flow) == 0) && pb.n_st > 0) {
