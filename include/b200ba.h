@@ -103,6 +103,16 @@ int b200ba_create(b200ba_handle** out, int device);
 int b200ba_destroy(b200ba_handle* h);
 const char* b200ba_last_error(const b200ba_handle* h);
 
+/* Multi-GPU behind the single-process call of sfm.py:264-268: ONE handle that fronts n_devices GPUs of this
+ * process (device_ids distinct CUDA ordinals, 1 <= n_devices <= 8).  b200ba_set_problem shards the points over the devices
+ * (contiguous point ranges balanced by observation count, cameras replicated), b200ba_solve / b200ba_solve_io /
+ * b200ba_residuals / b200ba_normal_equations (S only for n_cam <= 512) take and return the FULL arrays of the reference
+ * call; b200ba_set_fixed_cameras / set_loss / set_two_level / get_stats / reset_stats / set_profiling apply to every
+ * device.  Every other entry point returns B200BA_BAD_ARG on such a handle.  Each device is driven by its own host thread;
+ * the reduced camera system is exchanged through peer memory over NVLink (direct peer pointers), the small sums through
+ * NCCL.  The reference has no counterpart (its solve is single-threaded scipy). */
+int b200ba_create_multi(b200ba_handle** out, const int* device_ids, int n_devices);
+
 /* Multi-GPU (one process per GPU): rank 0 calls b200ba_nccl_unique_id, the host broadcasts the
  * 128 bytes (torch.distributed), every rank calls b200ba_comm_init.  The reference has no
  * collective; this is the all-reduce of the reduced camera system. */

@@ -50,6 +50,7 @@ _I64 = C.POINTER(C.c_int64)
 SIGNATURES = {
     "b200ba_version": (C.c_int, []),
     "b200ba_create": (C.c_int, [C.POINTER(_P), C.c_int]),
+    "b200ba_create_multi": (C.c_int, [C.POINTER(_P), C.POINTER(C.c_int), C.c_int]),
     "b200ba_destroy": (C.c_int, [_P]),
     "b200ba_last_error": (C.c_char_p, [_P]),
     "b200ba_nccl_unique_id": (C.c_int, [_P]),

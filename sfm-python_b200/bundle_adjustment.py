@@ -78,14 +78,26 @@ class _PinnedPool:
 class Engine:
     """One GPU's handle (``b200ba_handle``): problem upload, residual/Jacobian/normal equations, LM solve."""
 
-    def __init__(self, device=None):
+    def __init__(self, device=None, devices=None):
+        """``device``: one CUDA ordinal (default ``LOCAL_RANK`` or 0).  ``devices``: a list of ordinals -> ONE engine that
+        shards every problem over those GPUs inside this process (``b200ba_create_multi``); ``set_problem`` / ``residuals`` /
+        ``normal_equations`` / ``solve`` then take and return the full arrays exactly like the single-GPU engine."""
         self.lib = _lib.load()
-        self.device = default_device() if device is None else int(device)
         h = C.c_void_p()
-        rc = self.lib.b200ba_create(C.byref(h), self.device)
+        if devices is not None and len(devices) > 1:
+            self.devices = tuple(int(d) for d in devices)
+            self.device = self.devices[0]
+            ids = (C.c_int * len(self.devices))(*self.devices)
+            rc = self.lib.b200ba_create_multi(C.byref(h), ids, len(self.devices))
+        else:
+            self.device = default_device() if device is None else int(device)
+            if devices is not None and len(devices) == 1:
+                self.device = int(devices[0])
+            self.devices = (self.device,)
+            rc = self.lib.b200ba_create(C.byref(h), self.device)
         if rc != 0:
-            raise BAError(f"b200ba_create(device={self.device}) failed: {_lib.STATUS.get(rc, rc)} "
-                          "(a CUDA device is required; there is no CPU fallback)")
+            raise BAError(f"b200ba_create(devices={list(self.devices)}) failed: {_lib.STATUS.get(rc, rc)} "
+                          "(CUDA devices are required; there is no CPU fallback)")
         self.h = h
         self._pinned = _PinnedPool(self.lib)
         self.n_cam = self.n_pts = self.n_obs = 0
@@ -366,7 +378,15 @@ def pack_Rt(poses):
 # ---------------------------------------------------------------------------------------------
 # Reference call surface
 # ---------------------------------------------------------------------------------------------
-_cache = {"key": None, "engine": None}
+_cache = {"key": None, "engine": None, "n_gpus": None}
+
+
+def default_n_gpus():
+    """GPUs the drop-in call uses: ``B200BA_GPUS`` (default 1), so an unmodified ``sfm_lite/sfm.py`` reaches several GPUs."""
+    try:
+        return max(1, int(os.environ.get("B200BA_GPUS", "1")))
+    except ValueError:
+        return 1
 
 
 def _problem_key(n_cam, n_pts, ci, pi, uv, K):
@@ -381,11 +401,17 @@ def _problem_key(n_cam, n_pts, ci, pi, uv, K):
     return (int(n_cam), int(n_pts), h.digest())
 
 
-def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K):
-    """The engine holding this problem on the device (uploaded once, reused by later calls)."""
-    key = _problem_key(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
+def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K, n_gpus=None):
+    """The engine holding this problem on the device(s) (uploaded once, reused by later calls).  ``n_gpus`` (default
+    ``B200BA_GPUS`` or 1): the first n GPUs of the box inside this process."""
+    n_gpus = default_n_gpus() if n_gpus is None else max(1, int(n_gpus))
+    key = _problem_key(n_cam, n_pts, camera_indices, point_indices, points_2d, K) + (n_gpus,)
+    if _cache["engine"] is not None and _cache["n_gpus"] != n_gpus:
+        _cache["engine"].close()
+        _cache["engine"], _cache["key"] = None, None
     if _cache["key"] != key or _cache["engine"] is None:
-        eng = _cache["engine"] or _new_engine()
+        eng = _cache["engine"] or _new_engine(n_gpus)
+        _cache["n_gpus"] = n_gpus
         _cache["key"] = None                       # a failed upload leaves no stale key behind
         _cache["engine"] = eng
         eng.set_problem(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
@@ -393,8 +419,8 @@ def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K):
     return _cache["engine"]
 
 
-def _new_engine():
-    return Engine()
+def _new_engine(n_gpus=1):
+    return Engine(devices=list(range(n_gpus))) if n_gpus > 1 else Engine()
 
 
 def compute_residuals(x, n_cameras, n_points, camera_indices, point_indices, points_2d, K):
@@ -572,12 +598,13 @@ def _is_ba_residual(fun):
 
 def bundle_adjust(x0, n_cam, n_pts, camera_indices, point_indices, points_2d, K, ftol=1e-10, xtol=1e-8, gtol=1e-8,
                   max_nfev=None, verbose=0, solver="auto", engine=None, fixed_camera_indices=(), loss="linear", f_scale=1.0,
-                  **engine_opts):
+                  n_gpus=None, **engine_opts):
     """Global bundle adjustment of ``x0`` (layout of ``sfm.py:255-257``) on the GPU; returns :class:`BAResult`.
 
+    ``n_gpus``: GPUs of this process to shard the points over (default ``B200BA_GPUS`` or 1).
     ``fixed_camera_indices``: cameras held fixed, the hook of ``bundle_adjustment.py:6,13``; ``loss`` / ``f_scale``: scipy's
     robust-loss keywords (``result.cost`` is then ``0.5 * f_scale**2 * sum(rho((fun / f_scale)**2))`` like scipy's)."""
-    eng = engine or engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
+    eng = engine or engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K, n_gpus)
     fixed = tuple(sorted(int(i) for i in fixed_camera_indices))
     if fixed != tuple(sorted(getattr(eng, "fixed", ()))):
         eng.set_fixed_cameras(fixed)
@@ -606,6 +633,7 @@ def least_squares(fun, x0, jac="2-point", bounds=None, method="trf", ftol=1e-8, 
                         "compute_residuals and args=(n_cam, n_points, camera_indices, point_indices, points_2d, K)")
     n_cam, n_pts, ci, pi, uv, K = args
     solver = extra.pop("solver", "auto")
+    n_gpus = extra.pop("n_gpus", None)
     # keywords that would change scipy's answer are honoured or refused, never ignored
     if kwargs:
         raise NotImplementedError("`kwargs` for the residual function are not supported (the BA residual takes none)")
@@ -627,7 +655,7 @@ def least_squares(fun, x0, jac="2-point", bounds=None, method="trf", ftol=1e-8, 
         raise ValueError(f"`loss` must be one of {sorted(LOSSES)}")
     return bundle_adjust(x0, n_cam, n_pts, ci, pi, uv, K, ftol=ftol, xtol=xtol, gtol=gtol, max_nfev=max_nfev,
                          verbose=verbose, solver=solver, fixed_camera_indices=_fixed_from_mask(jac_sparsity, n_cam),
-                         loss=loss, f_scale=f_scale)
+                         loss=loss, f_scale=f_scale, n_gpus=n_gpus)
 
 
 def _fixed_from_mask(mask, n_cam):

@@ -188,7 +188,7 @@ __global__ void k_p2p_wait(const unsigned long long* __restrict__ flags, int nra
 void p2p_release(Handle* h) {
   P2P& q = h->p2p;
   for (int r = 0; r < P2P_MAX_RANKS; ++r)
-    if (q.peer[r] && q.peer[r] != q.base) cudaIpcCloseMemHandle(q.peer[r]);
+    if (q.peer[r] && q.peer[r] != q.base && !q.direct) cudaIpcCloseMemHandle(q.peer[r]);
   if (q.base) cudaFree(q.base);
   if (q.done) cudaFree(q.done);
   cudaGetLastError();
@@ -211,11 +211,19 @@ int p2p_setup(Handle* h) {
   memset(&mine, 0, sizeof(mine));
   if (cudaMalloc(&q.base, need) != cudaSuccess || cudaMalloc((void**)&q.done, 256) != cudaSuccess ||
       cudaMemset(q.base, 0, need) != cudaSuccess || cudaMemset(q.done, 0, 256) != cudaSuccess ||
-      cudaIpcGetMemHandle(&mine, q.base) != cudaSuccess) {
+      (!h->in_process && cudaIpcGetMemHandle(&mine, q.base) != cudaSuccess)) {
     cudaGetLastError();
     ok = 0;
   }
   q.bytes = need;
+  q.direct = h->in_process;
+  if (q.direct) {
+    // every rank is a handle of this process: the 64-byte slot carries {buffer address, device ordinal} instead of an
+    // IPC handle (an IPC handle cannot be opened by the process that exported it); peer access is enabled below
+    memset(&mine, 0, sizeof(mine));
+    long long v[2] = {(long long)(uintptr_t)q.base, (long long)h->device};
+    memcpy(&mine, v, sizeof(v));
+  }
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
   const int per = 9;   // 8 longs of handle + 1 status
   long long* d = (long long*)pool_alloc(h, (size_t)per * (h->nranks + 1) * sizeof(long long));
@@ -234,6 +242,19 @@ int p2p_setup(Handle* h) {
       if (r == h->rank) { q.peer[r] = q.base; continue; }
       cudaIpcMemHandle_t hh;
       memcpy(&hh, &all[(size_t)per * r], 64);
+      if (q.direct) {
+        long long v[2];
+        memcpy(v, &hh, sizeof(v));
+        int can = 0;
+        cudaError_t e = cudaDeviceCanAccessPeer(&can, h->device, (int)v[1]);
+        if (e == cudaSuccess && can) {
+          e = cudaDeviceEnablePeerAccess((int)v[1], 0);
+          if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); e = cudaSuccess; }
+        }
+        if (e != cudaSuccess || !can) { cudaGetLastError(); q.peer[r] = nullptr; ok = 0; }
+        else q.peer[r] = (void*)(uintptr_t)v[0];
+        continue;
+      }
       if (cudaIpcOpenMemHandle(&q.peer[r], hh, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
         cudaGetLastError();
         q.peer[r] = nullptr;
@@ -249,6 +270,9 @@ int p2p_setup(Handle* h) {
   BA_CUDA(h, cudaStreamSynchronize(h->stream));
   pool_free(h, d);
   for (int r = 0; r < h->nranks; ++r) ok = ok && all[r];
+  if (getenv("B200BA_SETUP_PROF") && atoi(getenv("B200BA_SETUP_PROF")))
+    fprintf(stderr, "[b200ba p2p] rank %d/%d: %s\n", h->rank, h->nranks,
+            !ok ? "peer mapping failed -> NCCL all-gather" : (q.direct ? "direct peer pointers (one process)" : "CUDA IPC"));
   if (!ok) { p2p_release(h); return 0; }
   q.epoch = 0;
   q.on = true;
@@ -475,3 +499,4 @@ int check_flow_error(Handle* h) {
 
 #include "ba_lm.inc"
 #include "ba_capi.inc"
+#include "ba_multi.inc"

@@ -206,6 +206,7 @@ struct P2P {
   void* peer[P2P_MAX_RANKS] = {};    // base of every rank's buffer as mapped here (own entry = base)
   unsigned int* done = nullptr;      // CTA counter of k_p2p_push
   unsigned long long epoch = 0;      // exchanges done since the buffer was (re)allocated; identical on every rank
+  bool direct = false;               // peers live in this process (b200ba_create_multi): raw pointers + peer access, no IPC
 };
 
 struct Handle {
@@ -224,6 +225,7 @@ struct Handle {
   // NCCL
   void* comm = nullptr;
   int rank = 0, nranks = 1;
+  bool in_process = false;         // all ranks are handles of one process (b200ba_create_multi)
   int64_t n_obs_global = 0;
   P2P p2p;
   // stats

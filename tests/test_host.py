@@ -155,3 +155,92 @@ def test_problem_key_is_a_content_digest():
     assert key(n_cam, n_pts, ci, pi, uv, K) == key(n_cam, n_pts, ci.copy(), pi.copy(), uv.copy(), K)
     assert key(n_cam, n_pts, ci, pi, uv, K) != key(n_cam, n_pts, ci, pi, uv2, K)
     assert key(n_cam, n_pts, ci, pi, uv, K) != key(n_cam, n_pts, ci, pi, uv.astype(np.int64), K)
+
+
+def _import_real_sfm():
+    """The reference's own sfm_lite.sfm, imported from /root/reference with matplotlib stubbed (absent here; the module
+    only uses it for plots).  Exists in the build container only: the GPU box has no reference tree."""
+    import sys
+    import types
+    ref = "/root/reference"
+    if not os.path.isdir(os.path.join(ref, "sfm_lite")):
+        pytest.skip("reference tree not present")
+    if "matplotlib" not in sys.modules:
+        try:
+            import matplotlib  # noqa: F401
+        except Exception:
+            mpl = types.ModuleType("matplotlib")
+            mpl.use = lambda *a, **k: None
+            sys.modules["matplotlib"] = mpl
+            sys.modules["matplotlib.pyplot"] = types.ModuleType("matplotlib.pyplot")
+    if ref not in sys.path:
+        sys.path.insert(0, ref)
+    try:
+        import sfm_lite.sfm as S
+    except Exception as e:      # a missing third-party import of the reference is not this repo's failure
+        pytest.skip(f"reference module does not import here: {e!r}")
+    return S
+
+
+def test_install_on_the_real_sfm_module():
+    """b200ba.install on the REAL sfm_lite.sfm: the three names the BA call of sfm.py:264-268 resolves are ours, and
+    SFM._apply_bundle_adjustment, run on a small stand-in graph, hands our least_squares exactly the reference's packing
+    (x0 layout of sfm.py:255-257, dense camera ranks, point-major observation arrays, ftol = tol) and writes back what it
+    returns (sfm.py:271-281)."""
+    import types
+
+    import b200ba
+    S = _import_real_sfm()
+    saved = (S.least_squares, S.compute_residuals, S.create_sparsity_matrix)
+    try:
+        b200ba.install(S)
+        g = S.SFM._apply_bundle_adjustment.__globals__
+        assert g["least_squares"] is b200ba.least_squares and g["compute_residuals"] is b200ba.compute_residuals
+        assert g["create_sparsity_matrix"] is b200ba.create_sparsity_matrix
+        # a stand-in for SFM.graph: 3 registered cameras (graph ids 5, 2, 9) + 1 unregistered, 4 points
+        rng = np.random.default_rng(0)
+
+        def pose(k):
+            from scipy.spatial.transform import Rotation as Rot
+            H = np.eye(4)
+            H[:3, :3] = Rot.from_rotvec(0.1 * rng.standard_normal(3)).as_matrix()
+            H[:3, 3] = rng.standard_normal(3)
+            return H
+        nodes = [types.SimpleNamespace(idx=i, registered=i != 7, H=pose(i)) for i in (5, 2, 7, 9)]
+        obs = [(0, None, 5, None, np.array([10, 20])), (0, None, 2, None, np.array([11, 21])),
+               (1, None, 2, None, np.array([12, 22])), (1, None, 9, None, np.array([13, 23])),
+               (2, None, 5, None, np.array([14, 24])), (2, None, 9, None, np.array([15, 25])),
+               (3, None, 5, None, np.array([16, 26])), (3, None, 2, None, np.array([17, 27]))]
+
+        class Graph:
+            def __init__(self):
+                self.nodes = nodes
+                self.X3d = rng.standard_normal((4, 3))
+
+            def pt3ds_pt2ds(self):
+                return iter(obs)
+
+            def __getitem__(self, cam_id):
+                return next(n for n in nodes if n.idx == cam_id)
+        seen = {}
+
+        def spy(fun, x0, **kw):
+            seen.update(fun=fun, x0=np.array(x0), kw=kw)
+            x = np.array(x0)
+            x[-12:] += 1.0                   # "optimised" points
+            return types.SimpleNamespace(x=x)
+        S.least_squares = spy
+        me = types.SimpleNamespace(graph=Graph(), K=np.eye(3))
+        X_before = me.graph.X3d.copy()
+        S.SFM._apply_bundle_adjustment(me, tol=1e-7, verbose=0)
+        assert seen["fun"] is b200ba.compute_residuals
+        n_cam, n_pts, ci, pi, uv, K = seen["kw"]["args"]
+        assert (n_cam, n_pts) == (3, 4) and seen["kw"]["ftol"] == 1e-7 and seen["kw"]["x_scale"] == "jac"
+        assert list(ci) == [0, 1, 1, 2, 0, 2, 0, 1] and list(pi) == [0, 0, 1, 1, 2, 2, 3, 3]       # dense ranks 5->0, 2->1, 9->2
+        assert np.asarray(uv).shape == (8, 2) and len(seen["x0"]) == 6 * 3 + 3 * 4
+        assert np.allclose(seen["x0"][3:6], nodes[0].H[:3, 3]) and np.allclose(seen["x0"][18:], X_before.ravel())
+        mask = seen["kw"]["jac_sparsity"]
+        assert isinstance(mask, b200ba.bundle_adjustment.JacobianSparsity) and mask.shape == (16, 30)
+        assert np.allclose(me.graph.X3d, X_before + 1.0)                                            # write-back of sfm.py:281
+    finally:
+        S.least_squares, S.compute_residuals, S.create_sparsity_matrix = saved
