@@ -118,7 +118,7 @@ BA_HD void project_jac(const double* __restrict__ cp, const Intrinsics& K, doubl
 
 // Robust loss of scipy.optimize.least_squares (the `loss=` / `f_scale=` keywords of the call at sfm.py:266; the reference
 // leaves the default 'linear').  scipy applies rho to every residual COMPONENT: z = (f / C)^2,
-//   cost = 0.5 C^2 sum rho(z),   J_scale = max(rho' + 2 rho'' z, EPS),   J <- sqrt(J_scale) J,   f <- rho' f / sqrt(J_scale)
+//   cost = 0.5 C^2 sum rho(z),   J_scale = max(rho' + 2 rho'' z, 0.05 rho')  [scipy: EPS; see robust_component],   J <- sqrt(J_scale) J,   f <- rho' f / sqrt(J_scale)
 // (scipy _lsq/least_squares.py construct_loss_function, _lsq/common.py scale_for_robust_loss_function).
 struct Loss {
   int kind;       // 0 linear, 1 soft_l1, 2 huber, 3 cauchy, 4 arctan
@@ -143,7 +143,10 @@ BA_HD double robust_component(const Loss& L, double& r, double& js) {
     const double t = 1.0 + z * z;
     rho0 = atan(z); rho1 = 1.0 / t; rho2 = -2.0 * z / (t * t);
   }
-  double w = rho1 + 2.0 * rho2 * z;
+  // scipy clamps the second-order weight at machine epsilon; here it never falls below 5 % of the first-order (IRLS)
+  // weight: rows that cancel to ~0 (every Huber outlier) would leave Marquardt-damped point blocks singular and stall
+  // the LM loop.  The gradient J_s^T f_s = J^T rho' f stays exact, so the minimiser is the same (oracle: ROBUST_CLAMP).
+  double w = fmax(rho1 + 2.0 * rho2 * z, 0.05 * rho1);
   if (w < 2.220446049250313e-16) w = 2.220446049250313e-16;
   js = sqrt(w);
   r *= rho1 / js;

@@ -51,29 +51,27 @@ def test_scaled_normal_equations_match_the_oracle(engine, loss):
 @pytest.mark.parametrize("k", [0, 1, 2])
 @pytest.mark.parametrize("loss", ["soft_l1", "huber", "cauchy"])
 def test_robust_converged_cost_vs_scipy(engine, k, loss):
-    """SceauxCastle calls 0-2 with 5 % gross outliers: converged robust cost vs scipy (real reference residual on call 0)
-    one-sided 1e-6, two-sided against the oracle LM with the same loss, through the drop-in least_squares."""
+    """SceauxCastle calls 0-2 with 5 % outliers, started at the converged linear-loss solution (a robust cost is not
+    convex: from the raw 292 px starts scipy and any LM end in different minima; goldens: oracle/make_golden.py robust).
+    Through the drop-in least_squares: the robust cost is the oracle's cost at the returned x (1e-9), never above scipy's
+    (one-sided 1e-6; scipy's TRF crawls on these gauge-free problems and mostly stops on its evaluation cap), two-sided
+    1e-6 where scipy itself converged, and within 1e-5 of the oracle LM run with the same loss."""
     import b200ba
     g = load_golden("robust_scipy.npz")
     d = load_golden(f"sceaux_ba_{k}.npz")
     n_cam, n_pts, ci, pi, _, K = golden_args(d)
-    uv = g[f"uv_{k}"]
-    f_scale = float(g["f_scale"])
+    uv, x_start, f_scale = g[f"uv_{k}"], g[f"x_start_{k}"], float(g["f_scale"])
     mask = b200ba.create_sparsity_matrix(n_cam, n_pts, len(ci), ci, pi)
-    res = b200ba.least_squares(b200ba.compute_residuals, d["x0"], jac_sparsity=mask, verbose=0, x_scale='jac', ftol=1e-10,
+    res = b200ba.least_squares(b200ba.compute_residuals, x_start, jac_sparsity=mask, verbose=0, x_scale='jac', ftol=1e-10,
                                method='trf', loss=loss, f_scale=f_scale, args=(n_cam, n_pts, ci, pi, uv, K))
     assert res.status > 0
     chk = O.robust_cost(O.residuals(res.x, n_cam, n_pts, ci, pi, uv, K), loss, f_scale)
     assert abs(chk - res.cost) <= 1e-9 * res.cost
     sc, lm = float(g[f"cost_{k}_{loss}"]), float(g[f"lm_cost_{k}_{loss}"])
-    best = min(sc, lm)
-    assert res.cost <= best * (1 + 1e-6), (res.cost, sc, lm)
-    if abs(sc - lm) <= 1e-6 * lm:                 # scipy and the oracle LM agree: two-sided
+    assert res.cost <= sc * (1 + 1e-6), (res.cost, sc, lm)
+    if int(g[f"status_{k}_{loss}"]) > 0 and abs(sc - lm) <= 1e-6 * lm:
         assert abs(res.cost - sc) <= 1e-6 * sc
-    # a robust minimum need not be unique: where the GPU found a lower one, the oracle LM from there must not improve it
-    if res.cost < best * (1 - 1e-6):
-        again = O.lm_solve(res.x, n_cam, n_pts, ci, pi, uv, K, ftol=1e-12, loss=loss, f_scale=f_scale, max_iter=20)
-        assert res.cost - again["cost"] <= 1e-6 * res.cost
+    assert abs(res.cost - lm) <= 1e-5 * lm, (res.cost, lm)
 
 
 def test_loss_resets_with_the_problem_and_bad_arguments(engine):

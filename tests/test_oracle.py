@@ -215,7 +215,7 @@ def test_robust_scaling_matches_scipy(loss):
     for C in (0.7, 2.5):
         lf = construct_loss_function(len(f), loss, C)
         Js, fs = scale_for_robust_loss_function(J.copy(), f.copy(), lf(f))
-        js, r = O.robust_scale(f, loss, C)
+        js, r = O.robust_scale(f, loss, C, clamp=0.0)          # clamp=0: scipy's own rows
         # where rho' + 2 rho'' z cancels to rounding noise (huber's linear part, far outliers) scipy's row factor is
         # sqrt(noise or eps) ~ 1e-8: only the products J_s^T J_s (~ 0) and J_s^T f_s = J^T rho' f are meaningful there
         ok = js > 1e-6
@@ -225,3 +225,10 @@ def test_robust_scaling_matches_scipy(loss):
         g_s, g_o = Js * fs[:, None], (J * js[:, None]) * r[:, None]
         assert np.abs(g_s - g_o).max() <= 1e-12 * np.abs(g_s).max()
         assert abs(lf(f, cost_only=True) - O.robust_cost(f, loss, C)) <= 1e-13 * O.robust_cost(f, loss, C)
+        # the default clamp (used by the LM loops) changes no row whose second-order weight is at least 5 % of rho' and
+        # never changes the gradient
+        jc, rc = O.robust_scale(f, loss, C)
+        keep = js * js >= O.ROBUST_CLAMP * O.robust_rho((f / C) ** 2, loss)[1]
+        assert np.array_equal(jc[keep], js[keep]) and np.abs(rc - r)[keep].max() == 0.0
+        g_c = (J * jc[:, None]) * rc[:, None]
+        assert np.abs(g_c - g_s).max() <= 1e-12 * np.abs(g_s).max()
