@@ -94,6 +94,7 @@ typedef struct b200ba_stats {
   int64_t n_tl_builds;    /* rebuilds of the coarse operator of the two-level PCG preconditioner */
   double ms_reproj;       /* k_reproj_err alone */
   double ms_residual_kernel;  /* k_residual alone (ms_residual also covers k_cam_prep and the partial reduction) */
+  double ms_chol_mc;      /* k_chol_mc alone: multi-CTA dense Cholesky on the FP64 tensor cores (factor + both substitutions) */
 } b200ba_stats;
 
 int b200ba_version(void);

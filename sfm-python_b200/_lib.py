@@ -39,7 +39,8 @@ class Stats(C.Structure):
                [(n, C.c_int64) for n in ("n_tiles", "n_pair_slots", "n_self_slots")] + [("ms_jacobian", C.c_double),
                                                                                          ("n_tl_builds", C.c_int64),
                                                                                          ("ms_reproj", C.c_double),
-                                                                                         ("ms_residual_kernel", C.c_double)]
+                                                                                         ("ms_residual_kernel", C.c_double),
+                                                                                         ("ms_chol_mc", C.c_double)]
 
 
 _P = C.c_void_p

@@ -345,7 +345,7 @@ static int alloc_work(Handle* h) {
   WALLOC(w.dc, 6 * C);
   WALLOC(w.pcg, 6 * C * 5 + C * 36);
   WALLOC(w.pcg_part, (int64_t)2 * 4 * std::max(pcg_grid(h), 1));
-  if (C <= DENSE_MAX_CAM) { WALLOC(w.dense, 36 * C * C); }
+  if (C <= DENSE_RESIDENT_CAM) { WALLOC(w.dense, 36 * C * C); }
   if (pb.tl) {
     WALLOC(w.tl_G, C * 42);
     WALLOC(w.tl_SP, (int64_t)pb.nnz_sp * 42);

@@ -25,7 +25,8 @@ constexpr int FLOW_CAM_SPAN = 64;     // staged camera window per tile (21 x 64 
 constexpr int FLOW_META_CAP = 8192;   // staged tile metadata (slot descriptors + entries), bytes
 constexpr int FLOW_IDX_BYTES = (FLOW_TILE + 8) * 4;  // staged cam[] / pt[] window incl. alignment slack
 constexpr int NSCAL = 32;          // device scalar slots
-constexpr int DENSE_MAX_CAM = 512; // dense S export / Cholesky limit
+constexpr int DENSE_MAX_CAM = 1024; // dense Cholesky limit (n = 6144: 302 MB of dense S)
+constexpr int DENSE_RESIDENT_CAM = 512;  // dense S export limit; the buffer is always allocated up to here
 constexpr int MAX_DEVICES = 64;    // per-device caches of function attributes / occupancy
 
 // scalar slots (device array `scal`); "sum" slots are all-reduced with ncclSum
@@ -178,7 +179,9 @@ struct Work {
   double* dc = nullptr;       // [6C] camera step
   double* pcg = nullptr;      // [6C*5 + C*36] r u p w s Minv
   double* pcg_part = nullptr; // [grid*4]
-  double* dense = nullptr;    // [(6C)^2] Cholesky work (only n_cam <= DENSE_MAX_CAM)
+  double* dense = nullptr;    // [(6C)^2] dense S (resident for n_cam <= DENSE_RESIDENT_CAM, else allocated by the first dense solve)
+  double* chol = nullptr;     // multi-CTA Cholesky: padded matrix, rhs, solution, inverses of the diagonal factors
+  int chol_np = 0;
   // two-level preconditioner
   double* tl_G = nullptr;     // [C*42]   G_c
   double* tl_SP = nullptr;    // [nnz_sp*42]

@@ -451,6 +451,7 @@ __global__ void __launch_bounds__(CHB_T) k_cholesky_blocked(int n, double* __res
 }
 
 #include "k_twolevel.cuh"
+#include "k_chol_mc.cuh"
 
 }  // namespace
 
@@ -556,20 +557,70 @@ int launch_pcg2(Handle* h, double rtol, int max_iter) {
   return 0;
 }
 
+// profiling only: CUDA events directly around one launch on the library stream
+struct KernelEvents {
+  Handle* h; double* acc; bool on;
+  KernelEvents(Handle* h_, double* acc_) : h(h_), acc(acc_), on(h_->profile) { if (on) cudaEventRecord(h->ev2, h->stream); }
+  void stop() {
+    if (!on) return;
+    cudaEventRecord(h->ev3, h->stream);
+    cudaEventSynchronize(h->ev3);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, h->ev2, h->ev3);
+    *acc += ms;
+  }
+};
+
 int launch_cholesky(Handle* h) {
   Work& w = h->w;
   const int n = (int)(6 * h->pb.C);
-  if (!w.dense) return fail(h, B200BA_BAD_ARG, "dense Cholesky needs n_cam <= 512");
+  if (h->pb.C > DENSE_MAX_CAM) return fail(h, B200BA_BAD_ARG, "dense Cholesky needs n_cam <= " + std::to_string(DENSE_MAX_CAM));
+  if (!w.dense) {   // allocated on first use above the always-resident size (36 C^2 doubles)
+    w.dense = (double*)dalloc(h, (size_t)36 * h->pb.C * h->pb.C * sizeof(double));
+    if (!w.dense) return B200BA_OOM;
+  }
   launch_densify(h, w.dense);
-  if (n <= CHB_MAX_N) {
+  const char* e_mc = getenv("B200BA_CHOL_MC");   // 1: the multi-CTA DMMA factorisation at every size (tests), 0: never
+  const bool want_mc = e_mc ? atoi(e_mc) != 0 : n > 384;   // measured: the single-CTA panel kernel takes 6 ms at n = 768, this one 1.2 ms
+  if (!want_mc && n <= CHB_MAX_N) {
     static bool attr_dev[MAX_DEVICES] = {};
     bool& attr = attr_dev[h->device % MAX_DEVICES];
     if (!attr) { cudaFuncSetAttribute(k_cholesky_blocked, cudaFuncAttributeMaxDynamicSharedMemorySize, CHB_SMEM); attr = true; }
     k_cholesky_blocked<<<1, CHB_T, CHB_SMEM, h->stream>>>(n, w.dense, w.b, w.dc, w.scal);
-  } else {
+    h->st.launches += 1;
+  } else if (!want_mc) {
     k_cholesky<<<1, CH_T, n * sizeof(double), h->stream>>>(n, w.dense, w.b, w.dc, w.scal);
+    h->st.launches += 1;
+  } else {
+    const int nb = (n + CM_NB - 1) / CM_NB, np = nb * CM_NB;
+    if (!w.chol || w.chol_np < np) {
+      w.chol = (double*)dalloc(h, ((size_t)np * np + 2 * (size_t)np + (size_t)nb * CM_NB * CM_NB + 8) * sizeof(double));
+      if (!w.chol) return B200BA_OOM;
+      w.chol_np = np;
+    }
+    CholMcArgs a;
+    a.n = n; a.np = np; a.nb = nb;
+    a.A = w.chol;
+    a.b = a.A + (size_t)np * np;
+    a.x = a.b + np;
+    a.Linv = a.x + np;
+    a.fail = reinterpret_cast<int*>(a.Linv + (size_t)nb * CM_NB * CM_NB);
+    a.scal = w.scal;
+    static int per_sm_dev[MAX_DEVICES] = {};
+    int& per_sm = per_sm_dev[h->device % MAX_DEVICES];
+    if (per_sm == 0) {
+      cudaFuncSetAttribute(k_chol_mc, cudaFuncAttributeMaxDynamicSharedMemorySize, CM_SMEM);
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_chol_mc, CM_T, CM_SMEM) != cudaSuccess || per_sm < 1) per_sm = 1;
+    }
+    k_chol_mc_pad<<<(unsigned)(((int64_t)np * np + 255) / 256), 256, 0, h->stream>>>(n, np, w.dense, w.b, a.A, a.b);
+    const int grid = std::min(per_sm, 2) * h->sm_count;
+    void* args[] = {&a};
+    KernelEvents ev(h, &h->st.ms_chol_mc);
+    BA_CUDA(h, cudaLaunchCooperativeKernel((void*)k_chol_mc, dim3(grid), dim3(CM_T), args, CM_SMEM, h->stream));
+    ev.stop();
+    BA_CUDA(h, cudaMemcpyAsync(w.dc, a.x, (size_t)n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    h->st.launches += 2;
   }
-  h->st.launches += 1;
   BA_CUDA(h, cudaGetLastError());
   return 0;
 }

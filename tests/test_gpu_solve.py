@@ -263,3 +263,43 @@ def test_two_level_with_shuffled_camera_numbering(engine):
     per_iter = {k: v[1] / v[2] for k, v in out.items()}
     assert per_iter["shuffled"] <= 1.5 * per_iter["ordered"] + 5, (out, b.pcg_iters)
     assert per_iter["shuffled"] * 3 < b.pcg_iters / b.n_iter, (out, b.pcg_iters, b.n_iter)
+
+
+# ------------------------------------------------------------------ multi-CTA dense Cholesky on the FP64 tensor cores
+def test_dense_cholesky_mc_step_matches_oracle(engine, monkeypatch):
+    """k_chol_mc (64 x 64 blocks, DMMA trailing update, both substitutions) forced on a small problem (n = 54, one padded
+    block) and on config B (n = 294 -> 5 blocks): the LM step equals the oracle's dense solve to 1e-6, and equals the
+    single-CTA blocked Cholesky to 1e-9."""
+    import b200ba
+    lam = 1e-3
+    for pb in (b200ba.synthetic.make_problem(9, 300, 1300, seed=5, window=8), b200ba.synthetic.make_config("B")):
+        engine.set_problem(*pb.args())
+        monkeypatch.setenv("B200BA_CHOL_MC", "0")
+        d0, pred0, new0 = engine.lm_step(pb.x0, lam, solver="cholesky")
+        monkeypatch.setenv("B200BA_CHOL_MC", "1")
+        d1, pred1, new1 = engine.lm_step(pb.x0, lam, solver="cholesky")
+        assert np.abs(d1 - d0).max() <= 1e-9 * np.abs(d0).max()
+        assert abs(new1 - new0) <= 1e-9 * new0
+        d_ref, pred_ref, _ = O.lm_step(pb.x0, *pb.args(), lam)
+        assert np.abs(d1 - d_ref).max() <= 1e-6 * np.abs(d_ref).max()
+        assert abs(pred1 - pred_ref) <= 1e-6 * abs(pred_ref)
+    monkeypatch.delenv("B200BA_CHOL_MC")
+
+
+def test_dense_cholesky_mc_at_600_cameras(engine):
+    """n = 3600 (57 block columns): solver='cholesky' takes the multi-CTA path by default above n = 768; its LM step
+    equals a PCG step solved to 1e-12 and the converged cost equals the PCG solve (1e-6), checked against the oracle
+    residual."""
+    import b200ba
+    pb = b200ba.synthetic.make_problem(600, 60000, 240000, seed=6)
+    engine.set_problem(*pb.args())
+    lam = 1e-4
+    dc, predc, newc = engine.lm_step(pb.x0, lam, solver="cholesky")
+    dp, predp, newp = engine.lm_step(pb.x0, lam, solver="pcg")
+    assert np.abs(dc - dp).max() <= 1e-6 * np.abs(dp).max()
+    assert abs(newc - newp) <= 1e-9 * newp
+    x_c, c = engine.solve(pb.x0, ftol=1e-10, solver="cholesky")
+    x_p, p = engine.solve(pb.x0, ftol=1e-10, solver="pcg")
+    assert c.status > 0 and abs(c.cost - p.cost) <= 1e-6 * p.cost
+    chk = 0.5 * float(np.sum(O.residuals(x_c, *pb.args()) ** 2))
+    assert abs(chk - c.cost) <= 1e-9 * c.cost

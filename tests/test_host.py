@@ -24,7 +24,7 @@ def test_library_exports_every_header_symbol():
 def test_struct_layouts_match_header():
     import b200ba
     L = b200ba.bundle_adjustment._lib
-    assert ctypes.sizeof(L.Options) == 64 and ctypes.sizeof(L.Result) == 80 and ctypes.sizeof(L.Stats) == 184
+    assert ctypes.sizeof(L.Options) == 64 and ctypes.sizeof(L.Result) == 80 and ctypes.sizeof(L.Stats) == 192
 
 
 def test_no_cpu_fallback_without_gpu():
