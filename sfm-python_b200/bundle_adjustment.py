@@ -452,8 +452,22 @@ def solve_pnp(point3ds, point2ds, K, dist_coeffs=None, engine=None, **kw):
     ``cv2_lite.solve_pnp.solve_pnp``): returns ``(success, rvec (3, 1), tvec (3, 1))``.  Distortion must be zero."""
     if dist_coeffs is not None and np.any(np.asarray(dist_coeffs) != 0):
         raise NotImplementedError("lens distortion is not part of the reference's pipeline (zeros at sfm.py:207)")
+    if pnp_is_degenerate(point3ds):
+        raise NotImplementedError("coplanar (or fewer than 6) object points: the 12-column DLT start is not unique there; "
+                                  "cv2.solvePnP switches to a homography start, which this library does not implement")
     o = (engine or _aux_engine()).solve_pnp_batch([(point3ds, point2ds)], K)[0]
     return bool(o[8] >= 0 and np.isfinite(o[6])), o[:3].reshape(3, 1).copy(), o[3:6].reshape(3, 1).copy()
+
+
+def pnp_is_degenerate(point3ds, rel_tol=1e-4):
+    """True when the DLT start of :func:`solve_pnp` is not unique: fewer than 6 points, or object points that are
+    (numerically) coplanar -- smallest singular value of the centred point cloud below ``rel_tol`` times the largest (the
+    planarity test cv2.solvePnP applies before choosing its homography initialisation)."""
+    X = np.asarray(point3ds, dtype=np.float64).reshape(-1, 3)
+    if len(X) < 6:
+        return True
+    sv = np.linalg.svd(X - X.mean(axis=0), compute_uv=False)
+    return bool(sv[2] <= rel_tol * max(sv[0], 1e-300))
 
 
 def triangulate_points(M1, M2, pts1, pts2, engine=None):
@@ -694,10 +708,12 @@ class _Cv2Proxy:
     def __getattr__(self, name):
         return getattr(self._real, name)
 
-    @staticmethod
-    def solvePnP(objectPoints, imagePoints, cameraMatrix, distCoeffs=None, *a, **kw):
-        return solve_pnp(np.asarray(objectPoints, dtype=np.float64).reshape(-1, 3),
-                         np.asarray(imagePoints, dtype=np.float64).reshape(-1, 2), cameraMatrix, distCoeffs)
+    def solvePnP(self, objectPoints, imagePoints, cameraMatrix, distCoeffs=None, *a, **kw):
+        X = np.asarray(objectPoints, dtype=np.float64).reshape(-1, 3)
+        if a or kw or pnp_is_degenerate(X) or (distCoeffs is not None and np.any(np.asarray(distCoeffs) != 0)):
+            # planar / tiny point sets, distortion, extrinsic guesses and solver flags stay with the real cv2
+            return self._real.solvePnP(objectPoints, imagePoints, cameraMatrix, distCoeffs, *a, **kw)
+        return solve_pnp(X, np.asarray(imagePoints, dtype=np.float64).reshape(-1, 2), cameraMatrix, distCoeffs)
 
     @staticmethod
     def triangulatePoints(projMatr1, projMatr2, projPoints1, projPoints2):

@@ -11,9 +11,17 @@
 
 #include <algorithm>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "ba_internal.h"
 
 namespace b200ba {
+
+// NVTX range of one LM phase (header-only NVTX 3: a no-op unless a profiler is attached)
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 int partial_capacity(const Handle* h);
 int pcg_grid(Handle* h);
@@ -404,6 +412,7 @@ struct PhaseTimer {
 
 // linearise at w.x (camprep must match) and reduce across ranks; leaves Sup, b, gc, udiag, sums ready
 int linearize_all(Handle* h, double lambda) {
+  NvtxRange nv("b200ba:linearize+schur+exchange");
   Work& w = h->w;
   launch_linearize(h, w.x, lambda);
   {
@@ -427,6 +436,7 @@ int linearize_all(Handle* h, double lambda) {
 }
 
 int camera_solve(Handle* h, int solver, double rtol, int max_iter) {
+  NvtxRange nv("b200ba:camera_solve");
   PhaseTimer t(h, &h->st.ms_camera_solve);
   if (solver == B200BA_SOLVER_AUTO) solver = (h->pb.C <= 64) ? B200BA_SOLVER_CHOLESKY : B200BA_SOLVER_PCG;
   if (solver == B200BA_SOLVER_CHOLESKY) return launch_cholesky(h);
@@ -456,6 +466,7 @@ void tl_note_iters(Handle* h, int iters) {
 
 // trial point: cameras x + dc -> xn, camprep_n; points by back-substitution; sums all-reduced
 int trial_step(Handle* h, double lambda) {
+  NvtxRange nv("b200ba:backsub+trial_cost");
   Work& w = h->w;
   PhaseTimer t(h, &h->st.ms_backsub_trial);
   launch_cam_prep(h, w.x, w.dc, w.xn, w.camprep_n, w.camprep, w.cstep);
@@ -466,6 +477,7 @@ int trial_step(Handle* h, double lambda) {
 }
 
 int fetch_scalars(Handle* h) {
+  NvtxRange nv("b200ba:fetch_scalars(host sync)");
   Work& w = h->w;
   BA_CUDA(h, cudaMemcpyAsync(w.h_scal, w.scal, NSCAL * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   BA_CUDA(h, cudaMemcpyAsync(w.h_scal + NSCAL, w.sums, S_NSUM * sizeof(double), cudaMemcpyDeviceToHost, h->stream));

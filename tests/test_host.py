@@ -86,7 +86,7 @@ def test_install_rebinds_names_and_cv2_proxy_delegates():
     import types
 
     import b200ba
-    fake_cv2 = types.SimpleNamespace(SIFT_create=lambda: "sift", NORM_L2=4, solvePnP=lambda *a: "cv2", triangulatePoints=lambda *a: "cv2")
+    fake_cv2 = types.SimpleNamespace(SIFT_create=lambda: "sift", NORM_L2=4, solvePnP=lambda *a, **k: "cv2", triangulatePoints=lambda *a: "cv2")
     mod = types.SimpleNamespace(least_squares=None, compute_residuals=None, create_sparsity_matrix=None, cv2=fake_cv2)
     b200ba.install(mod)
     assert mod.least_squares is b200ba.least_squares and mod.compute_residuals is b200ba.compute_residuals
@@ -97,6 +97,14 @@ def test_install_rebinds_names_and_cv2_proxy_delegates():
     proxy = mod.cv2
     b200ba.install(mod, geometry=True)
     assert mod.cv2 is proxy            # idempotent
+    # coplanar object points (cv2 starts from a homography there), fewer than 6 points, distortion: the real cv2 answers
+    plane = np.c_[np.random.default_rng(0).uniform(-1, 1, (12, 2)), np.full(12, 3.0)]
+    assert b200ba.bundle_adjustment.pnp_is_degenerate(plane) and b200ba.bundle_adjustment.pnp_is_degenerate(plane[:4])
+    assert not b200ba.bundle_adjustment.pnp_is_degenerate(np.random.default_rng(1).uniform(-1, 1, (12, 3)))
+    assert proxy.solvePnP(plane, np.zeros((12, 2)), np.eye(3), np.zeros((1, 5))) == "cv2"
+    assert proxy.solvePnP(np.random.default_rng(1).uniform(-1, 1, (12, 3)), np.zeros((12, 2)), np.eye(3), np.ones((1, 5))) == "cv2"
+    with pytest.raises(NotImplementedError):
+        b200ba.solve_pnp(plane, np.zeros((12, 2)), np.eye(3))
 
 
 def _ba_args(n=40):
