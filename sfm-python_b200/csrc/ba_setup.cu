@@ -61,6 +61,11 @@ __global__ void k_offsets(int64_t N, int M, const int* __restrict__ key, int* __
     for (int q = cur + 1; q <= M; ++q) off[q] = (int)N;
 }
 
+__global__ void k_cam_seen(int64_t N, const int* __restrict__ cam, int* __restrict__ seen) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < N) seen[cam[i]] = 1;   // every writer stores the same value
+}
+
 __global__ void k_iota(int64_t N, int* __restrict__ a) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i < N) a[i] = (int)i;
@@ -842,11 +847,15 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     const char* e_x = getenv("B200BA_XCHG");  // 0: always all-reduce, 1: always sparse exchange (when possible)
     const bool want_x = pb.fused && pb.schur_tiles && !(e_x && atoi(e_x) == 0);
     if (want_x) {
-      std::vector<int> h_cam_off(C + 1, 0);
-      BA_CUDA(h, cudaMemcpyAsync(h_cam_off.data(), pb.cam_off, (C + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
+      // cameras this rank observes (the camera-sorted offsets of step 4 only exist in the unfused pipeline)
+      std::vector<int> h_seen(C + 1, 0);
+      TMP_ALLOC(d_seen, int, C + 1);
+      BA_CUDA(h, cudaMemsetAsync(d_seen, 0, (C + 1) * sizeof(int), st));
+      if (N > 0) k_cam_seen<<<nblk(N, T), T, 0, st>>>(N, pb.cam, d_seen);
+      BA_CUDA(h, cudaMemcpyAsync(h_seen.data(), d_seen, (C + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
       BA_CUDA(h, cudaStreamSynchronize(st));
       for (int64_t c = 0; c < C; ++c)
-        if (h_cam_off[c + 1] > h_cam_off[c]) keys_host.push_back((long long)c * C + c);
+        if (h_seen[c]) keys_host.push_back((long long)c * C + c);
       std::sort(keys_host.begin(), keys_host.end());
       keys_host.erase(std::unique(keys_host.begin(), keys_host.end()), keys_host.end());
     }
