@@ -287,6 +287,21 @@ int p2p_setup(Handle* h) {
   return 0;
 }
 
+// Receive slot of this rank for the exchange that the next p2p_exchange call performs, in every rank's buffer.
+PeerDst p2p_next_dst(Handle* h) {
+  PeerDst d;
+  P2P& q = h->p2p;
+  if (!q.on) return d;
+  const unsigned long long e = q.epoch + 1;
+  const long long slots = 64 + (long long)(e & 1) * h->nranks * h->pb.x_stride;
+  for (int k = 1; k <= h->nranks; ++k) {
+    const int r = (h->rank + k) % h->nranks;
+    d.p[k - 1] = (double*)q.peer[r] + slots + (long long)h->rank * h->pb.x_stride;
+  }
+  d.n = h->nranks;
+  return d;
+}
+
 int p2p_exchange(Handle* h) {
   P2P& q = h->p2p;
   Problem& pb = h->pb;
@@ -296,10 +311,14 @@ int p2p_exchange(Handle* h) {
   const long long slots = 64 + parity * h->nranks * pb.x_stride;        // doubles from the base of a buffer
   PeerPtrs pp{};
   for (int r = 0; r < h->nranks; ++r) { pp.p[r] = (double*)q.peer[r]; pp.f[r] = (unsigned long long*)q.peer[r]; }
-  const long long n2 = pb.x_stride / 2;
-  const int grid = (int)std::min<long long>((n2 + 1023) / 1024, (long long)h->sm_count * 8);
-  k_p2p_push<<<grid, 256, 0, h->stream>>>(reinterpret_cast<const double2*>(w.xsend), n2, h->rank, h->nranks, pp,
-                                          slots + (long long)h->rank * pb.x_stride, q.epoch, q.done);
+  // the blocks of S were stored into the peers' slots by the slot reduction itself (launch_linearize, PeerDst); what is
+  // pushed here is the tail [b | g_c | diag U | scalars] -- and the epoch flag, which covers both (the reduction kernel
+  // has completed before this one starts: stream order)
+  const long long head = h->direct_push ? ((long long)pb.xl_max * 36) : 0;   // xl_max * 36 is even
+  const long long n2 = (pb.x_stride - head) / 2;
+  const int grid = (int)std::max<long long>(1, std::min<long long>((n2 + 1023) / 1024, (long long)h->sm_count * 8));
+  k_p2p_push<<<grid, 256, 0, h->stream>>>(reinterpret_cast<const double2*>(w.xsend + head), n2, h->rank, h->nranks, pp,
+                                          slots + (long long)h->rank * pb.x_stride + head, q.epoch, q.done);
   k_p2p_wait<<<1, 32, 0, h->stream>>>((const unsigned long long*)q.base, h->nranks, q.epoch,
                                       reinterpret_cast<int*>(w.scal + S_P2P_ERR));
   h->st.launches += 2;

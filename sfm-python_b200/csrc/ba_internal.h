@@ -202,6 +202,9 @@ struct Work {
 // rank through CUDA IPC.  k_p2p_push stores this rank's contribution straight into slot [parity][rank] of every peer
 // and then publishes the epoch in the peers' flag words; k_p2p_wait spins (bounded) on the local flags.
 constexpr int P2P_MAX_RANKS = 8;
+// destinations of a direct push from inside a producing kernel: base of this rank's receive slot in every rank's buffer
+// (own rank included), ordered so that rank r starts with rank r + 1 (at any moment the ranks write to different peers)
+struct PeerDst { double* p[P2P_MAX_RANKS]; int n = 0; };
 struct P2P {
   bool on = false;
   void* base = nullptr;              // local buffer
@@ -229,6 +232,7 @@ struct Handle {
   void* comm = nullptr;
   int rank = 0, nranks = 1;
   bool in_process = false;         // all ranks are handles of one process (b200ba_create_multi)
+  bool direct_push = false;        // this linearisation's slot reduction stored its blocks straight into the peers' slots
   int64_t n_obs_global = 0;
   P2P p2p;
   // stats
@@ -266,6 +270,7 @@ int comm_allgather_f64(Handle* h, const double* send, double* recv, int64_t coun
 int p2p_setup(Handle* h);      // collective; after setup_problem (needs pb.x_stride); leaves h->p2p.on
 void p2p_release(Handle* h);
 int p2p_exchange(Handle* h);   // xsend -> every rank's receive slots; sets w.xrecv to the slots of this epoch
+PeerDst p2p_next_dst(Handle* h);   // where the NEXT exchange's contribution of this rank goes (n = 0: no peer memory)
 
 // ---- ba_setup.cu
 int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam_idx, const int64_t* pt_idx,

@@ -342,7 +342,7 @@ __global__ void k_cam_sums(int C, const int* __restrict__ cam_dslot_off, const i
 __global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_list, const int* __restrict__ blk_r,
                                 const int* __restrict__ blk_c, const int* __restrict__ blk_slot_off,
                                 const int* __restrict__ blk_slots, const double* __restrict__ spart,
-                                const double* __restrict__ camsum, double lambda, double* __restrict__ Sup) {
+                                const double* __restrict__ camsum, double lambda, double* __restrict__ Sup, PeerDst dst) {
   const int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (t >= (int64_t)n_blk * 36) return;
   const int e = (int)(t % 36);
@@ -353,7 +353,15 @@ __global__ void k_slot_reduce_S(int n_blk, const int* __restrict__ blk_list, con
     s += camsum[c * DPART + tri6(min(r, cc), max(r, cc))];
     if (r == cc) s -= lambda * camsum[c * DPART + 21 + r];
   }
-  Sup[t] = -s;
+  if (dst.n > 0) {
+    // multi-GPU: the reduced block goes straight into this rank's receive slot on every rank (peer memory over NVLink;
+    // own buffer included) -- the transfer overlaps the reduction instead of following it as a separate copy pass
+    // (no fence here: the kernel boundary orders these stores before k_p2p_push, whose last CTA publishes the epoch with a
+    // system-scope fence + st.release.sys; a per-thread system fence made this kernel 60 % slower)
+    for (int k = 0; k < dst.n; ++k) dst.p[k][t] = -s;
+  } else {
+    Sup[t] = -s;
+  }
 }
 
 // Sparse exchange, receiving side: every block of S = sum of the ranks' packed contributions in ascending rank order;

@@ -201,14 +201,18 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
     t.begin();
     k_cam_sums<<<cdiv(pb.C * 40, 128), 128, 0, st>>>((int)pb.C, pb.cam_dslot_off, pb.cam_dslots, w.dpart, w.camsum, o_ud,
                                                     o_gc, o_b);
-    if (pb.xchg)
+    if (pb.xchg) {
+      const char* e_dp = getenv("B200BA_DIRECT_PUSH");   // 0: stage in xsend and copy afterwards (A/B)
+      PeerDst dst = (e_dp && atoi(e_dp) == 0) ? PeerDst{} : p2p_next_dst(h);
+      h->direct_push = dst.n > 0;
       k_slot_reduce_S<<<cdiv((int64_t)pb.xl_n * 36, 128), 128, 0, st>>>(pb.xl_n, pb.xl_blk, pb.blk_r, pb.blk_c,
                                                                         pb.blk_slot_off, pb.blk_slots, w.spart, w.camsum,
-                                                                        lambda, w.xsend);
-    else
+                                                                        lambda, w.xsend, dst);
+    } else {
       k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 128), 128, 0, st>>>(pb.n_blk, nullptr, pb.blk_r, pb.blk_c,
                                                                          pb.blk_slot_off, pb.blk_slots, w.spart, w.camsum,
-                                                                         lambda, w.Sup);
+                                                                         lambda, w.Sup, PeerDst{});
+    }
     t.end(&h->st.ms_slot_reduce);
     h->st.launches += 4;
     h->st.n_linearize += 1;
