@@ -174,6 +174,15 @@ int b200ba_solve_pnp(b200ba_handle* h, int64_t n_problems, const int64_t* counts
 int b200ba_triangulate(b200ba_handle* h, int64_t n, const double* M1, const double* M2, const double* pts1,
                        const double* pts2, const double* H1, const double* H2, double* X_out, unsigned char* mask_out);
 
+/* The reference's non-linear triangulation (cv2_lite/triangulate_points.py:122-184, not called by the pipeline itself): the
+ * DLT point of b200ba_triangulate refined by minimising the reference's objective (:94-118 -- the squared reprojection
+ * errors of the four image coordinates, squared again by its solver: a sum of 4th powers).  The reference hands all points
+ * to one scipy call with default tolerances; here every point runs its own damped Gauss-Newton to the minimiser, so the
+ * objective is never above the reference's and the points agree to the reference's own stopping accuracy (1e-3).
+ * X_out: n x 4 rows [X Y Z 1]; max_iter <= 0 -> 100. */
+int b200ba_triangulate_nonlinear(b200ba_handle* h, int64_t n, const double* M1, const double* M2, const double* pts1,
+                                 const double* pts2, int32_t max_iter, double* X_out);
+
 /* The per-observation reprojection-error loop of SFM._apply_increment (sfm.py:234-238), which calls
  * calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14) once per observation in Python:
  * err_i = || pi(K (R_c X_p + t_c)) - uv_i ||  over the observations of the problem on the handle, in the pipeline's

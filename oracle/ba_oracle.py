@@ -495,6 +495,56 @@ def triangulate_points_linear2(M1, M2, pts1, pts2):
     return X / X[3]
 
 
+def triangulation_objective(M1, M2, pts1, pts2, X3d):
+    """The reference's objective of cv2_lite/triangulate_points.py:94-118 per point: its residual vector is the SQUARED
+    reprojection error of each of the four image coordinates, which scipy squares again -- sum of the 4th powers."""
+    Xh = np.vstack([np.asarray(X3d, dtype=np.float64)[:3], np.ones(np.asarray(X3d).shape[1])])
+    a, b = np.asarray(M1) @ Xh, np.asarray(M2) @ Xh
+    e = np.vstack([a[:2] / a[2] - np.asarray(pts1), b[:2] / b[2] - np.asarray(pts2)])
+    return np.sum(e ** 4, axis=0)
+
+
+def triangulate_points_nonlinear(M1, M2, pts1, pts2, max_iter=100):
+    """cv2_lite/triangulate_points.py:122-184: DLT start, then minimise the objective above.  The reference hands all points
+    to one scipy least_squares call with default tolerances (it stops ~1e-3 short of the minimiser); the points are
+    independent, so this restatement runs a damped Gauss-Newton per point to the minimiser.  pts are (2, N); returns (4, N)."""
+    M1, M2 = np.asarray(M1, dtype=np.float64), np.asarray(M2, dtype=np.float64)
+    p1, p2 = np.asarray(pts1, dtype=np.float64), np.asarray(pts2, dtype=np.float64)
+    X = triangulate_points_linear2(M1, M2, p1, p2)[:3].copy()
+
+    def res(x, i):
+        xh = np.append(x, 1.0)
+        a, b = M1 @ xh, M2 @ xh
+        e = np.array([a[0] / a[2] - p1[0, i], a[1] / a[2] - p1[1, i], b[0] / b[2] - p2[0, i], b[1] / b[2] - p2[1, i]])
+        Je = np.stack([(M1[0, :3] - a[0] / a[2] * M1[2, :3]) / a[2], (M1[1, :3] - a[1] / a[2] * M1[2, :3]) / a[2],
+                       (M2[0, :3] - b[0] / b[2] * M2[2, :3]) / b[2], (M2[1, :3] - b[1] / b[2] * M2[2, :3]) / b[2]])
+        return e * e, 2.0 * e[:, None] * Je
+
+    for i in range(X.shape[1]):
+        x, lam = X[:, i].copy(), 1e-3
+        r, J = res(x, i)
+        c = float(r @ r)
+        for _ in range(max_iter):
+            Hm = J.T @ J
+            try:
+                dx = np.linalg.solve(Hm + lam * np.diag(np.diag(Hm)) + 1e-300 * np.eye(3), -(J.T @ r))
+            except np.linalg.LinAlgError:
+                break
+            r2, J2 = res(x + dx, i)
+            c2 = float(r2 @ r2)
+            if np.isfinite(c2) and c2 < c:
+                done = (c - c2) < 1e-16 * c or np.linalg.norm(dx) < 1e-14 * np.linalg.norm(x)
+                x, r, J, c, lam = x + dx, r2, J2, c2, max(lam / 3.0, 1e-12)
+                if done:
+                    break
+            else:
+                lam *= 4.0
+                if lam > 1e12:
+                    break
+        X[:, i] = x
+    return np.vstack([X, np.ones(X.shape[1])])
+
+
 def visibility_mask(H1, H2, X3d_H):
     """sfm.py:219-221: both cameras see the point in front of them."""
     P1 = np.linalg.inv(H1) @ X3d_H

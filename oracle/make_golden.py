@@ -345,8 +345,13 @@ def gen_triangulate():
                    [265.42037964, 989.33227539]])
     dcv = cv2.triangulatePoints(dM1, dM2, d1.T, d2.T)
     dcv = dcv / dcv[-1]
+    # the reference's non-linear refinement (triangulate_points.py:122-184; one scipy call over all points, ~20 s) on the
+    # visible points, and the value of its own objective there
+    vis = np.flatnonzero(mask)
+    nl = tp.triangulate_points(M1, M2, pts1[vis].T, pts2[vis].T)
+    nl_cost = float(np.sum(O.triangulation_objective(M1, M2, pts1[vis].T, pts2[vis].T, nl)))
     np.savez_compressed(os.path.join(GOLD, "ref_triangulate.npz"), K=K, H1=H1, H2=H2, pts1=pts1, pts2=pts2, X_cv2=cv,
-                        X_ref_linear2=ref2, mask=mask, doc_M1=dM1, doc_M2=dM2, doc_pts1=d1, doc_pts2=d2, doc_X_cv2=dcv,
+                        X_ref_linear2=ref2, mask=mask, X_ref_nonlinear=nl, ref_nonlinear_cost=nl_cost, doc_M1=dM1, doc_M2=dM2, doc_pts1=d1, doc_pts2=d2, doc_X_cv2=dcv,
                         cv2_version=cv2.__version__)
     print("triangulate golden: n", n, "visible", int(mask.sum()), "max |cv2 - linear2| rel",
           np.abs(cv - ref2).max() / np.abs(cv).max(), "cv2", cv2.__version__)

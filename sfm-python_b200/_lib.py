@@ -64,6 +64,7 @@ SIGNATURES = {
     "b200ba_unpack_cameras": (C.c_int, [_P, C.c_int64, _P, _P]),
     "b200ba_solve_pnp": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P, _P, C.c_int32, _P]),
     "b200ba_triangulate": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "b200ba_triangulate_nonlinear": (C.c_int, [_P, C.c_int64, _P, _P, _P, _P, C.c_int32, _P]),
     "b200ba_reproj_errors": (C.c_int, [_P, _P, _P, _P, _D]),
     "b200ba_reproj_errors_dev": (C.c_int, [_P, _P, _P, _P, _D]),
     "b200ba_jacobian_blocks": (C.c_int, [_P, _P, _P, _P]),

@@ -248,6 +248,20 @@ class Engine:
                                                 _ptr(X), _ptr(mask)))
         return (X, mask.astype(bool)) if mask is not None else X
 
+    def triangulate_nonlinear(self, M1, M2, pts1, pts2, max_iter=100):
+        """``cv2_lite.triangulate_points.triangulate_points`` (:122-184) for ``(n, 2)`` point arrays: DLT + per-point
+        refinement of the reference's objective; returns ``X (n, 4)`` rows ``[X Y Z 1]``."""
+        M1 = np.ascontiguousarray(M1, dtype=np.float64)
+        M2 = np.ascontiguousarray(M2, dtype=np.float64)
+        p1 = np.ascontiguousarray(pts1, dtype=np.float64).reshape(-1, 2)
+        p2 = np.ascontiguousarray(pts2, dtype=np.float64).reshape(-1, 2)
+        if M1.shape != (3, 4) or M2.shape != (3, 4) or len(p1) != len(p2):
+            raise ValueError("M1, M2 must be 3x4 and the point arrays of equal length")
+        X = np.empty((len(p1), 4), dtype=np.float64)
+        self._check(self.lib.b200ba_triangulate_nonlinear(self.h, len(p1), _ptr(M1), _ptr(M2), _ptr(p1), _ptr(p2),
+                                                          int(max_iter), _ptr(X)))
+        return X
+
     def normal_equations(self, x, lam, want_S=True):
         x = self._x(x)
         n = 6 * self.n_cam
@@ -477,6 +491,15 @@ def triangulate_points(M1, M2, pts1, pts2, engine=None):
     if p1.ndim != 2 or p1.shape[0] != 2 or p1.shape != p2.shape:
         raise ValueError("pts1, pts2 must be (2, N)")
     return np.ascontiguousarray((engine or _aux_engine()).triangulate(M1, M2, p1.T, p2.T).T)
+
+
+def triangulate_points_nonlinear(M1, M2, pts1, pts2, engine=None, max_iter=100):
+    """Same signature / layout as the reference's ``cv2_lite.triangulate_points.triangulate_points`` (:122-184): ``pts`` are
+    ``(2, N)``, returns ``(4, N)`` with a last row of ones."""
+    p1, p2 = np.asarray(pts1, dtype=np.float64), np.asarray(pts2, dtype=np.float64)
+    if p1.ndim != 2 or p1.shape[0] != 2 or p1.shape != p2.shape:
+        raise ValueError("pts1, pts2 must be (2, N)")
+    return np.ascontiguousarray((engine or _aux_engine()).triangulate_nonlinear(M1, M2, p1.T, p2.T, max_iter).T)
 
 
 def triangulate_visible(K, H1, H2, pts1, pts2, engine=None):

@@ -288,6 +288,8 @@ void launch_pnp(Handle* h, int n_problems, const void* probs_dev, const double* 
                 double* out_dev);
 void launch_triangulate(Handle* h, int64_t n, const double* M1, const double* M2, const double* pts1, const double* pts2,
                         const double* vis1, const double* vis2, double* X_out, unsigned char* mask_out);
+void launch_triangulate_refine(Handle* h, int64_t n, const double* M1, const double* M2, const double* pts1, const double* pts2,
+                               int max_iter, double* X);
 void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out /*nullable, caller order*/);
 void launch_jacobian(Handle* h, const double* x, const double* camprep, double* r_out, double* Jc, double* Jp);
 void launch_xchg_sum(Handle* h);  // sparse exchange: gathered per-rank contributions -> Sup, b, gc, udiag, cost, gpmax

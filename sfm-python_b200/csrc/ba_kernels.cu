@@ -292,6 +292,79 @@ __global__ void k_triangulate(int64_t n, const double* __restrict__ M1, const do
   }
 }
 
+
+// ------------------------------------------------------------------ non-linear triangulation refinement
+// cv2_lite/triangulate_points.py:122-184: from the DLT point, minimise the reference's objective (:94-118) -- its
+// residuals are the SQUARED reprojection errors of the four image coordinates, squared again by the solver, i.e. the sum
+// of 4th powers.  The reference passes all points to one scipy call; the points are independent, so one thread runs a
+// damped Gauss-Newton on its own 3 unknowns (4 residuals r_k = e_k^2, J_k = 2 e_k de_k/dX) to the minimiser.
+__global__ void k_triangulate_refine(int64_t n, const double* __restrict__ M1, const double* __restrict__ M2,
+                                     const double* __restrict__ pts1, const double* __restrict__ pts2, int max_iter,
+                                     double* __restrict__ X /* n x 4, [X Y Z 1] in and out */) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double obs[4] = {pts1[2 * i], pts1[2 * i + 1], pts2[2 * i], pts2[2 * i + 1]};
+  double x[3] = {X[4 * i], X[4 * i + 1], X[4 * i + 2]};
+  if (!(x[0] == x[0]) || !(fabs(x[0]) < 1e300)) return;
+  auto eval = [&](const double* xx, double* r, double (*J)[3]) -> double {
+    double c = 0.0;
+#pragma unroll
+    for (int v = 0; v < 2; ++v) {
+      const double* M = v ? M2 : M1;
+      const double a0 = M[0] * xx[0] + M[1] * xx[1] + M[2] * xx[2] + M[3];
+      const double a1 = M[4] * xx[0] + M[5] * xx[1] + M[6] * xx[2] + M[7];
+      const double a2 = M[8] * xx[0] + M[9] * xx[1] + M[10] * xx[2] + M[11];
+      const double ia = 1.0 / a2, pu = a0 * ia, pv = a1 * ia;
+      const double e0 = pu - obs[2 * v], e1 = pv - obs[2 * v + 1];
+      r[2 * v] = e0 * e0;
+      r[2 * v + 1] = e1 * e1;
+      c += r[2 * v] * r[2 * v] + r[2 * v + 1] * r[2 * v + 1];
+      if (J) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          J[2 * v][k] = 2.0 * e0 * (M[k] - pu * M[8 + k]) * ia;
+          J[2 * v + 1][k] = 2.0 * e1 * (M[4 + k] - pv * M[8 + k]) * ia;
+        }
+      }
+    }
+    return c;
+  };
+  double r[4], J[4][3], lam = 1e-3;
+  double c = eval(x, r, J);
+  for (int it = 0; it < max_iter; ++it) {
+    double H[6] = {0, 0, 0, 0, 0, 0}, g[3] = {0, 0, 0};   // H: 00 10 11 20 21 22
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      H[0] += J[k][0] * J[k][0]; H[1] += J[k][1] * J[k][0]; H[2] += J[k][1] * J[k][1];
+      H[3] += J[k][2] * J[k][0]; H[4] += J[k][2] * J[k][1]; H[5] += J[k][2] * J[k][2];
+      g[0] += J[k][0] * r[k]; g[1] += J[k][1] * r[k]; g[2] += J[k][2] * r[k];
+    }
+    double Li[6];
+    if (!point_factor(H, lam, Li)) { lam *= 4.0; if (lam > 1e12) break; continue; }
+    // dx = -(L L^T)^-1 g = -Linv^T (Linv g)
+    const double z0 = Li[0] * g[0], z1 = Li[1] * g[0] + Li[2] * g[1], z2 = Li[3] * g[0] + Li[4] * g[1] + Li[5] * g[2];
+    const double dx[3] = {-(Li[0] * z0 + Li[1] * z1 + Li[3] * z2), -(Li[2] * z1 + Li[4] * z2), -(Li[5] * z2)};
+    const double xn[3] = {x[0] + dx[0], x[1] + dx[1], x[2] + dx[2]};
+    double rn[4], Jn[4][3];
+    const double cn = eval(xn, rn, Jn);
+    if (cn == cn && cn < c) {
+      const double dn = sqrt(dx[0] * dx[0] + dx[1] * dx[1] + dx[2] * dx[2]);
+      const double xs = sqrt(x[0] * x[0] + x[1] * x[1] + x[2] * x[2]);
+      const bool done = (c - cn) < 1e-16 * c || dn < 1e-14 * xs;
+      x[0] = xn[0]; x[1] = xn[1]; x[2] = xn[2];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { r[k] = rn[k]; J[k][0] = Jn[k][0]; J[k][1] = Jn[k][1]; J[k][2] = Jn[k][2]; }
+      c = cn;
+      lam = fmax(lam / 3.0, 1e-12);
+      if (done) break;
+    } else {
+      lam *= 4.0;
+      if (lam > 1e12) break;
+    }
+  }
+  X[4 * i] = x[0]; X[4 * i + 1] = x[1]; X[4 * i + 2] = x[2];
+}
+
 // ------------------------------------------------------------------ per-observation reprojection error (sfm.py:234-238)
 // The loop of SFM._apply_increment calls calc_reproj_error (sfm.py:38-41) -> reproj_error (cv2_lite/solve_pnp.py:9-14)
 // once per observation: || pi(K (R X + t)) - uv ||, the pipeline's R X + t convention (NOT the R (X - T) of the BA

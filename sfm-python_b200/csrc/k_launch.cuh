@@ -133,6 +133,13 @@ void launch_triangulate(Handle* h, int64_t n, const double* M1, const double* M2
   h->st.launches += 1;
 }
 
+void launch_triangulate_refine(Handle* h, int64_t n, const double* M1, const double* M2, const double* pts1, const double* pts2,
+                               int max_iter, double* X) {
+  if (n <= 0) return;
+  k_triangulate_refine<<<cdiv(n, 128), 128, 0, h->stream>>>(n, M1, M2, pts1, pts2, max_iter, X);
+  h->st.launches += 1;
+}
+
 void launch_reproj_err(Handle* h, const double* Rt, const double* X, double* err_out) {
   const int g = obs_grid(h);
   KernelTimer t(h);

@@ -232,3 +232,19 @@ def test_robust_scaling_matches_scipy(loss):
         assert np.array_equal(jc[keep], js[keep]) and np.abs(rc - r)[keep].max() == 0.0
         g_c = (J * jc[:, None]) * rc[:, None]
         assert np.abs(g_c - g_s).max() <= 1e-12 * np.abs(g_s).max()
+
+
+def test_nonlinear_triangulation_oracle_vs_reference_golden():
+    """The oracle's per-point minimiser of the reference's triangulation objective reaches a value not above the REAL
+    reference function's (tests/golden/ref_triangulate.npz, cv2_lite/triangulate_points.py:122-184) and lands within the
+    reference's own stopping accuracy of its points."""
+    t = load_golden("ref_triangulate.npz")
+    M1, M2 = t["K"] @ t["H1"][:3], t["K"] @ t["H2"][:3]
+    vis = np.flatnonzero(t["mask"])[:120]
+    p1, p2 = t["pts1"][vis], t["pts2"][vis]
+    Xo = O.triangulate_points_nonlinear(M1, M2, p1.T, p2.T)
+    Xr = t["X_ref_nonlinear"][:, :120]
+    co = O.triangulation_objective(M1, M2, p1.T, p2.T, Xo)
+    cr = O.triangulation_objective(M1, M2, p1.T, p2.T, Xr)
+    assert float(co.sum()) <= float(cr.sum()) * (1 + 1e-12)
+    assert np.abs(Xo - Xr).max() <= 1e-2 * np.abs(Xr).max()
