@@ -355,7 +355,7 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
     """Reference LM loop (numpy twin of the engine's b200ba_solve).
 
     Marquardt damping lam*diag(H); accept iff the cost decreases; Nielsen update
-    lam *= max(1/3, 1-(2 rho-1)^3) on accept, lam *= nu, nu *= 2 on reject;
+    lam *= max(1/3, 1-(2 rho-1)^3) on accept (0.1 when rho > 0.9), lam *= nu, nu *= 2 on reject;
     scipy-compatible termination (scipy _lsq/common.py check_termination).
     """
     x = np.array(x0, dtype=np.float64)
@@ -385,7 +385,7 @@ def lm_solve(x0, n_cameras, n_points, camera_indices, point_indices, points_2d, 
             ftol_ok = actual < ftol * cost and rho > 0.25
             xtol_ok = step_norm < xtol * (xtol + float(np.linalg.norm(x)))
             x, cost = x_new, cost_new
-            lam *= max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3)
+            lam *= 0.1 if (rho > 0.9 and loss == "linear") else max(1.0 / 3.0, 1.0 - (2.0 * rho - 1.0) ** 3)   # as csrc/ba_lm.inc
             nu = 2.0
             if ftol_ok and xtol_ok:
                 status = 4
