@@ -318,15 +318,17 @@ __global__ void k_fix_cameras(int n_blk, int C, const int* __restrict__ blk_r, c
   if (t < 6 * (int64_t)C && fixed[t / 6]) { b[t] = 0.0; gc[t] = 0.0; }
 }
 
-// camera-side scalars of the step: g_c.dc, dc^T diag(U) dc, |dc|^2, |x_c|^2, max|g_c|
+// camera-side scalars of the step: g_c.dc, dc^T diag(U) dc, |dc|^2, |x_c|^2, max|g_c|.  Two stages (per-CTA partials over
+// contiguous chunks, then one CTA sums them in CTA order): a single CTA over 60 000 entries took 63 us per LM iteration.
 __global__ void __launch_bounds__(1024)
-k_cam_dots(int n, const double* __restrict__ gc, const double* __restrict__ dc, const double* __restrict__ udiag,
-           const double* __restrict__ xc, double* __restrict__ scal) {
+k_cam_dots(int n, int chunk, const double* __restrict__ gc, const double* __restrict__ dc, const double* __restrict__ udiag,
+           const double* __restrict__ xc, double* __restrict__ part) {
   __shared__ double sm[32 * 5];
   double v[5] = {0, 0, 0, 0, 0};
   double mx = 0.0;
+  const int lo = blockIdx.x * chunk, hi = min(n, lo + chunk);
 #pragma unroll 4
-  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+  for (int i = lo + threadIdx.x; i < hi; i += blockDim.x) {
     const double g = gc[i], d = dc[i], xx = xc[i];
     v[0] += g * d;
     v[1] += d * d * udiag[i];
@@ -341,12 +343,24 @@ k_cam_dots(int n, const double* __restrict__ gc, const double* __restrict__ dc, 
   if (threadIdx.x == 0) {
     double m = 0.0;
     for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmax(m, sm[w]);
-    scal[S_GC_DC] = v[0];
-    scal[S_DC_D_DC] = v[1];
-    scal[S_DC2] = v[2];
-    scal[S_XC2] = v[3];
-    scal[S_GCMAX] = m;
+    double* o = part + 8 * blockIdx.x;
+    o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3]; o[4] = m;
   }
+}
+
+__global__ void k_cam_dots_final(int nparts, const double* __restrict__ part, double* __restrict__ scal) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  double v[4] = {0, 0, 0, 0}, m = 0.0;
+  for (int b = 0; b < nparts; ++b) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) v[k] += part[8 * b + k];
+    m = fmax(m, part[8 * b + 4]);
+  }
+  scal[S_GC_DC] = v[0];
+  scal[S_DC_D_DC] = v[1];
+  scal[S_DC2] = v[2];
+  scal[S_XC2] = v[3];
+  scal[S_GCMAX] = m;
 }
 
 // dense symmetric 6C x 6C copy of the block upper triangle (tests, Cholesky)
