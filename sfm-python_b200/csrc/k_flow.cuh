@@ -17,7 +17,10 @@
 //
 // Outputs are bit-identical to k_lin_fused: every slot partial is produced by one lane group in a fixed order.
 
-constexpr int FLOW_THREADS = 512;
+#ifndef B200BA_FLOW_THREADS
+#define B200BA_FLOW_THREADS 512
+#endif
+constexpr int FLOW_THREADS = B200BA_FLOW_THREADS;
 constexpr int FLOW_WARPS = FLOW_THREADS / 32;
 constexpr int FLOW_SPI = 32 / FG;  // slots per item
 constexpr int FLOW_MAX_WT = 2 * FLOW_TILE / 32 + 4;  // warp tiles per tile: two consecutive ones hold > 32 observations
