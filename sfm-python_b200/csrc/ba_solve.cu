@@ -581,7 +581,8 @@ int launch_cholesky(Handle* h) {
   }
   launch_densify(h, w.dense);
   const char* e_mc = getenv("B200BA_CHOL_MC");   // 1: the multi-CTA DMMA factorisation at every size (tests), 0: never
-  const bool want_mc = e_mc ? atoi(e_mc) != 0 : n > 384;   // measured: the single-CTA panel kernel takes 6 ms at n = 768, this one 1.2 ms
+  const bool want_mc = e_mc ? atoi(e_mc) != 0 : n > 192;   // measured per LM iteration (tools/exp_small_solvers.py): n = 144 single-CTA
+                                                         // 0.29 ms vs 0.35; n = 294 (config B) 0.77 vs 0.51; n = 384 1.23 vs 0.57; n = 768 6 vs 1.2
   if (!want_mc && n <= CHB_MAX_N) {
     static bool attr_dev[MAX_DEVICES] = {};
     bool& attr = attr_dev[h->device % MAX_DEVICES];
