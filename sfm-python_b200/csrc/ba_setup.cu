@@ -885,9 +885,17 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       keys_host.insert(keys_host.end(), all.begin() + (size_t)r * mx, all.begin() + (size_t)r * mx + counts[r]);
     if (x_ok) { x_all.swap(all); x_counts = counts; x_mx = mx; }
   }
-  for (int64_t c = 0; c < C; ++c) keys_host.push_back((long long)c * C + c);
-  std::sort(keys_host.begin(), keys_host.end());
-  keys_host.erase(std::unique(keys_host.begin(), keys_host.end()), keys_host.end());
+  {
+    // union with every diagonal block.  One rank: the local list is already sorted (device run-length encode) and so
+    // are the diagonal keys -> a linear merge instead of a 170 k-element sort (2.5 ms at config D)
+    std::vector<long long> diag((size_t)C);
+    for (int64_t c = 0; c < C; ++c) diag[(size_t)c] = (long long)c * C + c;
+    if (h->nranks > 1 || !std::is_sorted(keys_host.begin(), keys_host.end())) std::sort(keys_host.begin(), keys_host.end());
+    std::vector<long long> merged(keys_host.size() + diag.size());
+    std::merge(keys_host.begin(), keys_host.end(), diag.begin(), diag.end(), merged.begin());
+    merged.erase(std::unique(merged.begin(), merged.end()), merged.end());
+    keys_host.swap(merged);
+  }
   const int n_blk = (int)keys_host.size();
   pb.n_blk = n_blk;
   if (x_ok) {
