@@ -232,6 +232,10 @@ struct Handle {
   void* comm = nullptr;
   int rank = 0, nranks = 1;
   bool in_process = false;         // all ranks are handles of one process (b200ba_create_multi)
+  // page-locked staging for the small host-built arrays of set_problem: copies from it are truly asynchronous, so the
+  // per-array stream syncs of pageable uploads disappear (16+ per set_problem); reset at the end of setup_problem
+  char* stage = nullptr;
+  size_t stage_bytes = 0, stage_off = 0;
   bool direct_push = false;        // this linearisation's slot reduction stored its blocks straight into the peers' slots
   int64_t n_obs_global = 0;
   P2P p2p;

@@ -393,8 +393,16 @@ int upload(Handle* h, T** dst, const std::vector<T>& src) {
   size_t n = std::max<size_t>(src.size(), 1);
   *dst = (T*)dalloc(h, n * sizeof(T));
   if (!*dst) return B200BA_OOM;
-  if (!src.empty())
-    BA_CUDA(h, cudaMemcpyAsync(*dst, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+  if (src.empty()) return 0;
+  const size_t bytes = src.size() * sizeof(T), pad = (bytes + 255) & ~(size_t)255;
+  if (h->stage && h->stage_off + pad <= h->stage_bytes) {
+    // through the page-locked staging area: no stream sync, src may die at once
+    memcpy(h->stage + h->stage_off, src.data(), bytes);
+    BA_CUDA(h, cudaMemcpyAsync(*dst, h->stage + h->stage_off, bytes, cudaMemcpyHostToDevice, h->stream));
+    h->stage_off += pad;
+    return 0;
+  }
+  BA_CUDA(h, cudaMemcpyAsync(*dst, src.data(), bytes, cudaMemcpyHostToDevice, h->stream));
   BA_CUDA(h, cudaStreamSynchronize(h->stream));  // src may be a temporary
   return 0;
 }
@@ -604,6 +612,8 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   cudaStream_t st = h->stream;
   pb = Problem();
   pb.C = C; pb.P = P; pb.N = N;
+  cudaStreamSynchronize(st);   // nothing of an earlier call still reads the staging area
+  h->stage_off = 0;
   pb.Cs = (C + 1) & ~(int64_t)1;
   for (int i = 0; i < 9; ++i) pb.K.k[i] = K[i];
   Tmp tmp(h);

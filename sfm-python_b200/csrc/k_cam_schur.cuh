@@ -322,7 +322,7 @@ __global__ void k_fix_cameras(int n_blk, int C, const int* __restrict__ blk_r, c
 // contiguous chunks, then one CTA sums them in CTA order): a single CTA over 60 000 entries took 63 us per LM iteration.
 __global__ void __launch_bounds__(1024)
 k_cam_dots(int n, int chunk, const double* __restrict__ gc, const double* __restrict__ dc, const double* __restrict__ udiag,
-           const double* __restrict__ xc, double* __restrict__ part) {
+           const double* __restrict__ xc, double* __restrict__ part, double* __restrict__ scal) {
   __shared__ double sm[32 * 5];
   double v[5] = {0, 0, 0, 0, 0};
   double mx = 0.0;
@@ -343,8 +343,12 @@ k_cam_dots(int n, int chunk, const double* __restrict__ gc, const double* __rest
   if (threadIdx.x == 0) {
     double m = 0.0;
     for (int w = 0; w < (blockDim.x >> 5); ++w) m = fmax(m, sm[w]);
-    double* o = part + 8 * blockIdx.x;
-    o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3]; o[4] = m;
+    if (gridDim.x == 1) {   // small problems: one CTA, results straight into the scalar block (one launch less)
+      scal[S_GC_DC] = v[0]; scal[S_DC_D_DC] = v[1]; scal[S_DC2] = v[2]; scal[S_XC2] = v[3]; scal[S_GCMAX] = m;
+    } else {
+      double* o = part + 8 * blockIdx.x;
+      o[0] = v[0]; o[1] = v[1]; o[2] = v[2]; o[3] = v[3]; o[4] = m;
+    }
   }
 }
 

@@ -313,9 +313,9 @@ void launch_cam_dots(Handle* h) {
   const int n = (int)(6 * h->pb.C);
   const int nparts = std::max(1, std::min(std::min(w.n_part, 64), (n + 1023) / 1024));
   const int chunk = (n + nparts - 1) / nparts;
-  k_cam_dots<<<nparts, 1024, 0, h->stream>>>(n, chunk, w.gc, w.dc, w.udiag, w.x, w.part);
-  k_cam_dots_final<<<1, 32, 0, h->stream>>>(nparts, w.part, w.scal);
-  h->st.launches += 2;
+  k_cam_dots<<<nparts, 1024, 0, h->stream>>>(n, chunk, w.gc, w.dc, w.udiag, w.x, w.part, w.scal);
+  if (nparts > 1) k_cam_dots_final<<<1, 32, 0, h->stream>>>(nparts, w.part, w.scal);
+  h->st.launches += nparts > 1 ? 2 : 1;
 }
 
 void launch_densify(Handle* h, double* dense) {
