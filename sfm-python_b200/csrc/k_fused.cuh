@@ -308,6 +308,9 @@ k_lin_fused(Problem pb, const double* __restrict__ x, const double* __restrict__
 
 // Fixed-order sum of a list of strided partials with 8 independent chains (the loads of a round are in flight
 // together; the order of the additions is fixed, so the result is bit-reproducible).
+#ifndef REDUCE_LDCS
+#define REDUCE_LDCS 0
+#endif
 __device__ __forceinline__ double list_sum8(const int* __restrict__ list, int a, int b, const double* __restrict__ base,
                                             int stride, int e) {
   double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -317,7 +320,7 @@ __device__ __forceinline__ double list_sum8(const int* __restrict__ list, int a,
     for (int u = 0; u < 8; ++u) id[u] = (q + u < b) ? list[q + u] : -1;
 #pragma unroll
     for (int u = 0; u < 8; ++u)
-      if (id[u] >= 0) s[u] += base[(int64_t)id[u] * stride + e];
+      if (id[u] >= 0) s[u] += REDUCE_LDCS ? __ldcs(base + (int64_t)id[u] * stride + e) : base[(int64_t)id[u] * stride + e];
   }
   return ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
 }

@@ -56,6 +56,9 @@ __global__ void __launch_bounds__(256) k_fp64_peak(int iters, double seed, doubl
 
 }  // namespace
 
+#ifndef REDUCE_T
+#define REDUCE_T 128
+#endif
 static inline int point_grid(const Handle* h) {
   return (int)std::min<int64_t>(cdiv(h->pb.n_wt, LIN_WARPS), (int64_t)h->sm_count * 16);
 }
@@ -212,11 +215,11 @@ void launch_linearize(Handle* h, const double* x, double lambda) {
       const char* e_dp = getenv("B200BA_DIRECT_PUSH");   // 0: stage in xsend and copy afterwards (A/B)
       PeerDst dst = (e_dp && atoi(e_dp) == 0) ? PeerDst{} : p2p_next_dst(h);
       h->direct_push = dst.n > 0;
-      k_slot_reduce_S<<<cdiv((int64_t)pb.xl_n * 36, 128), 128, 0, st>>>(pb.xl_n, pb.xl_blk, pb.blk_r, pb.blk_c,
+      k_slot_reduce_S<<<cdiv((int64_t)pb.xl_n * 36, REDUCE_T), REDUCE_T, 0, st>>>(pb.xl_n, pb.xl_blk, pb.blk_r, pb.blk_c,
                                                                         pb.blk_slot_off, pb.blk_slots, w.spart, w.camsum,
                                                                         lambda, w.xsend, dst);
     } else {
-      k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, 128), 128, 0, st>>>(pb.n_blk, nullptr, pb.blk_r, pb.blk_c,
+      k_slot_reduce_S<<<cdiv((int64_t)pb.n_blk * 36, REDUCE_T), REDUCE_T, 0, st>>>(pb.n_blk, nullptr, pb.blk_r, pb.blk_c,
                                                                          pb.blk_slot_off, pb.blk_slots, w.spart, w.camsum,
                                                                          lambda, w.Sup, PeerDst{});
     }
