@@ -20,8 +20,15 @@ constexpr int FUSED_REC_BYTES = 176;  // per-observation record of k_lin_fused (
 constexpr int FUSED_TILE_2CTA = 640;  // 640 * 176 B = 110 KB: two CTAs of 256 threads per SM
 constexpr int FUSED_TILE_1CTA = 1312; // 1312 * 176 B = 225.5 KB: one CTA of 512 threads per SM
 // dataflow kernel (k_lin_flow): one persistent CTA of 512 threads per SM, two record buffers, bulk-copy staging
-constexpr int FLOW_TILE = 512;        // observations per tile: 2 * 512 * 176 B = 176 KB of records
-constexpr int FLOW_CAM_SPAN = 64;     // staged camera window per tile (21 x 64 doubles)
+#ifndef B200BA_FLOW_TILE
+#define B200BA_FLOW_TILE 544
+#endif
+#ifndef B200BA_FLOW_CAM_SPAN
+#define B200BA_FLOW_CAM_SPAN 32
+#endif
+constexpr int FLOW_TILE = B200BA_FLOW_TILE;        // observations per tile: 2 * 544 * 176 B = 187 KB of records (measured: 448 -> 512 -> 544
+                                                   // observations = 2.67 -> 2.43 -> 2.35 ms at config D; 544 is what fits 227 KB)
+constexpr int FLOW_CAM_SPAN = B200BA_FLOW_CAM_SPAN;     // staged camera window per tile (21 x 32 doubles; wider tiles read the table from global memory)
 constexpr int FLOW_META_CAP = 8192;   // staged tile metadata (slot descriptors + entries), bytes
 constexpr int FLOW_IDX_BYTES = (FLOW_TILE + 8) * 4;  // staged cam[] / pt[] window incl. alignment slack
 constexpr int NSCAL = 32;          // device scalar slots
