@@ -4,6 +4,7 @@
 // and the Schur pair-entry list sorted by reduced-camera-system block (atomics-free accumulation).
 // One-off per problem; CUB sort/scan/run-length are used here (not on the per-iteration path).
 #include <chrono>
+#include <thread>
 #include <algorithm>
 #include <cub/cub.cuh>
 
@@ -864,10 +865,14 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       if (N > 0) k_cam_seen<<<nblk(N, T), T, 0, st>>>(N, pb.cam, d_seen);
       BA_CUDA(h, cudaMemcpyAsync(h_seen.data(), d_seen, (C + 1) * sizeof(int), cudaMemcpyDeviceToHost, st));
       BA_CUDA(h, cudaStreamSynchronize(st));
+      // both lists are ascending (radix-sorted unique keys; camera order): a linear merge, not a sort
+      std::vector<long long> dg, mg;
       for (int64_t c = 0; c < C; ++c)
-        if (h_seen[c]) keys_host.push_back((long long)c * C + c);
-      std::sort(keys_host.begin(), keys_host.end());
-      keys_host.erase(std::unique(keys_host.begin(), keys_host.end()), keys_host.end());
+        if (h_seen[c]) dg.push_back((long long)c * C + c);
+      mg.resize(keys_host.size() + dg.size());
+      std::merge(keys_host.begin(), keys_host.end(), dg.begin(), dg.end(), mg.begin());
+      mg.erase(std::unique(mg.begin(), mg.end()), mg.end());
+      keys_host.swap(mg);
     }
     long long my_n[2] = {(long long)keys_host.size(), want_x ? 1 : 0};
     TMP_ALLOC(d_n, long long, 2 * (h->nranks + 1));
@@ -890,17 +895,26 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     std::vector<long long> all((size_t)mx * h->nranks);
     BA_CUDA(h, cudaMemcpyAsync(all.data(), d_recv, all.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
     BA_CUDA(h, cudaStreamSynchronize(st));
+    // every rank's list is ascending: merge them one after the other (duplicates are removed with the diagonal below)
     keys_host.clear();
-    for (int r = 0; r < h->nranks; ++r)
-      keys_host.insert(keys_host.end(), all.begin() + (size_t)r * mx, all.begin() + (size_t)r * mx + counts[r]);
+    {
+      std::vector<long long> tmp;
+      for (int r = 0; r < h->nranks; ++r) {
+        const long long* a0 = all.data() + (size_t)r * mx;
+        tmp.resize(keys_host.size() + (size_t)counts[r]);
+        std::merge(keys_host.begin(), keys_host.end(), a0, a0 + counts[r], tmp.begin());
+        keys_host.swap(tmp);
+      }
+    }
     if (x_ok) { x_all.swap(all); x_counts = counts; x_mx = mx; }
+    mark("6a gather block keys");
   }
   {
     // union with every diagonal block.  One rank: the local list is already sorted (device run-length encode) and so
     // are the diagonal keys -> a linear merge instead of a 170 k-element sort (2.5 ms at config D)
     std::vector<long long> diag((size_t)C);
     for (int64_t c = 0; c < C; ++c) diag[(size_t)c] = (long long)c * C + c;
-    if (h->nranks > 1 || !std::is_sorted(keys_host.begin(), keys_host.end())) std::sort(keys_host.begin(), keys_host.end());
+    if (!std::is_sorted(keys_host.begin(), keys_host.end())) std::sort(keys_host.begin(), keys_host.end());
     std::vector<long long> merged(keys_host.size() + diag.size());
     std::merge(keys_host.begin(), keys_host.end(), diag.begin(), diag.end(), merged.begin());
     merged.erase(std::unique(merged.begin(), merged.end()), merged.end());
@@ -908,6 +922,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
   const int n_blk = (int)keys_host.size();
   pb.n_blk = n_blk;
+  mark("6b union of keys");
   if (x_ok) {
     // worth it when the gathered buffer (nranks x the largest local list) is smaller than what an all-reduce moves
     // (about twice the union); the decision depends only on gathered counts, so every rank takes the same one
@@ -918,9 +933,10 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       std::vector<std::vector<int>> idx(h->nranks);
       for (int r = 0; r < h->nranks; ++r) {
         idx[r].resize(x_counts[r]);
+        int g = 0;   // the rank's keys ascend and are all in the union: one forward walk instead of a search per key
         for (long long k = 0; k < x_counts[r]; ++k) {
-          const int g = (int)(std::lower_bound(keys_host.begin(), keys_host.end(), x_all[(size_t)r * x_mx + k]) -
-                              keys_host.begin());
+          const long long key = x_all[(size_t)r * x_mx + k];
+          while (g + 1 < n_blk && keys_host[g] < key) ++g;
           idx[r][k] = g;
           xoff[g + 1]++;
         }
@@ -938,6 +954,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       if (int rc = upload(h, &pb.xc_src, xsrc)) return rc;
       pb.xchg = true;
     }
+    mark("6c exchange lists");
   }
 
   // entry range of every global block in the local sorted entry list (stream mode only)
@@ -953,13 +970,30 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
 
   mark("6 block structure");
-  // ---- 7. host: block coordinates, Schur chunks, full BSR view
-  {
-    std::vector<int> br(n_blk), bc(n_blk), diag(C, -1), sb, sa, se, choff(n_blk + 1, 0);
+  // ---- 7. host: block coordinates, Schur chunks, full BSR view, camera aggregates of the two-level preconditioner.
+  // Pure host work on the gathered keys (about 5 ms at config D): it runs on a worker thread while this thread drives
+  // the device through steps 8 - 10, which only need the keys already uploaded in step 6; the results are uploaded
+  // after the join (step 10b).
+  struct HostBsr {
+    std::vector<int> br, bc, diag, sb, sa, se, choff, rowptr, col, src;
+    std::vector<int> cam_agg, agg_off, agg_cams, sp_rowptr, sp_col, sp_of;
+    int n_agg = 0;
+    bool tl = false;
+  } hb;
+  const char* e_tl = getenv("B200BA_TWOLEVEL");   // 0: block-Jacobi only
+  const char* e_agg = getenv("B200BA_AGG");       // cameras per aggregate (default max(16, C / 320))
+  const bool want_tl = C >= 128 && !(e_tl && atoi(e_tl) == 0);
+  const int agg_env = (e_agg && atoi(e_agg) >= 2) ? atoi(e_agg) : 0;
+  auto host_bsr = [&hb, &keys_host, &h_blk_off, n_blk, C, want_tl, agg_env]() {
+    std::vector<int>&br = hb.br, &bc = hb.bc, &diag = hb.diag, &sb = hb.sb, &sa = hb.sa, &se = hb.se, &choff = hb.choff;
+    std::vector<int>&rowptr = hb.rowptr, &col = hb.col, &src = hb.src;
+    br.resize(n_blk); bc.resize(n_blk); diag.assign(C, -1); choff.assign(n_blk + 1, 0);
     std::vector<int> rowcnt(C + 1, 0);
+    long long row = 0;   // keys ascend: follow the row instead of a 64-bit division per block
     for (int g = 0; g < n_blk; ++g) {
-      br[g] = (int)(keys_host[g] / C);
-      bc[g] = (int)(keys_host[g] % C);
+      while (keys_host[g] >= (row + 1) * (long long)C) ++row;
+      br[g] = (int)row;
+      bc[g] = (int)(keys_host[g] - row * (long long)C);
       if (br[g] == bc[g]) { diag[br[g]] = g; rowcnt[br[g]]++; }
       else { rowcnt[br[g]]++; rowcnt[bc[g]]++; }
       choff[g] = (int)sb.size();
@@ -968,11 +1002,11 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
       }
     }
     choff[n_blk] = (int)sb.size();
-    pb.n_sch = (int)sb.size();
-    std::vector<int> rowptr(C + 1, 0);
+    rowptr.assign(C + 1, 0);
     for (int64_t c = 0; c < C; ++c) rowptr[c + 1] = rowptr[c] + rowcnt[c];
-    pb.nnzb = rowptr[C];
-    std::vector<int> col(pb.nnzb), src(pb.nnzb), fill(rowptr.begin(), rowptr.end() - 1);
+    const int nnzb = rowptr[C];
+    col.resize(nnzb); src.resize(nnzb);
+    std::vector<int> fill(rowptr.begin(), rowptr.end() - 1);
     // keys are sorted by (r,c): pushing the direct block into row r and the transposed one into row c keeps
     // every row's columns ascending (transposed entries of row c come from r < c, direct ones from c' >= c)
     for (int pass = 0; pass < 2; ++pass)
@@ -980,126 +1014,133 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
         if (pass == 0 && br[g] != bc[g]) { int q = fill[bc[g]]++; col[q] = br[g]; src[q] = g | (int)0x80000000; }
         if (pass == 1) { int q = fill[br[g]]++; col[q] = bc[g]; src[q] = g; }
       }
-    if (int rc = upload(h, &pb.blk_r, br)) return rc;
-    if (int rc = upload(h, &pb.blk_c, bc)) return rc;
-    if (int rc = upload(h, &pb.diag_blk, diag)) return rc;
-    if (int rc = upload(h, &pb.sch_blk, sb)) return rc;
-    if (int rc = upload(h, &pb.sch_a, sa)) return rc;
-    if (int rc = upload(h, &pb.sch_b, se)) return rc;
-    if (int rc = upload(h, &pb.blk_choff, choff)) return rc;
-    if (int rc = upload(h, &pb.bsr_rowptr, rowptr)) return rc;
-    if (int rc = upload(h, &pb.bsr_col, col)) return rc;
-    if (int rc = upload(h, &pb.bsr_src, src)) return rc;
     // two-level preconditioner (k_twolevel.cuh): camera aggregates and the block structure of S P
-    const char* e_tl = getenv("B200BA_TWOLEVEL");   // 0: block-Jacobi only
-    const char* e_agg = getenv("B200BA_AGG");       // cameras per aggregate (default max(16, C / 320))
-    if (C >= 128 && !(e_tl && atoi(e_tl) == 0)) {
-      int per = (int)std::max<int64_t>(16, (C + 319) / 320);
-      if (e_agg && atoi(e_agg) >= 2) per = atoi(e_agg);
-      int n_agg = (int)((C + per - 1) / per);
-      if (n_agg > 1 && C - (int64_t)(n_agg - 1) * per < 2) --n_agg;   // a one-camera aggregate has only 6 free motions
-      if ((int64_t)n_agg * 7 <= 3584) {
-        // Aggregates = connected groups of about `per` cameras of the graph of S (block (i, j) present <=> the two cameras
-        // share a point), grown greedily from the lowest unassigned camera by strongest connection to the group.  On
-        // an ordered sequence this gives index runs; on an arbitrary camera numbering (incremental SfM registers cameras
-        // in match order) it still groups cameras that see the same points, which is what makes a locally rigid motion
-        // cheap.  Groups smaller than half the target are merged into the neighbouring aggregate they touch most.
-        std::vector<int> cam_agg(C, -1);
-        std::vector<int> agg_size;
-        {
-          // greedy growth: repeatedly add the unassigned camera with the most blocks of S into the aggregate so far
-          // (ties: lowest index) -- on a sequence this walks outwards from the seed, whatever the numbering
-          std::vector<int> score(C, 0), cand;
-          for (int64_t seed = 0; seed < C; ++seed) {
-            if (cam_agg[seed] >= 0) continue;
-            const int I = (int)agg_size.size();
-            cand.clear();
-            int size = 0, next = (int)seed;
-            while (next >= 0) {
-              cam_agg[next] = I;
-              ++size;
-              for (int q = rowptr[next]; q < rowptr[next + 1]; ++q) {
-                const int j = col[q];
-                if (cam_agg[j] >= 0) continue;
-                if (score[j]++ == 0) cand.push_back(j);
-              }
-              next = -1;
-              if (size >= per) break;
-              int best = -1;
-              for (size_t k = 0; k < cand.size(); ++k) {
-                const int j = cand[k];
-                if (cam_agg[j] >= 0) continue;
-                if (best < 0 || score[j] > score[best] || (score[j] == score[best] && j < best)) best = j;
-              }
-              next = best;
-            }
-            for (int j : cand) score[j] = 0;
-            agg_size.push_back(size);
+    if (!want_tl) return;
+    int per = (int)std::max<int64_t>(16, (C + 319) / 320);
+    if (agg_env) per = agg_env;
+    int n_agg = (int)((C + per - 1) / per);
+    if (n_agg > 1 && C - (int64_t)(n_agg - 1) * per < 2) --n_agg;   // a one-camera aggregate has only 6 free motions
+    if ((int64_t)n_agg * 7 > 3584) return;
+    // Aggregates = connected groups of about `per` cameras of the graph of S (block (i, j) present <=> the two cameras
+    // share a point), grown greedily from the lowest unassigned camera by strongest connection to the group.  On
+    // an ordered sequence this gives index runs; on an arbitrary camera numbering (incremental SfM registers cameras
+    // in match order) it still groups cameras that see the same points, which is what makes a locally rigid motion
+    // cheap.  Groups smaller than half the target are merged into the neighbouring aggregate they touch most.
+    std::vector<int>& cam_agg = hb.cam_agg;
+    cam_agg.assign(C, -1);
+    std::vector<int> agg_size;
+    {
+      // greedy growth: repeatedly add the unassigned camera with the most blocks of S into the aggregate so far
+      // (ties: lowest index) -- on a sequence this walks outwards from the seed, whatever the numbering
+      std::vector<int> score(C, 0), cand;
+      for (int64_t seed = 0; seed < C; ++seed) {
+        if (cam_agg[seed] >= 0) continue;
+        const int I = (int)agg_size.size();
+        cand.clear();
+        int size = 0, next = (int)seed;
+        while (next >= 0) {
+          cam_agg[next] = I;
+          ++size;
+          for (int q = rowptr[next]; q < rowptr[next + 1]; ++q) {
+            const int j = col[q];
+            if (cam_agg[j] >= 0) continue;
+            if (score[j]++ == 0) cand.push_back(j);
           }
-          // merge fragments (a one-camera aggregate has only 6 free motions for 7 coarse unknowns)
-          const int n0 = (int)agg_size.size();
-          std::vector<int> target(n0);
-          for (int I = 0; I < n0; ++I) target[I] = I;
-          if (n0 > 1) {
-            std::vector<int> votes(n0);
-            for (int I = 0; I < n0; ++I) {
-              if (agg_size[I] * 2 >= per) continue;
-              std::fill(votes.begin(), votes.end(), 0);
-              for (int64_t c = 0; c < C; ++c)
-                if (cam_agg[c] == I)
-                  for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) {
-                    int J = cam_agg[col[q]];
-                    while (target[J] != J) J = target[J];
-                    if (J != I) votes[J]++;
-                  }
-              int best = -1;
-              for (int J = 0; J < n0; ++J) if (votes[J] > 0 && (best < 0 || votes[J] > votes[best])) best = J;
-              if (best < 0 && agg_size[I] < 2) best = (I > 0) ? I - 1 : 1;   // isolated camera: any partner
-              if (best >= 0) {
-                while (target[best] != best) best = target[best];
-                if (best != I) { target[I] = best; agg_size[best] += agg_size[I]; agg_size[I] = 0; }
-              }
+          next = -1;
+          if (size >= per) break;
+          int best = -1;
+          for (size_t k = 0; k < cand.size(); ++k) {
+            const int j = cand[k];
+            if (cam_agg[j] >= 0) continue;
+            if (best < 0 || score[j] > score[best] || (score[j] == score[best] && j < best)) best = j;
+          }
+          next = best;
+        }
+        for (int j : cand) score[j] = 0;
+        agg_size.push_back(size);
+      }
+      // merge fragments (a one-camera aggregate has only 6 free motions for 7 coarse unknowns)
+      const int n0 = (int)agg_size.size();
+      std::vector<int> target(n0);
+      for (int I = 0; I < n0; ++I) target[I] = I;
+      if (n0 > 1) {
+        // cameras of every first-pass aggregate (counting sort), so that a fragment only walks its own cameras and
+        // the aggregates it touches: linear in the fragments' blocks, not fragments x cameras
+        std::vector<int> aoff(n0 + 1, 0), acam(C), touched;
+        for (int64_t c = 0; c < C; ++c) aoff[cam_agg[c] + 1]++;
+        for (int I = 0; I < n0; ++I) aoff[I + 1] += aoff[I];
+        {
+          std::vector<int> afill(aoff.begin(), aoff.end() - 1);
+          for (int64_t c = 0; c < C; ++c) acam[afill[cam_agg[c]]++] = (int)c;
+        }
+        std::vector<int> votes(n0, 0);
+        for (int I = 0; I < n0; ++I) {
+          if (agg_size[I] * 2 >= per) continue;
+          touched.clear();
+          for (int kc = aoff[I]; kc < aoff[I + 1]; ++kc) {
+            const int c = acam[kc];
+            for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) {
+              int J = cam_agg[col[q]];
+              while (target[J] != J) J = target[J];
+              if (J != I && votes[J]++ == 0) touched.push_back(J);
             }
           }
-          std::vector<int> renum(n0, -1);
-          int n_new = 0;
-          for (int I = 0; I < n0; ++I) { int J = I; while (target[J] != J) J = target[J]; if (renum[J] < 0) renum[J] = n_new++; }
-          for (int64_t c = 0; c < C; ++c) { int J = cam_agg[c]; while (target[J] != J) J = target[J]; cam_agg[c] = renum[J]; }
-          n_agg = n_new;
-        }
-        if ((int64_t)n_agg * 7 <= 3584) {
-        std::vector<int> agg_off(n_agg + 1, 0), agg_cams(C), sp_rowptr(C + 1, 0), sp_col, sp_of(pb.nnzb);
-        for (int64_t c = 0; c < C; ++c) agg_off[cam_agg[c] + 1]++;
-        for (int I = 0; I < n_agg; ++I) agg_off[I + 1] += agg_off[I];
-        {
-          std::vector<int> fill(agg_off.begin(), agg_off.end() - 1);
-          for (int64_t c = 0; c < C; ++c) agg_cams[fill[cam_agg[c]]++] = (int)c;   // ascending camera index inside an aggregate
-        }
-        std::vector<int> rowJ;
-        for (int64_t c = 0; c < C; ++c) {
-          rowJ.clear();
-          for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) rowJ.push_back(cam_agg[col[q]]);
-          std::sort(rowJ.begin(), rowJ.end());
-          rowJ.erase(std::unique(rowJ.begin(), rowJ.end()), rowJ.end());
-          const int base = (int)sp_col.size();
-          for (int q = rowptr[c]; q < rowptr[c + 1]; ++q)
-            sp_of[q] = base + (int)(std::lower_bound(rowJ.begin(), rowJ.end(), cam_agg[col[q]]) - rowJ.begin());
-          sp_col.insert(sp_col.end(), rowJ.begin(), rowJ.end());
-          sp_rowptr[c + 1] = (int)sp_col.size();
-        }
-        pb.n_agg = n_agg; pb.nc = 7 * n_agg; pb.ncp = (pb.nc + 63) / 64 * 64; pb.nnz_sp = (int)sp_col.size();
-        if (int rc = upload(h, &pb.cam_agg, cam_agg)) return rc;
-        if (int rc = upload(h, &pb.agg_off, agg_off)) return rc;
-        if (int rc = upload(h, &pb.agg_cams, agg_cams)) return rc;
-        if (int rc = upload(h, &pb.sp_rowptr, sp_rowptr)) return rc;
-        if (int rc = upload(h, &pb.sp_col, sp_col)) return rc;
-        if (int rc = upload(h, &pb.sp_of, sp_of)) return rc;
-        pb.tl = true;
+          int best = -1;   // most votes, ties to the lowest aggregate index (as a scan over all aggregates would pick)
+          for (int J : touched) if (best < 0 || votes[J] > votes[best] || (votes[J] == votes[best] && J < best)) best = J;
+          for (int J : touched) votes[J] = 0;
+          if (best < 0 && agg_size[I] < 2) best = (I > 0) ? I - 1 : 1;   // isolated camera: any partner
+          if (best >= 0) {
+            while (target[best] != best) best = target[best];
+            if (best != I) { target[I] = best; agg_size[best] += agg_size[I]; agg_size[I] = 0; }
+          }
         }
       }
+      std::vector<int> renum(n0, -1);
+      int n_new = 0;
+      for (int I = 0; I < n0; ++I) { int J = I; while (target[J] != J) J = target[J]; if (renum[J] < 0) renum[J] = n_new++; }
+      for (int64_t c = 0; c < C; ++c) { int J = cam_agg[c]; while (target[J] != J) J = target[J]; cam_agg[c] = renum[J]; }
+      n_agg = n_new;
     }
-  }
-  mark("7 host BSR");
+    if ((int64_t)n_agg * 7 > 3584) return;
+    std::vector<int>&agg_off = hb.agg_off, &agg_cams = hb.agg_cams, &sp_rowptr = hb.sp_rowptr, &sp_col = hb.sp_col, &sp_of = hb.sp_of;
+    agg_off.assign(n_agg + 1, 0); agg_cams.resize(C); sp_rowptr.assign(C + 1, 0); sp_of.resize(nnzb);
+    for (int64_t c = 0; c < C; ++c) agg_off[cam_agg[c] + 1]++;
+    for (int I = 0; I < n_agg; ++I) agg_off[I + 1] += agg_off[I];
+    {
+      std::vector<int> afill(agg_off.begin(), agg_off.end() - 1);
+      for (int64_t c = 0; c < C; ++c) agg_cams[afill[cam_agg[c]]++] = (int)c;   // ascending camera index inside an aggregate
+    }
+    // row c of S P: the distinct aggregates of the row's cameras in ascending order.  A row touches a handful of
+    // aggregates: they are collected through a marker array and insertion-sorted (no sort of the whole row, no search)
+    std::vector<int> pos(n_agg, -1), rowJ;
+    sp_col.reserve((size_t)C * 4);
+    for (int64_t c = 0; c < C; ++c) {
+      rowJ.clear();
+      for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) {
+        const int J = cam_agg[col[q]];
+        if (pos[J] < 0) {
+          pos[J] = 0;
+          size_t k = rowJ.size();
+          rowJ.push_back(J);
+          while (k > 0 && rowJ[k - 1] > J) { rowJ[k] = rowJ[k - 1]; --k; }
+          rowJ[k] = J;
+        }
+      }
+      const int base = (int)sp_col.size();
+      for (size_t k = 0; k < rowJ.size(); ++k) pos[rowJ[k]] = base + (int)k;
+      for (int q = rowptr[c]; q < rowptr[c + 1]; ++q) sp_of[q] = pos[cam_agg[col[q]]];
+      for (int J : rowJ) pos[J] = -1;
+      sp_col.insert(sp_col.end(), rowJ.begin(), rowJ.end());
+      sp_rowptr[c + 1] = (int)sp_col.size();
+    }
+    hb.n_agg = n_agg;
+    hb.tl = true;
+  };
+  struct Joiner {   // an early return must not destroy a running thread
+    std::thread t;
+    ~Joiner() { if (t.joinable()) t.join(); }
+  } worker;
+  worker.t = std::thread(host_bsr);
   // ---- 8. tile mode: pair slots = (tile, block) cells ordered inside each tile by decreasing entry count,
   //         per-block reduce lists, entries packed to tile-local 16-bit indices
   if (pb.schur_tiles) {
@@ -1181,6 +1222,32 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     }
   }
   mark("10 dataflow blobs");
+  // ---- 10b. results of the host worker (step 7)
+  worker.t.join();
+  mark("7 host BSR (wait for the worker)");
+  pb.n_sch = (int)hb.sb.size();
+  pb.nnzb = (int)hb.col.size();
+  if (int rc = upload(h, &pb.blk_r, hb.br)) return rc;
+  if (int rc = upload(h, &pb.blk_c, hb.bc)) return rc;
+  if (int rc = upload(h, &pb.diag_blk, hb.diag)) return rc;
+  if (int rc = upload(h, &pb.sch_blk, hb.sb)) return rc;
+  if (int rc = upload(h, &pb.sch_a, hb.sa)) return rc;
+  if (int rc = upload(h, &pb.sch_b, hb.se)) return rc;
+  if (int rc = upload(h, &pb.blk_choff, hb.choff)) return rc;
+  if (int rc = upload(h, &pb.bsr_rowptr, hb.rowptr)) return rc;
+  if (int rc = upload(h, &pb.bsr_col, hb.col)) return rc;
+  if (int rc = upload(h, &pb.bsr_src, hb.src)) return rc;
+  if (hb.tl) {
+    pb.n_agg = hb.n_agg; pb.nc = 7 * hb.n_agg; pb.ncp = (pb.nc + 63) / 64 * 64; pb.nnz_sp = (int)hb.sp_col.size();
+    if (int rc = upload(h, &pb.cam_agg, hb.cam_agg)) return rc;
+    if (int rc = upload(h, &pb.agg_off, hb.agg_off)) return rc;
+    if (int rc = upload(h, &pb.agg_cams, hb.agg_cams)) return rc;
+    if (int rc = upload(h, &pb.sp_rowptr, hb.sp_rowptr)) return rc;
+    if (int rc = upload(h, &pb.sp_col, hb.sp_col)) return rc;
+    if (int rc = upload(h, &pb.sp_of, hb.sp_of)) return rc;
+    pb.tl = true;
+  }
+  mark("10b BSR uploads");
   if (N > 0) {
     BA_CUDA(h, cudaStreamWaitEvent(st, h->ev_b, 0));
     k_gather_uv<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_uv, pb.u, pb.v);

@@ -19,9 +19,18 @@ import b200ba  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="D")
 ap.add_argument("--iters", type=int, default=5)
+ap.add_argument("--shard", type=int, default=1, help="take the first of this many point shards (one GPU, no exchange)")
 a = ap.parse_args()
 n_cam, n_pts, n_obs = b200ba.synthetic.CONFIGS[a.workload]
-pb = b200ba.synthetic.make_problem(n_cam, n_pts, n_obs, seed=0)
+if a.shard > 1:
+    from b200ba import dist as bd
+    deg = b200ba.synthetic.point_degrees(n_pts, n_obs, min(16, n_cam), 0)
+    lo, hi = bd.plan_shards_from_degrees(deg, a.shard)[0]
+    pb = b200ba.synthetic.make_problem(n_cam, n_pts, n_obs, seed=0, point_range=(lo, hi))
+    pb.point_indices = pb.point_indices - lo
+    n_pts = hi - lo
+else:
+    pb = b200ba.synthetic.make_problem(n_cam, n_pts, n_obs, seed=0)
 pin = lambda arr: torch.from_numpy(np.ascontiguousarray(arr)).pin_memory().numpy()
 ci, pi, uv, x0 = pin(pb.camera_indices), pin(pb.point_indices), pin(pb.points_2d), pin(pb.x0)
 eng = b200ba.Engine(0)
