@@ -111,10 +111,12 @@ def _chain(n_cam=256, n_pts=12000, n_obs=48000, seed=7):
     return b200ba.synthetic.make_problem(n_cam, n_pts, n_obs, seed=seed)
 
 
-def test_two_level_coarse_inverse_matches_numpy(engine):
+@pytest.mark.parametrize("shape", [(256, 12000, 48000), (400, 16000, 64000)], ids=["2tiles", "3tiles"])
+def test_two_level_coarse_inverse_matches_numpy(engine, shape):
     """The coarse operator A_c = P^T S P built and inverted on the GPU (gauge modes about each aggregate's centroid,
-    S P product, assembly, blocked Gauss-Jordan) equals the dense numpy construction from the engine's own S."""
-    pb = _chain()
+    S P product, assembly, blocked Gauss-Jordan; coarse matrices of two and three 64 x 64 tiles) equals the dense numpy
+    construction from the engine's own S."""
+    pb = _chain(*shape)
     engine.set_problem(*pb.args())
     engine.set_two_level(2)
     try:
@@ -143,6 +145,7 @@ def test_two_level_coarse_inverse_matches_numpy(engine):
         A = P.T @ S @ P
         err = np.abs(Ainv @ A - np.eye(nc)).max()
         assert err <= 1e-7, err
+        assert np.abs(Ainv - Ainv.T).max() <= 1e-12 * np.abs(Ainv).max()
     finally:
         engine.set_two_level(1)
 
