@@ -1140,7 +1140,8 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     std::thread t;
     ~Joiner() { if (t.joinable()) t.join(); }
   } worker;
-  worker.t = std::thread(host_bsr);
+  if (n_blk >= 4096) worker.t = std::thread(host_bsr);   // small problems: starting a thread costs more than the work
+  else host_bsr();
   // ---- 8. tile mode: pair slots = (tile, block) cells ordered inside each tile by decreasing entry count,
   //         per-block reduce lists, entries packed to tile-local 16-bit indices
   if (pb.schur_tiles) {
@@ -1223,7 +1224,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
   mark("10 dataflow blobs");
   // ---- 10b. results of the host worker (step 7)
-  worker.t.join();
+  if (worker.t.joinable()) worker.t.join();
   mark("7 host BSR (wait for the worker)");
   pb.n_sch = (int)hb.sb.size();
   pb.nnzb = (int)hb.col.size();
