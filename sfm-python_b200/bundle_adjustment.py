@@ -392,7 +392,7 @@ def pack_Rt(poses):
 # ---------------------------------------------------------------------------------------------
 # Reference call surface
 # ---------------------------------------------------------------------------------------------
-_cache = {"key": None, "engine": None, "n_gpus": None}
+_cache = {"key": None, "engine": None, "n_gpus": None, "refs": ()}
 
 
 def default_n_gpus():
@@ -403,34 +403,71 @@ def default_n_gpus():
         return 1
 
 
+_FULL_DIGEST_BYTES = 8 << 20     # above this a blake2b pass over the arrays costs more than the solve it would save
+
+
 def _problem_key(n_cam, n_pts, ci, pi, uv, K):
-    """Content digest of the problem (blake2b over the index, pixel and K bytes): two different problems never share a
-    key, so a cached device problem is only reused for the very same arrays."""
+    """Key of the cached device problem.  Up to 8 MB of index / pixel data: a content digest (blake2b over the bytes of
+    the three arrays and K), so two different problems never share a key.  Above that the digest would dominate the call
+    (blake2b runs at about 0.4 GB/s: 1.5 s for the 640 MB of config D, ten times the solve): the key is then the identity
+    of the caller's arrays -- object, address, shape, strides, dtype -- plus a digest of 3 x 73 k sampled elements, and
+    `engine_for` keeps weak references to the arrays so that a recycled id or address cannot match.  What this does not
+    see is an in-place edit of unsampled elements between two calls; `b200ba.reset()` drops the cached problem."""
     import hashlib
     h = hashlib.blake2b(digest_size=16)
-    for a, dt in ((ci, np.int64), (pi, np.int64), (uv, None), (K, np.float64)):
-        a = np.ascontiguousarray(a) if dt is None else np.ascontiguousarray(a, dtype=dt)
-        h.update(str((a.dtype.str, a.shape)).encode())
-        h.update(memoryview(a).cast("B"))
-    return (int(n_cam), int(n_pts), h.digest())
+    big = [ci, pi, uv]
+    total = sum(a.nbytes for a in big if isinstance(a, np.ndarray))
+    if total <= _FULL_DIGEST_BYTES or not all(isinstance(a, np.ndarray) for a in big):
+        for a, dt in ((ci, np.int64), (pi, np.int64), (uv, None), (K, np.float64)):
+            a = np.ascontiguousarray(a) if dt is None else np.ascontiguousarray(a, dtype=dt)
+            h.update(str((a.dtype.str, a.shape)).encode())
+            h.update(memoryview(a).cast("B"))
+        return (int(n_cam), int(n_pts), "digest", h.digest())
+    ident = []
+    for a in big:
+        ident.append((id(a), a.__array_interface__["data"][0], a.shape, a.strides, a.dtype.str))
+        flat = a.reshape(-1) if a.flags.c_contiguous else a.ravel()
+        step = max(1, flat.size // 65536)
+        for part in (flat[:4096], flat[-4096:], flat[::step]):
+            h.update(np.ascontiguousarray(part).tobytes())
+    h.update(np.ascontiguousarray(K, dtype=np.float64).tobytes())
+    return (int(n_cam), int(n_pts), "identity", tuple(ident), h.digest())
+
+
+def _key_alive(key, arrays):
+    """An identity key only stands while the very arrays it was taken from are alive (ids and addresses get recycled)."""
+    if key is None or key[2] != "identity":
+        return True
+    refs = _cache.get("refs") or ()
+    return len(refs) == len(arrays) and all(r() is a for r, a in zip(refs, arrays))
 
 
 def engine_for(n_cam, n_pts, camera_indices, point_indices, points_2d, K, n_gpus=None):
     """The engine holding this problem on the device(s) (uploaded once, reused by later calls).  ``n_gpus`` (default
     ``B200BA_GPUS`` or 1): the first n GPUs of the box inside this process."""
+    import weakref
     n_gpus = default_n_gpus() if n_gpus is None else max(1, int(n_gpus))
     key = _problem_key(n_cam, n_pts, camera_indices, point_indices, points_2d, K) + (n_gpus,)
+    arrays = (camera_indices, point_indices, points_2d)
     if _cache["engine"] is not None and _cache["n_gpus"] != n_gpus:
         _cache["engine"].close()
         _cache["engine"], _cache["key"] = None, None
-    if _cache["key"] != key or _cache["engine"] is None:
+    if _cache["key"] != key or _cache["engine"] is None or not _key_alive(_cache["key"], arrays):
         eng = _cache["engine"] or _new_engine(n_gpus)
         _cache["n_gpus"] = n_gpus
         _cache["key"] = None                       # a failed upload leaves no stale key behind
         _cache["engine"] = eng
         eng.set_problem(n_cam, n_pts, camera_indices, point_indices, points_2d, K)
         _cache["key"] = key
+        _cache["refs"] = tuple(weakref.ref(a) for a in arrays) if key[2] == "identity" else ()
     return _cache["engine"]
+
+
+def reset():
+    """Drop the cached device problem (and its engine): the next call uploads again."""
+    if _cache["engine"] is not None:
+        _cache["engine"].close()
+    _cache.update(key=None, engine=None, n_gpus=None, refs=())
 
 
 def _new_engine(n_gpus=1):

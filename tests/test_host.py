@@ -165,6 +165,30 @@ def test_problem_key_is_a_content_digest():
     assert key(n_cam, n_pts, ci, pi, uv, K) != key(n_cam, n_pts, ci, pi, uv.astype(np.int64), K)
 
 
+def test_problem_key_of_large_arrays_is_identity_plus_sample(monkeypatch):
+    """Above the full-digest limit the key is the identity of the caller's arrays plus a sampled digest (a blake2b pass over
+    config D's 640 MB takes ten times the solve): the same objects give the same key, copies do not, a change in a
+    sampled element does, and the cache insists that the very objects are still alive."""
+    import b200ba
+    B = b200ba.bundle_adjustment
+    monkeypatch.setattr(B, "_FULL_DIGEST_BYTES", 1024)
+    n_cam, n_pts, ci, pi, uv, K = _ba_args()
+    k1 = B._problem_key(n_cam, n_pts, ci, pi, uv, K)
+    assert k1[2] == "identity" and k1 == B._problem_key(n_cam, n_pts, ci, pi, uv, K)
+    assert k1 != B._problem_key(n_cam, n_pts, ci.copy(), pi, uv, K)
+    uv[0, 0] += 1.0
+    assert k1 != B._problem_key(n_cam, n_pts, ci, pi, uv, K)
+    uv[0, 0] -= 1.0
+    import weakref
+    monkeypatch.setitem(B._cache, "refs", tuple(weakref.ref(a) for a in (ci, pi, uv)))
+    assert B._key_alive(k1 + (1,), (ci, pi, uv))
+    assert not B._key_alive(k1 + (1,), (ci.copy(), pi, uv))
+    monkeypatch.setitem(B._cache, "refs", ())
+    assert not B._key_alive(k1 + (1,), (ci, pi, uv))
+    # lists cannot be identified: they fall back to the full digest
+    assert B._problem_key(n_cam, n_pts, ci.tolist(), pi, uv, K)[2] == "digest"
+
+
 def _import_real_sfm():
     """The reference's own sfm_lite.sfm, imported from /root/reference with matplotlib stubbed (absent here; the module
     only uses it for plots).  Exists in the build container only: the GPU box has no reference tree."""
