@@ -36,6 +36,105 @@ int cuda_fail(Handle* h, cudaError_t e, const char* where) {
   return fail(h, e == cudaErrorMemoryAllocation ? B200BA_OOM : B200BA_CUDA, m);
 }
 
+// ------------------------------------------------------------------ threaded pageable <-> device copies
+int BigCopy::wait() {
+  for (std::thread& t : th)
+    if (t.joinable()) t.join();
+  th.clear();
+  if (start) { cudaEventDestroy(start); start = nullptr; }
+  int rc = 0;
+  for (int r : rcs)
+    if (r && !rc) rc = r;
+  rcs.clear();
+  return rc;
+}
+
+int big_copy_start(Handle* h, BigCopy& bc, void* dst, const void* src, size_t bytes, bool to_device, cudaStream_t st) {
+  if (bytes == 0) return 0;
+  const cudaMemcpyKind kind = to_device ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToHost;
+  const void* host = to_device ? src : dst;
+  constexpr size_t CH = (size_t)2 << 20, MIN_BYTES = (size_t)8 << 20;
+  int want = 0;
+  if (bytes >= MIN_BYTES) {
+    cudaPointerAttributes at;
+    const cudaError_t e = cudaPointerGetAttributes(&at, host);
+    if (e != cudaSuccess) cudaGetLastError();
+    if (e != cudaSuccess || at.type == cudaMemoryTypeUnregistered) {
+      const char* env = getenv("B200BA_COPY_THREADS");   // 0: leave pageable copies to the driver
+      const unsigned hw = std::thread::hardware_concurrency();
+      want = env ? atoi(env) : (int)std::min<unsigned>(8, std::max<unsigned>(2, hw / 4));
+      want = std::max(0, std::min(want, 16));
+    }
+  }
+  if (want > 0) {
+    const size_t need = (size_t)want * 2 * CH;
+    if (h->xfer_bytes < need) {
+      if (h->xfer) cudaFreeHost(h->xfer);
+      h->xfer = nullptr;
+      h->xfer_bytes = 0;
+      if (cudaMallocHost((void**)&h->xfer, need) == cudaSuccess) h->xfer_bytes = need;
+      else { cudaGetLastError(); want = 0; }
+    }
+  }
+  if (want == 0) {
+    BA_CUDA(h, cudaMemcpyAsync(dst, src, bytes, kind, st));
+    return 0;
+  }
+  BA_CUDA(h, cudaEventCreateWithFlags(&bc.start, cudaEventDisableTiming));
+  BA_CUDA(h, cudaEventRecord(bc.start, st));
+  const size_t nch = (bytes + CH - 1) / CH;
+  const int T = (int)std::min<size_t>((size_t)want, nch);
+  bc.rcs.assign(T, 0);
+  const int device = h->device;
+  char* slots = h->xfer;
+  cudaEvent_t start = bc.start;
+  for (int t = 0; t < T; ++t) {
+    int* rc = &bc.rcs[t];
+    bc.th.emplace_back([=]() {
+      auto bad = [&](cudaError_t e) { if (e != cudaSuccess) { cudaGetLastError(); *rc = B200BA_CUDA; return true; } return false; };
+      if (bad(cudaSetDevice(device))) return;
+      cudaStream_t s = nullptr;
+      cudaEvent_t ev[2] = {nullptr, nullptr};
+      if (bad(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking))) return;
+      bool ok = !bad(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming)) &&
+                !bad(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming)) && !bad(cudaStreamWaitEvent(s, start, 0));
+      char* slot[2] = {slots + (size_t)(2 * t) * CH, slots + (size_t)(2 * t + 1) * CH};
+      size_t prev_c = 0;
+      bool have_prev = false;
+      int k = 0;
+      for (size_t c = (size_t)t; ok && c < nch; c += (size_t)T, ++k) {
+        const size_t off = c * CH, len = std::min(CH, bytes - off);
+        const int b = k & 1;
+        if (to_device) {
+          if (k >= 2 && bad(cudaEventSynchronize(ev[b]))) { ok = false; break; }   // the slot's previous DMA has read it
+          memcpy(slot[b], (const char*)src + off, len);
+          ok = !bad(cudaMemcpyAsync((char*)dst + off, slot[b], len, cudaMemcpyHostToDevice, s)) && !bad(cudaEventRecord(ev[b], s));
+        } else {
+          // slot b was drained two chunks ago (below): start this chunk's DMA, then drain the previous chunk
+          ok = !bad(cudaMemcpyAsync(slot[b], (const char*)src + off, len, cudaMemcpyDeviceToHost, s)) && !bad(cudaEventRecord(ev[b], s));
+          if (ok && have_prev) {
+            const size_t poff = prev_c * CH, plen = std::min(CH, bytes - poff);
+            if (bad(cudaEventSynchronize(ev[b ^ 1]))) { ok = false; break; }
+            memcpy((char*)dst + poff, slot[b ^ 1], plen);
+          }
+          prev_c = c;
+          have_prev = true;
+        }
+      }
+      if (ok && !to_device && have_prev) {
+        const int b = (k - 1) & 1;
+        const size_t poff = prev_c * CH, plen = std::min(CH, bytes - poff);
+        if (!bad(cudaEventSynchronize(ev[b]))) memcpy((char*)dst + poff, slot[b], plen);
+      }
+      bad(cudaStreamSynchronize(s));
+      if (ev[0]) cudaEventDestroy(ev[0]);
+      if (ev[1]) cudaEventDestroy(ev[1]);
+      cudaStreamDestroy(s);
+    });
+  }
+  return 0;
+}
+
 void* pool_alloc(Handle* h, size_t bytes) {
   void* p = nullptr;
   cudaError_t e = h->pool ? cudaMallocFromPoolAsync(&p, bytes, h->pool, h->stream) : cudaMalloc(&p, bytes);

@@ -5,6 +5,7 @@
 
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/b200ba.h"
@@ -243,6 +244,8 @@ struct Handle {
   // per-array stream syncs of pageable uploads disappear (16+ per set_problem); reset at the end of setup_problem
   char* stage = nullptr;
   size_t stage_bytes = 0, stage_off = 0;
+  char* xfer = nullptr;             // page-locked slots of the threaded pageable <-> device copies (big_copy), lazily allocated
+  size_t xfer_bytes = 0;
   bool direct_push = false;        // this linearisation's slot reduction stored its blocks straight into the peers' slots
   int64_t n_obs_global = 0;
   P2P p2p;
@@ -263,6 +266,19 @@ struct Handle {
 int fail(Handle* h, int code, const std::string& msg);
 int ensure_Y(Handle* h, int64_t count);  // grow w.Y (staging / Jacobian export)
 int cuda_fail(Handle* h, cudaError_t e, const char* where);
+// Large copy between host memory and the device, ordered after the work already queued on `st`.
+// Page-locked (or managed) host memory: one cudaMemcpyAsync on `st`.  PAGEABLE host memory of 8 MB or more: the driver
+// would stage it through one internal buffer on the calling thread (about 10 GB/s); here a few worker threads copy
+// their chunks through page-locked slots of their own and issue the DMA on their own streams.  The workers run in the
+// background: wait() (or the destructor) joins them and returns the first error; until then neither side may be touched.
+struct BigCopy {
+  std::vector<std::thread> th;
+  std::vector<int> rcs;
+  cudaEvent_t start = nullptr;
+  int wait();
+  ~BigCopy() { wait(); }
+};
+int big_copy_start(Handle* h, BigCopy& bc, void* dst, const void* src, size_t bytes, bool to_device, cudaStream_t st);
 void* dalloc(Handle* h, size_t bytes);  // nullptr on failure (h->err set)
 void* pool_alloc(Handle* h, size_t bytes);  // raw stream-ordered allocation from h->pool (nullptr on failure)
 void pool_free(Handle* h, void* p);

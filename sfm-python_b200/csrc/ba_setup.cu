@@ -631,6 +631,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   };
 
   // ---- 1. raw inputs to the device, range / order check, int32 indices
+  BigCopy uv_copy;   // declared after `tmp`: its workers are joined before the scratch (d_uv) is freed on an early return
   TMP_ALLOC(d_cam64, int64_t, N);
   TMP_ALLOC(d_pt64, int64_t, N);
   TMP_ALLOC(d_uv, double, 2 * N);
@@ -640,13 +641,19 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   TMP_ALLOC(d_flags, int, 1);
   BA_CUDA(h, cudaMemsetAsync(d_flags, 0, sizeof(int), st));
   if (N > 0) {
-    BA_CUDA(h, cudaMemcpyAsync(d_cam64, cam_idx, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));
-    BA_CUDA(h, cudaMemcpyAsync(d_pt64, pt_idx, N * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    // page-locked sources go as one DMA each; pageable ones (what numpy hands over) through big_copy's worker threads
+    {
+      BigCopy bc;
+      if (int rc = big_copy_start(h, bc, d_cam64, cam_idx, N * sizeof(int64_t), true, st)) return rc;
+      if (bc.wait()) return fail(h, B200BA_CUDA, "upload of the camera indices failed");
+      if (int rc = big_copy_start(h, bc, d_pt64, pt_idx, N * sizeof(int64_t), true, st)) return rc;
+      if (bc.wait()) return fail(h, B200BA_CUDA, "upload of the point indices failed");
+    }
     // the pixel array (half of the upload) goes on the second stream; nothing needs it before k_gather_uv at the end
     BA_CUDA(h, cudaEventRecord(h->ev_a, st));                 // d_uv is a stream-ordered allocation of `st`
     BA_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_a, 0));
-    BA_CUDA(h, cudaMemcpyAsync(d_uv, uv, 2 * N * sizeof(double), cudaMemcpyHostToDevice, h->stream2));
-    BA_CUDA(h, cudaEventRecord(h->ev_b, h->stream2));
+    if (int rc = big_copy_start(h, uv_copy, d_uv, uv, 2 * N * sizeof(double), true, h->stream2)) return rc;
+    if (uv_copy.th.empty()) BA_CUDA(h, cudaEventRecord(h->ev_b, h->stream2));
     k_check_convert<<<nblk(N, T), T, 0, st>>>(N, C, P, d_cam64, d_pt64, d_cam_in, d_pt_in, d_iota, d_flags);
   }
   int flags = 0;
@@ -1250,7 +1257,11 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
   mark("10b BSR uploads");
   if (N > 0) {
-    BA_CUDA(h, cudaStreamWaitEvent(st, h->ev_b, 0));
+    if (!uv_copy.th.empty()) {   // pageable pixels: the worker threads finish the upload (host-synchronous)
+      if (uv_copy.wait()) return fail(h, B200BA_CUDA, "upload of the pixel array failed");
+    } else {
+      BA_CUDA(h, cudaStreamWaitEvent(st, h->ev_b, 0));
+    }
     k_gather_uv<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_uv, pb.u, pb.v);
   }
   mark("11 pixels");

@@ -19,6 +19,7 @@ import b200ba  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="D")
 ap.add_argument("--iters", type=int, default=5)
+ap.add_argument("--pageable", action="store_true", help="hand over plain numpy arrays (what sfm.py does) instead of page-locked ones")
 ap.add_argument("--shard", type=int, default=1, help="take the first of this many point shards (one GPU, no exchange)")
 a = ap.parse_args()
 n_cam, n_pts, n_obs = b200ba.synthetic.CONFIGS[a.workload]
@@ -31,7 +32,7 @@ if a.shard > 1:
     n_pts = hi - lo
 else:
     pb = b200ba.synthetic.make_problem(n_cam, n_pts, n_obs, seed=0)
-pin = lambda arr: torch.from_numpy(np.ascontiguousarray(arr)).pin_memory().numpy()
+pin = (lambda arr: np.ascontiguousarray(arr).copy()) if a.pageable else (lambda arr: torch.from_numpy(np.ascontiguousarray(arr)).pin_memory().numpy())
 ci, pi, uv, x0 = pin(pb.camera_indices), pin(pb.point_indices), pin(pb.points_2d), pin(pb.x0)
 eng = b200ba.Engine(0)
 solver = "pcg" if n_cam > 64 else "cholesky"
