@@ -223,6 +223,14 @@ struct P2P {
   bool direct = false;               // peers live in this process (b200ba_create_multi): raw pointers + peer access, no IPC
 };
 
+// Host-built block-CSR view of S and the camera aggregates of the two-level preconditioner (set_problem step 7).
+struct HostBsr {
+  std::vector<int> br, bc, diag, sb, sa, se, choff, rowptr, col, src;
+  std::vector<int> cam_agg, agg_off, agg_cams, sp_rowptr, sp_col, sp_of;
+  int n_agg = 0;
+  bool tl = false;
+};
+
 struct Handle {
   int device = 0;
   int sm_count = 148;
@@ -244,6 +252,7 @@ struct Handle {
   // per-array stream syncs of pageable uploads disappear (16+ per set_problem); reset at the end of setup_problem
   char* stage = nullptr;
   size_t stage_bytes = 0, stage_off = 0;
+  HostBsr hb;                       // set_problem scratch kept between calls (capacity reuse)
   char* xfer = nullptr;             // page-locked slots of the threaded pageable <-> device copies (big_copy), lazily allocated
   size_t xfer_bytes = 0;
   bool direct_push = false;        // this linearisation's slot reduction stored its blocks straight into the peers' slots
