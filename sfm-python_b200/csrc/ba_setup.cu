@@ -88,19 +88,24 @@ __global__ void k_pair_count(int P, const int* __restrict__ pt_off, const int* _
 
 __global__ void k_pair_fill(int P, long long C, const int* __restrict__ pt_off, const int* __restrict__ cam,
                             bool skip_self, const long long* __restrict__ ent_off, const int* __restrict__ pt_tile,
-                            long long* __restrict__ keys, long long* __restrict__ vals) {
+                            long long* __restrict__ keys, long long* __restrict__ vals, const int* __restrict__ st_off,
+                            unsigned* __restrict__ vals32) {
   int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   int a = pt_off[p], b = pt_off[p + 1];
   long long e = ent_off[p];
   const long long tbase = pt_tile ? (long long)pt_tile[p] * C * C : 0;
+  // tile mode: the value is the pair of tile-local 16-bit observation indices the kernels read (4 instead of 8 bytes
+  // through the sort, no repacking pass afterwards)
+  const int obase = vals32 ? st_off[pt_tile[p]] : 0;
   for (int i = a; i < b; ++i) {
     int ci = cam[i];
     for (int j = a; j < b; ++j) {
       int cj = cam[j];
       if (ci <= cj && !(skip_self && i == j)) {
         keys[e] = tbase + (long long)ci * C + cj;
-        vals[e] = ((long long)i << 32) | (unsigned int)j;
+        if (vals32) vals32[e] = ((unsigned)(i - obase) << 16) | (unsigned)(j - obase);
+        else vals[e] = ((long long)i << 32) | (unsigned int)j;
         ++e;
       }
     }
@@ -791,8 +796,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   pb.n_ent = n_ent;
   long long* d_ent64 = nullptr;  // sorted (i << 32) | j : kept in stream mode, scratch in tile mode
   if (pb.schur_tiles) {
-    d_ent64 = (long long*)tmp.get(std::max<size_t>(n_ent, 1) * sizeof(long long));
-    if (!d_ent64) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+    DEV_ALLOC(pb.tent, unsigned, n_ent);   // the sort writes the packed tile-local entries straight into place
   } else {
     DEV_ALLOC(pb.ent, long long, n_ent);
     d_ent64 = pb.ent;
@@ -804,19 +808,37 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   std::vector<long long> keys_host;  // unique local block keys
   {
     TMP_ALLOC(d_keys, long long, n_ent);
-    TMP_ALLOC(d_vals, long long, n_ent);
+    long long* d_vals = nullptr;
+    unsigned* d_vals32 = nullptr;
+    if (pb.schur_tiles) {
+      d_vals32 = (unsigned*)tmp.get(std::max<size_t>(n_ent, 1) * sizeof(unsigned));
+      if (!d_vals32) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+    } else {
+      d_vals = (long long*)tmp.get(std::max<size_t>(n_ent, 1) * sizeof(long long));
+      if (!d_vals) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+    }
     if (P > 0)
       k_pair_fill<<<nblk(P, T), T, 0, st>>>((int)P, (long long)C, pb.pt_off, pb.cam, pb.fused, d_ent_off, d_pt_tile, d_keys,
-                                            d_vals);
+                                            d_vals, pb.st_off, d_vals32);
     if (n_ent > 0) {
       const double kmax = (double)CC * (double)(pb.schur_tiles ? pb.n_st : 1);
       int end_bit = 1;
       while (end_bit < 63 && (double)((long long)1 << end_bit) < kmax) ++end_bit;
       size_t bytes = 0;
-      cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_keys, d_keys_sorted, d_vals, d_ent64, (int)n_ent, 0, end_bit, st);
-      TMP_ALLOC(d_sort, char, bytes);
-      BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort, bytes, d_keys, d_keys_sorted, d_vals, d_ent64, (int)n_ent, 0,
-                                                 end_bit, st));
+      char* d_sort = nullptr;
+      if (pb.schur_tiles) {
+        cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_keys, d_keys_sorted, d_vals32, pb.tent, (int)n_ent, 0, end_bit, st);
+        d_sort = (char*)tmp.get(std::max<size_t>(bytes, 1));
+        if (!d_sort) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+        BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort, bytes, d_keys, d_keys_sorted, d_vals32, pb.tent, (int)n_ent, 0,
+                                                   end_bit, st));
+      } else {
+        cub::DeviceRadixSort::SortPairs(nullptr, bytes, d_keys, d_keys_sorted, d_vals, d_ent64, (int)n_ent, 0, end_bit, st);
+        d_sort = (char*)tmp.get(std::max<size_t>(bytes, 1));
+        if (!d_sort) return fail(h, B200BA_OOM, "out of device memory in set_problem (scratch)");
+        BA_CUDA(h, cub::DeviceRadixSort::SortPairs(d_sort, bytes, d_keys, d_keys_sorted, d_vals, d_ent64, (int)n_ent, 0,
+                                                   end_bit, st));
+      }
       TMP_ALLOC(d_nruns, int, 1);
       bytes = 0;
       cub::DeviceRunLengthEncode::Encode(nullptr, bytes, d_keys_sorted, d_uniq, d_runs, d_nruns, (int)n_ent, st);
@@ -1152,7 +1174,6 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   // ---- 8. tile mode: pair slots = (tile, block) cells ordered inside each tile by decreasing entry count,
   //         per-block reduce lists, entries packed to tile-local 16-bit indices
   if (pb.schur_tiles) {
-    DEV_ALLOC(pb.tent, unsigned, n_ent);
     DEV_ALLOC(pb.tile_ent_off, int, pb.n_st + 1);
     BA_CUDA(h, cudaMemsetAsync(pb.tile_ent_off, 0, (pb.n_st + 1) * sizeof(int), st));
     SlotList sl;
@@ -1160,7 +1181,6 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
     pb.n_slot = sl.n_slot; pb.slot_a = sl.slot_a; pb.slot_n = sl.slot_n;
     pb.tile_slot_off = sl.tile_off; pb.blk_slot_off = sl.grp_off; pb.blk_slots = sl.grp_slots;
     if (n_ent > 0) {
-      k_pack_entries<<<nblk(n_ent, T), T, 0, st>>>(n_ent, d_ent64, pb.st_off, pb.n_st, pb.tent);
       k_tile_ent_off<<<nblk(pb.n_st + 1, T), T, 0, st>>>(pb.n_st, (int)n_ent, d_keys_sorted, CC, pb.tile_ent_off);
     }
   }
