@@ -236,7 +236,7 @@ struct Handle {
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaStream_t stream2 = nullptr;   // set_problem: upload of the pixel array underneath the index pipeline
-  cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+  cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr;
   cudaMemPool_t pool = nullptr;   // stream-ordered pool that keeps freed blocks: re-running set_problem costs no cudaMalloc
   std::string err;
   bool has_problem = false;

@@ -16,19 +16,28 @@ namespace {
 
 constexpr int SLOT_CAP = 32;  // pair entries per Schur slot (tile mode)
 
-__global__ void k_check_convert(int64_t N, int64_t C, int64_t P, const int64_t* __restrict__ cam64,
-                                const int64_t* __restrict__ pt64, int* __restrict__ cam32, int* __restrict__ pt32,
-                                int* __restrict__ iota, int* __restrict__ flags) {
+// point indices: range check, order check, int32 copy, identity permutation (flags: 1 out of range, 2 unsorted)
+__global__ void k_check_convert_pt(int64_t N, int64_t P, const int64_t* __restrict__ pt64, int* __restrict__ pt32,
+                                   int* __restrict__ iota, int* __restrict__ flags) {
   int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (i >= N) return;
-  int64_t c = cam64[i], p = pt64[i];
+  int64_t p = pt64[i];
   int f = 0;
-  if (c < 0 || c >= C || p < 0 || p >= P) { f |= 1; c = 0; p = 0; }
+  if (p < 0 || p >= P) { f |= 1; p = 0; }
   if (i > 0 && pt64[i - 1] > pt64[i]) f |= 2;
   if (f) atomicOr(flags, f);
-  cam32[i] = (int)c;
   pt32[i] = (int)p;
   iota[i] = (int)i;
+}
+
+// camera indices: range check and int32 copy; runs on the second stream behind their upload (flags[1]: 1 out of range)
+__global__ void k_check_convert_cam(int64_t N, int64_t C, const int64_t* __restrict__ cam64, int* __restrict__ cam32,
+                                    int* __restrict__ flags) {
+  int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i >= N) return;
+  int64_t c = cam64[i];
+  if (c < 0 || c >= C) { atomicOr(flags + 1, 1); c = 0; }
+  cam32[i] = (int)c;
 }
 
 __global__ void k_gather_obs(int64_t N, const int* __restrict__ perm, const int* __restrict__ cam_in,
@@ -643,30 +652,34 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   TMP_ALLOC(d_cam_in, int, N);
   TMP_ALLOC(d_pt_in, int, N);
   TMP_ALLOC(d_iota, int, N);
-  TMP_ALLOC(d_flags, int, 1);
-  BA_CUDA(h, cudaMemsetAsync(d_flags, 0, sizeof(int), st));
+  TMP_ALLOC(d_flags, int, 2);
+  BA_CUDA(h, cudaMemsetAsync(d_flags, 0, 2 * sizeof(int), st));
   if (N > 0) {
-    // page-locked sources go as one DMA each; pageable ones (what numpy hands over) through big_copy's worker threads
+    // Page-locked sources go as one DMA each; pageable ones (what numpy hands over) through big_copy's worker threads.
+    // Only the point indices are needed at once (order, offsets, tiles): the camera indices and then the pixels travel
+    // on the second stream underneath steps 2 and 3, the camera check / conversion runs there too.
+    BA_CUDA(h, cudaEventRecord(h->ev_a, st));                 // the scratch arrays are stream-ordered allocations of `st`
+    BA_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_a, 0));
     {
       BigCopy bc;
-      if (int rc = big_copy_start(h, bc, d_cam64, cam_idx, N * sizeof(int64_t), true, st)) return rc;
-      if (bc.wait()) return fail(h, B200BA_CUDA, "upload of the camera indices failed");
       if (int rc = big_copy_start(h, bc, d_pt64, pt_idx, N * sizeof(int64_t), true, st)) return rc;
       if (bc.wait()) return fail(h, B200BA_CUDA, "upload of the point indices failed");
+      k_check_convert_pt<<<nblk(N, T), T, 0, st>>>(N, P, d_pt64, d_pt_in, d_iota, d_flags);
+      if (int rc = big_copy_start(h, bc, d_cam64, cam_idx, N * sizeof(int64_t), true, h->stream2)) return rc;
+      if (bc.wait()) return fail(h, B200BA_CUDA, "upload of the camera indices failed");
     }
-    // the pixel array (half of the upload) goes on the second stream; nothing needs it before k_gather_uv at the end
-    BA_CUDA(h, cudaEventRecord(h->ev_a, st));                 // d_uv is a stream-ordered allocation of `st`
-    BA_CUDA(h, cudaStreamWaitEvent(h->stream2, h->ev_a, 0));
+    k_check_convert_cam<<<nblk(N, T), T, 0, h->stream2>>>(N, C, d_cam64, d_cam_in, d_flags);
+    BA_CUDA(h, cudaEventRecord(h->ev_c, h->stream2));
+    // the pixel array (half of the upload): nothing needs it before k_gather_uv at the end
     if (int rc = big_copy_start(h, uv_copy, d_uv, uv, 2 * N * sizeof(double), true, h->stream2)) return rc;
     if (uv_copy.th.empty()) BA_CUDA(h, cudaEventRecord(h->ev_b, h->stream2));
-    k_check_convert<<<nblk(N, T), T, 0, st>>>(N, C, P, d_cam64, d_pt64, d_cam_in, d_pt_in, d_iota, d_flags);
   }
   int flags = 0;
   BA_CUDA(h, cudaMemcpyAsync(&flags, d_flags, sizeof(int), cudaMemcpyDeviceToHost, st));
   BA_CUDA(h, cudaStreamSynchronize(st));
   if (flags & 1) return fail(h, B200BA_INDEX_RANGE, "camera or point index out of range");
 
-  mark("1 upload+check");
+  mark("1 upload+check (points)");
   // ---- 2. point-major order (stable); identity when the input is already sorted (graph.py:186-191)
   DEV_ALLOC(pb.u, double, N + 2);  // + slack for 16-byte aligned prefetch windows
   DEV_ALLOC(pb.v, double, N + 2);
@@ -685,10 +698,7 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   } else if (N > 0) {
     BA_CUDA(h, cudaMemcpyAsync(pb.pt, d_pt_in, N * sizeof(int), cudaMemcpyDeviceToDevice, st));
   }
-  if (N > 0) {
-    k_gather_obs<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_cam_in, pb.cam);
-    k_offsets<<<nblk(N, T), T, 0, st>>>(N, (int)P, pb.pt, pb.pt_off);
-  }
+  if (N > 0) k_offsets<<<nblk(N, T), T, 0, st>>>(N, (int)P, pb.pt, pb.pt_off);
 
   mark("2 point-major order");
   // ---- 3. warp tiles: greedy packing of whole points into <= 32 observations (a point with more is its own tile),
@@ -732,6 +742,16 @@ int setup_problem(Handle* h, int64_t C, int64_t P, int64_t N, const int64_t* cam
   }
 
   mark("3 warp/CTA tiles");
+  // ---- 3b. camera indices into point-major order (their upload and check ran underneath steps 2 and 3)
+  if (N > 0) {
+    BA_CUDA(h, cudaStreamWaitEvent(st, h->ev_c, 0));
+    k_gather_obs<<<nblk(N, T), T, 0, st>>>(N, pb.perm, d_cam_in, pb.cam);
+    int cflag = 0;
+    BA_CUDA(h, cudaMemcpyAsync(&cflag, d_flags + 1, sizeof(int), cudaMemcpyDeviceToHost, st));
+    BA_CUDA(h, cudaStreamSynchronize(st));
+    if (cflag & 1) return fail(h, B200BA_INDEX_RANGE, "camera or point index out of range");
+  }
+  mark("3b camera indices");
   // ---- 4. camera-sorted permutation and chunks: only the unfused pipeline (k_cam_side / k_cam_reduce) reads them; the
   //         fused kernels group a tile's observations by camera through the self slots of step 9 (4.6 ms saved at config D)
   if (!pb.fused) {
