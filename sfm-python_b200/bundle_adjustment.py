@@ -75,6 +75,23 @@ class _PinnedPool:
             self.lib.b200ba_host_free(C.c_void_p(ptr))
 
 
+def _as_dtype(a, dtype):
+    """``np.ascontiguousarray(a, dtype)``; a LARGE array of another dtype (the reference's int64 pixel array at the
+    size of config D is 320 MB) is converted in chunks on a few threads -- numpy's cast loop releases the GIL and one
+    thread runs it at 1-2 GB/s."""
+    a = np.asarray(a)
+    if a.dtype == dtype or a.size < (1 << 21) or not a.flags.c_contiguous:
+        return np.ascontiguousarray(a, dtype=dtype)
+    from concurrent.futures import ThreadPoolExecutor
+    out = np.empty(a.shape, dtype=dtype)
+    src, dst = a.reshape(-1), out.reshape(-1)
+    n_thr = max(1, min(8, (os.cpu_count() or 2) // 2))
+    step = -(-src.size // (4 * n_thr))
+    with ThreadPoolExecutor(n_thr) as ex:
+        list(ex.map(lambda k: np.copyto(dst[k:k + step], src[k:k + step], casting="unsafe"), range(0, src.size, step)))
+    return out
+
+
 class Engine:
     """One GPU's handle (``b200ba_handle``): problem upload, residual/Jacobian/normal equations, LM solve."""
 
@@ -140,9 +157,9 @@ class Engine:
 
     # -- problem
     def set_problem(self, n_cam, n_pts, camera_indices, point_indices, points_2d, K):
-        ci = np.ascontiguousarray(camera_indices, dtype=np.int64).ravel()
-        pi = np.ascontiguousarray(point_indices, dtype=np.int64).ravel()
-        uv = np.ascontiguousarray(points_2d, dtype=np.float64)
+        ci = _as_dtype(camera_indices, np.int64).ravel()
+        pi = _as_dtype(point_indices, np.int64).ravel()
+        uv = _as_dtype(points_2d, np.float64)        # the reference's pixels are int64 (graph.py:112-113)
         if len(ci) != len(pi):
             raise ValueError("camera_indices and point_indices differ in length")
         if uv.size != 2 * len(ci):

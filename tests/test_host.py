@@ -276,3 +276,18 @@ def test_install_on_the_real_sfm_module():
         assert np.allclose(me.graph.X3d, X_before + 1.0)                                            # write-back of sfm.py:281
     finally:
         S.least_squares, S.compute_residuals, S.create_sparsity_matrix = saved
+
+
+def test_large_host_arrays_are_converted_in_threads_with_identical_values():
+    """The reference's pixel array is int64 (graph.py:112-113): above 2 M elements the cast to float64 runs chunked on
+    threads; values, shape and contiguity are those of np.ascontiguousarray."""
+    import b200ba
+    f = b200ba.bundle_adjustment._as_dtype
+    uv = np.random.default_rng(3).integers(-5, 4000, size=(1_200_000, 2))
+    out = f(uv, np.float64)
+    assert out.dtype == np.float64 and out.shape == uv.shape and out.flags.c_contiguous
+    assert np.array_equal(out, uv.astype(np.float64))
+    assert f(uv.astype(np.float64), np.float64).dtype == np.float64
+    idx = np.arange(3_000_000, dtype=np.int32)
+    assert np.array_equal(f(idx, np.int64), idx.astype(np.int64)) and f(idx, np.int64).dtype == np.int64
+    assert np.array_equal(f([[1, 2], [3, 4]], np.float64), np.array([[1.0, 2.0], [3.0, 4.0]]))
